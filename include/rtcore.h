@@ -1,0 +1,238 @@
+/*
+ * rtcore.h — C-ABI of the B200-native path-tracing core (librtcore.so).
+ *
+ * This is the drop-in boundary for the render hot path of tigert1998/ray-tracing-cuda.
+ * Every entry point cites the reference interface it replaces (paths relative to the
+ * reference tree).  Plain pointers and sizes only; no C++/torch types.
+ *
+ * Conventions
+ *   - every function returns RT_OK (0) or a negative RT_ERR_* code; rt_last_error_string()
+ *     gives the message of the last failure on the calling thread.  The library never
+ *     aborts (the reference CHECK-aborts: utils.cu:143-152); the C++ `Main` wrapper CHECKs.
+ *   - a context is bound to one CUDA device; one context per device; not thread-safe.
+ *   - "h_" pointers are host memory, "d_" pointers are device memory of the context's device.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - there is NO CPU fallback: every compute entry point fails with RT_ERR_CUDA when no
+ *     CUDA device is usable.
+ */
+#ifndef RTCORE_H_
+#define RTCORE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+enum {
+  RT_OK = 0,
+  RT_ERR_INVALID = -1, /* bad argument / call order */
+  RT_ERR_CUDA = -2,    /* CUDA runtime failure (message has cudaGetErrorString) */
+  RT_ERR_NOMEM = -3,
+  RT_ERR_LIMIT = -4,   /* exceeds a documented limit (e.g. HitableList::kMaxHitables) */
+  RT_ERR_NCCL = -5
+};
+
+/* ---- scene description (type-tagged records replacing the virtual object graph) ---------- */
+
+/* Material tags.  Replaces the virtual Material hierarchy (material.cuh:13-20). */
+enum {
+  RT_MAT_LAMBERTIAN = 0,    /* lambertian.cuh:11-29   color = albedo, or texture>=0          */
+  RT_MAT_METAL = 1,         /* metal.cuh:5-19         color = albedo, fuzz (clamped to <=1)   */
+  RT_MAT_DIELECTRIC = 2,    /* dielectric.cuh:5-17    color = attenuation, ior                */
+  RT_MAT_DIFFUSE_LIGHT = 3, /* diffuse_light.cuh:6-18 color = emission, or texture>=0         */
+  RT_MAT_SKY = 4            /* sky.cuh:8-15           gradient miss shader                    */
+};
+
+typedef struct rt_material {
+  int32_t type;
+  int32_t texture; /* -1: ConstantTexture(color) (constant_texture.cuh); >=0: image texture index */
+  float color[3];
+  float fuzz;
+  double ior;
+} rt_material; /* 32 bytes */
+
+/* Top-level hitable tags.  Replaces Hitable subclasses appended to HitableList
+ * (hitable_list.cuh:8-22).  A Parallelepiped (parallelepiped.cuh:16-29) is described as its
+ * six Parallelograms in AddCorner order (parallelepiped.cu:25-32) sharing one `group` id. */
+enum {
+  RT_HIT_SPHERE = 0,        /* sphere.cuh:8-25        p[0]=centre, radius                      */
+  RT_HIT_TRIANGLE = 1,      /* triangle.cuh:7-17      p[0..2]                                  */
+  RT_HIT_PARALLELOGRAM = 2, /* parallelogram.cuh:7-17 p[0..3], p[3]=p[1]+p[2]-p[0] (ctor value) */
+  RT_HIT_SKY = 3,           /* sky.cuh:17-26          hit at t=1e9                             */
+  RT_HIT_MESH = 4           /* bvh.cuh:161-183        BVH<Face<B>,AABB> over meshes[mesh]      */
+};
+
+typedef struct rt_hitable {
+  int32_t type;
+  int32_t material; /* index into materials; for RT_HIT_MESH the mesh-wide material (bvh.cuh:178) */
+  float p[4][3];
+  double radius;
+  int32_t mesh;  /* RT_HIT_MESH: index into meshes, else -1 */
+  int32_t group; /* >=0: id of the enclosing Parallelepiped; -1 otherwise (informational) */
+} rt_hitable; /* 72 bytes */
+
+/* A triangle mesh in the reference's Face<> layout (bvh.cuh:21-66): has_texcoord=0 -> 9 floats
+ * per face (3 positions); has_texcoord=1 -> 15 floats (3 positions, then 3 uv pairs).
+ * Faces are given in caller order; the library reproduces the reference build's in-place
+ * stable sort by positions_[0].x for n_faces > 2048 (bvh.cuh:96-98,113-121), and face indices
+ * reported by rt_trace_closest refer to that post-sort order. */
+typedef struct rt_mesh {
+  const float *h_faces;
+  int32_t n_faces;
+  int32_t has_texcoord;
+} rt_mesh;
+
+/* RGBA8 image sampled like the reference's cudaTextureObject_t (image_texture.cu:17-38):
+ * normalized coords, point filter, wrap addressing, uchar4 -> float/255, v flipped by caller. */
+typedef struct rt_texture {
+  const uint8_t *h_rgba;
+  int32_t height, width;
+  int64_t pitch_bytes;
+} rt_texture;
+
+/* Camera frame: the seven vectors + lens fields the reference Camera holds (camera.cuh:12-14). */
+typedef struct rt_camera {
+  float position[3], lower_left_corner[3], horizontal[3], vertical[3], u[3], v[3], w[3];
+  int32_t is_defocus;
+  double lens_radius;
+} rt_camera; /* 96 bytes */
+
+typedef struct rt_scene_desc {
+  const rt_hitable *hitables;
+  int32_t n_hitables; /* <= 1024 after grouping, as HitableList::kMaxHitables (hitable_list.cuh:10) */
+  const rt_material *materials;
+  int32_t n_materials;
+  const rt_mesh *meshes;
+  int32_t n_meshes;
+  const rt_texture *textures;
+  int32_t n_textures;
+} rt_scene_desc;
+
+/* ---- results ------------------------------------------------------------------------------ */
+
+/* Closest-hit record of the parity hook.  `t` is the double the reference stores in
+ * HitRecord::t (hitable.cuh:13-17).  obj = index in the top-level list (Append order, a
+ * Parallelepiped counting as its 6 parallelograms); sub = 0/1 for the two triangles of a
+ * parallelogram, the post-sort face index for a mesh, 0 otherwise.  obj = -1: no hit. */
+typedef struct rt_hit {
+  double t;
+  int32_t obj;
+  int32_t sub;
+  float u, v; /* HitRecord::u,v narrowed to float (sky leaves them undefined: reported 0) */
+  float normal[3];
+  int32_t material;
+} rt_hit; /* 40 bytes */
+
+typedef struct rt_build_stats {
+  int32_t n_prims;      /* leaf primitives in the unified BVH (spheres+triangles+parallelograms+faces) */
+  int32_t n_nodes;      /* 32-byte nodes */
+  int32_t n_spheres, n_quads, n_tris;
+  int32_t max_depth;
+  float build_ms;       /* device time of the BVH build (CUDA events) */
+  float upload_ms;
+  float sah_cost;
+} rt_build_stats;
+
+typedef struct rt_render_stats {
+  uint64_t samples;       /* camera samples started */
+  uint64_t rays;          /* closest-hit queries executed by this core */
+  uint64_t rays_ref_equiv;/* queries the reference loop would issue for the same paths (ray_tracing.cu:22) */
+  uint64_t node_visits;   /* only when built with RT_STATS=1, else 0 */
+  uint64_t prim_tests;
+  uint32_t iterations;    /* wavefront iterations */
+  uint32_t kernel_launches;
+  float render_ms;        /* device time, CUDA events on `stream` */
+  float extend_ms, shade_ms; /* per-stage device time when profiling is enabled, else 0 */
+} rt_render_stats;
+
+/* ---- entry points -------------------------------------------------------------------------- */
+
+typedef struct rt_ctx rt_ctx;
+
+int rt_abi_version(void);
+const char *rt_last_error_string(void);
+
+/* Replaces the cudaMalloc block at the top of Main / DistributedMain (utils.cu:139-142,194-197). */
+int rt_ctx_create(int device, rt_ctx **out);
+int rt_ctx_destroy(rt_ctx *ctx);
+
+/* Replaces scene construction by device-side `new` + HitableList::Append (hitable_list.cu:27-29)
+ * and the single-thread BVHNode build (bvh.cuh:113-121): copies the description to the device,
+ * flattens it into SoA records and builds the unified LBVH on the device. */
+int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *desc, rt_build_stats *stats /*nullable*/);
+
+/* Replaces the Camera constructors (camera.cu:6-47). rt_camera_look_at computes the frame with
+ * the reference's arithmetic on the host; aperture<0 selects the pinhole constructor. */
+int rt_camera_set(rt_ctx *ctx, const rt_camera *cam);
+int rt_camera_look_at(const float position[3], const float look_at[3], const float up[3],
+                      double field_of_view, double width_height_aspect, double aperture,
+                      double focus_distance, rt_camera *out);
+
+/* Parity hook: replaces HitableList::Hit (hitable_list.cu:7-25) on explicit rays.
+ * rays = n x 6 floats (position xyz, direction xyz); the direction is used as stored (callers
+ * pass Ray::direction_, i.e. already normalized by Ray::Ray, ray.cu:8-11).
+ * mode 0: unified-BVH traversal (product path); mode 1: brute force over every primitive. */
+int rt_trace_closest_host(rt_ctx *ctx, const float *h_rays, int64_t n, double t_from, double t_to,
+                          int mode, rt_hit *h_hits);
+int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t n, double t_from, double t_to,
+                            int mode, rt_hit *d_hits, void *stream);
+
+/* Pixel-centre primary rays, as PathTracing would form them with both jitters = 0.5
+ * (ray_tracing.cu:68-74).  h_rays = height*width*6 floats, row-major like out_image. */
+int rt_primary_rays_host(rt_ctx *ctx, int height, int width, float *h_rays);
+
+typedef struct rt_render_params {
+  int32_t height, width;
+  int32_t spp_begin, spp_count; /* global sample indices [spp_begin, spp_begin+spp_count) per pixel */
+  int32_t max_depth;            /* TRACE_DEPTH_LIMIT (ray_tracing.cu:10); reference value 10 */
+  int32_t flags;                /* RT_RENDER_* */
+  uint64_t seed;                /* Philox key */
+} rt_render_params;
+
+enum {
+  RT_RENDER_DEFAULT = 0,
+  RT_RENDER_CLEAR = 1,     /* zero the accumulation buffer first */
+  RT_RENDER_PROFILE = 2,   /* per-stage event timing (serialises stages) */
+  RT_RENDER_FUSED = 4,     /* fused extend+shade kernel per bounce */
+  RT_RENDER_NO_SORT = 8    /* single shade queue instead of material-sorted queues */
+};
+
+/* Replaces the PathTracing<<<>>> launch with post_processing=false (ray_tracing.cu:56-85,
+ * utils.cu:220-221): adds the radiance SUM of the requested samples into d_accum_rgb
+ * (height*width*3 floats, the reference's glm::vec3 image layout). */
+int rt_render(rt_ctx *ctx, const rt_render_params *params, float *d_accum_rgb,
+              rt_render_stats *stats /*nullable*/, void *stream);
+
+/* Replaces the post-processing tail of PathTracing (ray_tracing.cu:78-83) and the host loops in
+ * GatherImageData / WriteImage (utils.cu:126-129, 87-96): out = sqrt(clamp(accum/spp_total,0,1));
+ * either output may be NULL.  d_rgb8 gets trunc(out*255) like WriteImage. */
+int rt_resolve(rt_ctx *ctx, const float *d_accum_rgb, int height, int width, int spp_total,
+               float *d_rgb /*nullable*/, uint8_t *d_rgb8 /*nullable*/, void *stream);
+
+/* End-to-end convenience through host buffers: commit-independent render + resolve + D2H.
+ * h_accum_rgb (nullable) receives the raw sums, h_rgb (nullable) the post-processed floats. */
+int rt_render_host(rt_ctx *ctx, const rt_render_params *params, float *h_accum_rgb, float *h_rgb,
+                   rt_render_stats *stats /*nullable*/);
+
+/* Replaces GetWorkload (utils.cu:111-113): samples of rank `rank`, and its first global index. */
+int rt_get_workload(int rank, int world_size, int spp, int *spp_begin /*nullable*/);
+
+/* Replaces D2H + MPI_Reduce in GatherImageData (utils.cu:115-125,232-238): in-place SUM of the
+ * accumulation buffers of all ranks to `root` with one ncclReduce on `stream`.
+ * `nccl_comm` is an ncclComm_t passed as void*. */
+int rt_reduce(rt_ctx *ctx, void *nccl_comm, float *d_accum_rgb, int64_t n_floats, int root,
+              void *stream);
+
+/* Image writers replacing stbi_write_jpg in WriteImage (utils.cu:87-96). */
+int rt_write_jpeg(const char *path, int width, int height, const uint8_t *h_rgb8, int quality);
+int rt_write_ppm(const char *path, int width, int height, const uint8_t *h_rgb8);
+int rt_write_pfm(const char *path, int width, int height, const float *h_rgb);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTCORE_H_ */
