@@ -197,8 +197,9 @@ enum {
   RT_RENDER_DEFAULT = 0,
   RT_RENDER_CLEAR = 1,     /* zero the accumulation buffer first */
   RT_RENDER_PROFILE = 2,   /* per-stage event timing (serialises stages) */
-  RT_RENDER_FUSED = 4,     /* fused extend+shade kernel per bounce */
-  RT_RENDER_NO_SORT = 8    /* single shade queue instead of material-sorted queues */
+  RT_RENDER_FUSED = 4,     /* force the fused persistent-path kernel (paths regenerated in registers) */
+  RT_RENDER_NO_SORT = 8,   /* wavefront: single shade queue instead of material-sorted queues */
+  RT_RENDER_WAVEFRONT = 16 /* force the wavefront pipeline (logic/shade -> extend over compacted queues) */
 };
 
 /* Replaces the PathTracing<<<>>> launch with post_processing=false (ray_tracing.cu:56-85,
@@ -226,6 +227,14 @@ int rt_get_workload(int rank, int world_size, int spp, int *spp_begin /*nullable
  * `nccl_comm` is an ncclComm_t passed as void*. */
 int rt_reduce(rt_ctx *ctx, void *nccl_comm, float *d_accum_rgb, int64_t n_floats, int root,
               void *stream);
+
+/* Communicator helpers for callers that have no ncclComm_t of their own (the reference ranks talk
+ * through MPI_COMM_WORLD, utils.cu:118-125): rank 0 creates a 128-byte ncclUniqueId, the caller
+ * ships it to the other ranks with whatever plumbing it has (torch.distributed, a file, MPI), and
+ * every rank binds a communicator to its context.  rt_reduce(ctx, NULL, ...) then uses it. */
+int rt_nccl_unique_id(char out_id[128]);
+int rt_nccl_init(rt_ctx *ctx, const char id[128], int world_size, int rank);
+int rt_nccl_destroy(rt_ctx *ctx);
 
 /* Image writers replacing stbi_write_jpg in WriteImage (utils.cu:87-96). */
 int rt_write_jpeg(const char *path, int width, int height, const uint8_t *h_rgb8, int quality);

@@ -14,6 +14,7 @@ RT_RENDER_CLEAR = 1
 RT_RENDER_PROFILE = 2
 RT_RENDER_FUSED = 4
 RT_RENDER_NO_SORT = 8
+RT_RENDER_WAVEFRONT = 16
 
 material_dtype = np.dtype(
     {

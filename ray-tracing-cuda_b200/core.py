@@ -47,6 +47,9 @@ def lib():
     L.rt_render_host.argtypes = [vp, C.POINTER(abi.RtRenderParams), vp, vp, C.POINTER(abi.RtRenderStats)]
     L.rt_get_workload.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]
     L.rt_reduce.argtypes = [vp, vp, vp, i64, C.c_int, vp]
+    L.rt_nccl_unique_id.argtypes = [vp]
+    L.rt_nccl_init.argtypes = [vp, vp, C.c_int, C.c_int]
+    L.rt_nccl_destroy.argtypes = [vp]
     L.rt_write_jpeg.argtypes = [C.c_char_p, C.c_int, C.c_int, vp, C.c_int]
     L.rt_write_ppm.argtypes = [C.c_char_p, C.c_int, C.c_int, vp]
     L.rt_write_pfm.argtypes = [C.c_char_p, C.c_int, C.c_int, vp]
@@ -143,3 +146,33 @@ class Context:
 
     def reduce(self, nccl_comm, d_accum_ptr, n_floats, root=0, stream=None):
         _check(lib().rt_reduce(self._h, nccl_comm, d_accum_ptr, n_floats, root, stream))
+
+    def nccl_init(self, unique_id, world_size, rank):
+        """Bind an NCCL communicator to this context from a 128-byte ncclUniqueId (see nccl_unique_id)."""
+        buf = C.create_string_buffer(bytes(unique_id), 128)
+        _check(lib().rt_nccl_init(self._h, buf, world_size, rank))
+
+    def nccl_destroy(self):
+        lib().rt_nccl_destroy(self._h)
+
+
+def nccl_unique_id():
+    buf = C.create_string_buffer(128)
+    _check(lib().rt_nccl_unique_id(buf))
+    return buf.raw
+
+
+def write_image(path, rgb8):
+    """WriteImage (utils.cu:87-96): rgb8 uint8 [H, W, 3] -> .jpeg / .jpg / .ppm by extension."""
+    rgb8 = np.ascontiguousarray(rgb8, np.uint8)
+    h, w = rgb8.shape[:2]
+    if path.endswith(".ppm"):
+        _check(lib().rt_write_ppm(path.encode(), w, h, rgb8.ctypes.data))
+    else:
+        _check(lib().rt_write_jpeg(path.encode(), w, h, rgb8.ctypes.data, 100))
+
+
+def write_pfm(path, rgb):
+    rgb = np.ascontiguousarray(rgb, np.float32)
+    h, w = rgb.shape[:2]
+    _check(lib().rt_write_pfm(path.encode(), w, h, rgb.ctypes.data))

@@ -1,0 +1,606 @@
+// rt_build.cu — rt_scene_commit: flattening of the scene description into type-tagged records and
+// the device-side LBVH build (Morton keys -> radix sort -> Karras hierarchy -> bottom-up refit with
+// SAH leaf collapse) emitting 32-byte nodes.
+//
+// Replaces, in the reference: scene construction by device-side `new` + HitableList::Append
+// (hitable_list.cu:27-29), the single-thread BVHNode constructor with its sequential thrust::sort
+// (bvh.cuh:113-121), Face::GetBV (bvh.cuh:71-82) and the virtual object graph as a whole.
+#include <cub/cub.cuh>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+
+#include "rt_internal.h"
+
+namespace rtc {
+
+constexpr int kRefLeafMin = 2048;  // bvh.cuh:105: ranges of <= kMin faces are never sorted
+
+__device__ __forceinline__ uint32_t float_orderable(float f) {
+  uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// ---- mesh faces -> records ---------------------------------------------------------------------
+// Sort key of Face::operator< (bvh.cuh:96-98): positions_[0].x, with -0 == +0 as `<` sees them.
+__global__ void k_face_keys(const float *faces, int stride, int n, uint32_t *keys, uint32_t *vals) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float x = faces[(size_t)i * stride];
+  if (x == 0.0f) x = 0.0f;
+  keys[i] = float_orderable(x);
+  vals[i] = i;
+}
+
+__global__ void k_face_records(const float *faces, int stride, const uint32_t *perm, int n, int obj, uint32_t word,
+                               float4 *recs, float *uv) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int src = perm ? (int)perm[i] : i;
+  const float *f = faces + (size_t)src * stride;
+  V3 p0 = mk(f[0], f[1], f[2]), p1 = mk(f[3], f[4], f[5]), p2 = mk(f[6], f[7], f[8]);
+  V3 e1 = p1 - p0, e2 = p2 - p0;  // utils.cu:54-55
+  recs[3 * (size_t)i + 0] = make_float4(p0.x, p0.y, p0.z, __int_as_float(obj));
+  recs[3 * (size_t)i + 1] = make_float4(e1.x, e1.y, e1.z, __int_as_float(i));
+  recs[3 * (size_t)i + 2] = make_float4(e2.x, e2.y, e2.z, __uint_as_float(word));
+  if (uv) {
+    for (int k = 0; k < 6; k++) uv[6 * (size_t)i + k] = stride == 15 ? f[9 + k] : 0.f;
+  }
+}
+
+// ---- build primitives ----------------------------------------------------------------------------
+__global__ void k_head_flags(const float4 *recs, int n, uint32_t *flags) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t kind = __float_as_uint(recs[3 * (size_t)i + 2].w) & KIND_MASK;
+  flags[i] = (kind == K_TRI || kind == K_QUAD0 || kind == K_SPHERE) ? 1u : 0u;
+}
+__global__ void k_scatter_heads(const uint32_t *flags, const uint32_t *pos, int n, uint32_t *bp_first) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (flags[i]) bp_first[pos[i]] = i;
+}
+
+__device__ __forceinline__ void grow(V3 &lo, V3 &hi, V3 p) {
+  lo = mk(fminf(lo.x, p.x), fminf(lo.y, p.y), fminf(lo.z, p.z));
+  hi = mk(fmaxf(hi.x, p.x), fmaxf(hi.y, p.y), fmaxf(hi.z, p.z));
+}
+__device__ __forceinline__ void rec_bounds(const float4 *recs, size_t k, V3 &lo, V3 &hi) {
+  float4 r0 = recs[3 * k], r1 = recs[3 * k + 1], r2 = recs[3 * k + 2];
+  uint32_t kind = __float_as_uint(r2.w) & KIND_MASK;
+  if (kind == K_SPHERE) {
+    float rad = fabsf(__double2float_ru(fabs(rec_radius(r1))));
+    rad = rad + rad * 1e-5f;
+    grow(lo, hi, xyz(r0) - mk(rad, rad, rad));
+    grow(lo, hi, xyz(r0) + mk(rad, rad, rad));
+  } else {
+    grow(lo, hi, xyz(r0));
+    grow(lo, hi, xyz(r0) + xyz(r1));
+    grow(lo, hi, xyz(r0) + xyz(r2));
+  }
+}
+
+// Padded box per build primitive + centroid bounds of the scene (ordered-int atomics).
+__global__ void k_bp_bounds(const float4 *recs, const uint32_t *bp_first, int n_bp, float4 *bp_lo, float4 *bp_hi,
+                            uint32_t *scene_bounds) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_bp) return;
+  size_t k = bp_first[i];
+  V3 lo = mk(CUDART_INF_F, CUDART_INF_F, CUDART_INF_F), hi = mk(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
+  rec_bounds(recs, k, lo, hi);
+  uint32_t kind = __float_as_uint(recs[3 * k + 2].w) & KIND_MASK;
+  int nrec = 1;
+  if (kind == K_QUAD0) {
+    rec_bounds(recs, k + 1, lo, hi);
+    nrec = 2;
+  }
+  // guard band: MT accepts rays within rounding of the edges; culling must stay conservative
+  float m = fmaxf(fmaxf(hi.x - lo.x, hi.y - lo.y), hi.z - lo.z);
+  m = fmaxf(m, fmaxf(fmaxf(fabsf(lo.x), fabsf(lo.y)), fabsf(lo.z)));
+  m = fmaxf(m, fmaxf(fmaxf(fabsf(hi.x), fabsf(hi.y)), fabsf(hi.z)));
+  float pad = m * 2e-5f + 1e-30f;
+  lo = lo - mk(pad, pad, pad);
+  hi = hi + mk(pad, pad, pad);
+  bp_lo[i] = make_float4(lo.x, lo.y, lo.z, __int_as_float(nrec));
+  bp_hi[i] = make_float4(hi.x, hi.y, hi.z, 0.f);
+  V3 c = (lo + hi) * 0.5f;
+  atomicMin(scene_bounds + 0, float_orderable(c.x));
+  atomicMin(scene_bounds + 1, float_orderable(c.y));
+  atomicMin(scene_bounds + 2, float_orderable(c.z));
+  atomicMax(scene_bounds + 3, float_orderable(c.x));
+  atomicMax(scene_bounds + 4, float_orderable(c.y));
+  atomicMax(scene_bounds + 5, float_orderable(c.z));
+}
+
+__device__ __forceinline__ float orderable_float(uint32_t u) {
+  return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+__device__ __forceinline__ uint64_t expand21(uint64_t v) {
+  v &= 0x1fffffull;
+  v = (v | v << 32) & 0x1f00000000ffffull;
+  v = (v | v << 16) & 0x1f0000ff0000ffull;
+  v = (v | v << 8) & 0x100f00f00f00f00full;
+  v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+  v = (v | v << 2) & 0x1249249249249249ull;
+  return v;
+}
+__global__ void k_morton(const float4 *bp_lo, const float4 *bp_hi, int n_bp, const uint32_t *scene_bounds,
+                         uint64_t *keys, uint32_t *vals) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_bp) return;
+  float4 lo = bp_lo[i], hi = bp_hi[i];
+  float c[3] = {(lo.x + hi.x) * 0.5f, (lo.y + hi.y) * 0.5f, (lo.z + hi.z) * 0.5f};
+  uint64_t q[3];
+  for (int a = 0; a < 3; a++) {
+    float mn = orderable_float(scene_bounds[a]), mx = orderable_float(scene_bounds[3 + a]);
+    double ext = (double)mx - (double)mn;
+    double x = ext > 0 ? ((double)c[a] - (double)mn) / ext : 0.0;
+    x = fmin(fmax(x * 2097152.0, 0.0), 2097151.0);
+    q[a] = (uint64_t)x;
+  }
+  keys[i] = expand21(q[0]) << 2 | expand21(q[1]) << 1 | expand21(q[2]);
+  vals[i] = i;
+}
+
+__global__ void k_sorted_nrec(const float4 *bp_lo, const uint32_t *order, int n_bp, uint32_t *nrec) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_bp) return;
+  nrec[j] = (uint32_t)__float_as_int(bp_lo[order[j]].w);
+}
+
+// Records copied into BVH (Morton) order; single-primitive leaf nodes written; per-leaf SAH data.
+__global__ void k_emit(const float4 *recs_seq, const float *uv_seq, const uint32_t *bp_first, const float4 *bp_lo,
+                       const float4 *bp_hi, const uint32_t *order, const uint32_t *off, int n_bp, float4 *recs,
+                       float *uv, float4 *nodes, float *cost, int *depth) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_bp) return;
+  uint32_t bp = order[j];
+  size_t src = bp_first[bp];
+  uint32_t dst = off[j], n = off[j + 1] - off[j];
+  for (uint32_t r = 0; r < n; r++) {
+    for (int q = 0; q < 3; q++) recs[3 * (size_t)(dst + r) + q] = recs_seq[3 * (src + r) + q];
+    if (uv)
+      for (int q = 0; q < 6; q++) uv[6 * (size_t)(dst + r) + q] = uv_seq[6 * (src + r) + q];
+  }
+  size_t node = (size_t)(n_bp - 1) + j;
+  float4 lo = bp_lo[bp], hi = bp_hi[bp];
+  nodes[2 * node] = make_float4(lo.x, lo.y, lo.z, __uint_as_float(dst));
+  nodes[2 * node + 1] = make_float4(hi.x, hi.y, hi.z, __uint_as_float(LEAF_FLAG | n));
+  cost[node] = (float)n;
+  depth[node] = 1;
+}
+
+// ---- Karras 2012: one thread per internal node ----------------------------------------------------
+__device__ __forceinline__ int lbvh_delta(const uint64_t *keys, int n, int i, int j) {
+  if (j < 0 || j >= n) return -1;
+  uint64_t a = keys[i], b = keys[j];
+  if (a == b) return 64 + __clz(i ^ j);
+  return __clzll(a ^ b);
+}
+__global__ void k_hierarchy(const uint64_t *keys, int n, uint32_t *left, uint32_t *right, uint32_t *parent,
+                            uint2 *range) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n - 1) return;
+  int d = lbvh_delta(keys, n, i, i + 1) - lbvh_delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
+  int dmin = lbvh_delta(keys, n, i, i - d);
+  int lmax = 2;
+  while (lbvh_delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+  int l = 0;
+  for (int t = lmax / 2; t >= 1; t /= 2)
+    if (lbvh_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+  int j = i + l * d;
+  int dnode = lbvh_delta(keys, n, i, j);
+  int s = 0, t = l;
+  do {
+    t = (t + 1) / 2;
+    if (lbvh_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+  } while (t > 1);
+  int gamma = i + s * d + min(d, 0);
+  int lo = min(i, j), hi = max(i, j);
+  uint32_t lc = (lo == gamma) ? (uint32_t)(n - 1 + gamma) : (uint32_t)gamma;
+  uint32_t rc = (hi == gamma + 1) ? (uint32_t)(n - 1 + gamma + 1) : (uint32_t)(gamma + 1);
+  left[i] = lc;
+  right[i] = rc;
+  parent[lc] = i;
+  parent[rc] = i;
+  range[i] = make_uint2((uint32_t)lo, (uint32_t)hi);
+  if (i == 0) parent[0] = 0xffffffffu;
+}
+
+__device__ __forceinline__ float half_area(float4 lo, float4 hi) {
+  float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+  return dx * dy + dy * dz + dz * dx;
+}
+
+// Bottom-up refit: the second thread to reach a node owns it.  Writes the node's box and words;
+// collapses the subtree into a leaf when the SAH says so (records of a subtree are contiguous).
+__global__ void k_refit(const uint32_t *left, const uint32_t *right, const uint32_t *parent, const uint2 *range,
+                        const uint32_t *off, int n, int max_leaf, float c_trav, uint32_t *visits, float4 *nodes,
+                        float *cost, int *depth) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  uint32_t cur = parent[(size_t)(n - 1) + j];
+  while (cur != 0xffffffffu) {
+    __threadfence();
+    if (atomicAdd(visits + cur, 1u) == 0) return;
+    __threadfence();
+    uint32_t lc = left[cur], rc = right[cur];
+    float4 l0 = __ldcg(nodes + 2 * (size_t)lc), l1 = __ldcg(nodes + 2 * (size_t)lc + 1);
+    float4 r0 = __ldcg(nodes + 2 * (size_t)rc), r1 = __ldcg(nodes + 2 * (size_t)rc + 1);
+    float4 lo = make_float4(fminf(l0.x, r0.x), fminf(l0.y, r0.y), fminf(l0.z, r0.z), 0.f);
+    float4 hi = make_float4(fmaxf(l1.x, r1.x), fmaxf(l1.y, r1.y), fmaxf(l1.z, r1.z), 0.f);
+    float a = half_area(lo, hi);
+    float cl = __ldcg(cost + lc), cr = __ldcg(cost + rc);
+    float c_split = a > 0.f ? c_trav + (half_area(l0, l1) * cl + half_area(r0, r1) * cr) / a : c_trav + cl + cr;
+    uint2 rg = range[cur];
+    uint32_t first = off[rg.x], nrec = off[rg.y + 1] - first;
+    float c_leaf = (float)nrec;
+    bool collapse = nrec <= (uint32_t)max_leaf && c_leaf <= c_split;
+    if (collapse) {
+      lo.w = __uint_as_float(first);
+      hi.w = __uint_as_float(LEAF_FLAG | nrec);
+      cost[cur] = c_leaf;
+      depth[cur] = 1;
+    } else {
+      lo.w = __uint_as_float(lc);
+      hi.w = __uint_as_float(rc);
+      cost[cur] = c_split;
+      depth[cur] = 1 + max(__ldcg(depth + lc), __ldcg(depth + rc));
+    }
+    nodes[2 * (size_t)cur] = lo;
+    nodes[2 * (size_t)cur + 1] = hi;
+    cur = parent[cur];
+  }
+}
+
+}  // namespace rtc
+
+// =================================================================================================
+// host side
+// =================================================================================================
+using namespace rtc;
+
+namespace {
+
+inline int nblk(size_t n, int b = 256) { return (int)((n + b - 1) / b); }
+
+struct HostRec {
+  float4 r[3];
+};
+inline float as_f(int32_t i) {
+  float f;
+  memcpy(&f, &i, 4);
+  return f;
+}
+inline float as_fu(uint32_t i) {
+  float f;
+  memcpy(&f, &i, 4);
+  return f;
+}
+inline uint32_t rec_word(uint32_t kind, uint32_t flags, int material) {
+  return kind | flags | ((uint32_t)material << KIND_BITS);
+}
+inline HostRec tri_rec(const float p0[3], const float p1[3], const float p2[3], int obj, int sub, uint32_t word) {
+  HostRec h;
+  // utils.cu:54-55: v0v1 = p1 - p0, v0v2 = p2 - p0 (single float subtractions)
+  h.r[0] = make_float4(p0[0], p0[1], p0[2], as_f(obj));
+  h.r[1] = make_float4(p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2], as_f(sub));
+  h.r[2] = make_float4(p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2], as_fu(word));
+  return h;
+}
+
+}  // namespace
+
+extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_stats *stats) {
+  if (!ctx || !d) {
+    set_error("rt_scene_commit: null argument");
+    return RT_ERR_INVALID;
+  }
+  if (d->n_hitables < 0 || d->n_materials < 0 || (d->n_hitables > 0 && !d->hitables) ||
+      (d->n_materials > 0 && !d->materials)) {
+    set_error("rt_scene_commit: bad counts");
+    return RT_ERR_INVALID;
+  }
+  RT_CUDA(cudaSetDevice(ctx->device));
+  ctx->has_scene = false;
+  cudaStream_t st = 0;
+  RT_CUDA(cudaEventRecord(ctx->ev0, st));
+
+  // ---- materials -------------------------------------------------------------------------------
+  std::vector<DMaterial> hm(std::max(d->n_materials, 1));
+  for (int i = 0; i < d->n_materials; i++) {
+    const rt_material &m = d->materials[i];
+    if (m.texture >= d->n_textures) {
+      set_error("rt_scene_commit: material texture index out of range");
+      return RT_ERR_INVALID;
+    }
+    hm[i].color_fuzz = make_float4(m.color[0], m.color[1], m.color[2], m.fuzz);
+    hm[i].type = m.type;
+    hm[i].texture = m.texture;
+    hm[i].eta_in = (float)m.ior / 1.0f;
+    hm[i].eta_out = 1.0f / (float)m.ior;
+  }
+  RT_CUDA(ctx->mats.reserve(hm.size() * sizeof(DMaterial)));
+  RT_CUDA(cudaMemcpyAsync(ctx->mats.p, hm.data(), hm.size() * sizeof(DMaterial), cudaMemcpyHostToDevice, st));
+
+  // ---- textures --------------------------------------------------------------------------------
+  for (void *p : ctx->tex_allocs) cudaFree(p);
+  ctx->tex_allocs.clear();
+  std::vector<DTexture> ht(std::max(d->n_textures, 1));
+  for (int i = 0; i < d->n_textures; i++) {
+    const rt_texture &t = d->textures[i];
+    if (!t.h_rgba || t.height <= 0 || t.width <= 0 || t.pitch_bytes < (int64_t)t.width * 4) {
+      set_error("rt_scene_commit: bad texture");
+      return RT_ERR_INVALID;
+    }
+    void *p = nullptr;
+    size_t bytes = (size_t)t.pitch_bytes * t.height;
+    RT_CUDA(cudaMalloc(&p, bytes));
+    ctx->tex_allocs.push_back(p);
+    RT_CUDA(cudaMemcpyAsync(p, t.h_rgba, bytes, cudaMemcpyHostToDevice, st));
+    ht[i].rgba = (const uint8_t *)p;
+    ht[i].height = t.height;
+    ht[i].width = t.width;
+    ht[i].pitch = t.pitch_bytes;
+  }
+  RT_CUDA(ctx->textures.reserve(ht.size() * sizeof(DTexture)));
+  RT_CUDA(cudaMemcpyAsync(ctx->textures.p, ht.data(), ht.size() * sizeof(DTexture), cudaMemcpyHostToDevice, st));
+
+  // ---- sequential record list (Append order) ----------------------------------------------------
+  size_t n_seq = 0;
+  bool any_uv = false;
+  int sky_obj = -1, sky_mat = -1, n_spheres = 0, n_quads = 0, n_tris = 0;
+  for (int i = 0; i < d->n_hitables; i++) {
+    const rt_hitable &h = d->hitables[i];
+    if (h.material < 0 || h.material >= d->n_materials) {
+      set_error("rt_scene_commit: hitable material index out of range");
+      return RT_ERR_INVALID;
+    }
+    switch (h.type) {
+      case RT_HIT_SPHERE: n_seq += 1; n_spheres++; break;
+      case RT_HIT_TRIANGLE: n_seq += 1; n_tris++; break;
+      case RT_HIT_PARALLELOGRAM: n_seq += 2; n_quads++; break;
+      case RT_HIT_SKY:
+        n_seq += 1;
+        if (sky_obj < 0) {
+          sky_obj = i;
+          sky_mat = h.material;
+        }
+        break;
+      case RT_HIT_MESH:
+        if (h.mesh < 0 || h.mesh >= d->n_meshes || d->meshes[h.mesh].n_faces < 0 ||
+            (d->meshes[h.mesh].n_faces > 0 && !d->meshes[h.mesh].h_faces)) {
+          set_error("rt_scene_commit: bad mesh reference");
+          return RT_ERR_INVALID;
+        }
+        n_seq += (size_t)d->meshes[h.mesh].n_faces;
+        n_tris += d->meshes[h.mesh].n_faces;
+        any_uv |= d->meshes[h.mesh].has_texcoord != 0;
+        break;
+      default:
+        set_error("rt_scene_commit: unknown hitable type");
+        return RT_ERR_INVALID;
+    }
+  }
+  if (n_seq >= 0x7fffffffull / 4) {
+    set_error("rt_scene_commit: too many primitives");
+    return RT_ERR_LIMIT;
+  }
+  RT_CUDA(ctx->recs_seq.reserve(std::max<size_t>(n_seq, 1) * 48));
+  if (any_uv) {
+    RT_CUDA(ctx->face_uv_seq.reserve(n_seq * 24));
+    RT_CUDA(cudaMemsetAsync(ctx->face_uv_seq.p, 0, n_seq * 24, st));
+  }
+  float4 *recs_seq = ctx->recs_seq.as<float4>();
+  float *uv_seq = any_uv ? ctx->face_uv_seq.as<float>() : nullptr;
+
+  std::vector<HostRec> run;
+  size_t run_start = 0, pos = 0;
+  auto flush = [&]() -> cudaError_t {
+    cudaError_t e = cudaSuccess;
+    if (!run.empty())
+      e = cudaMemcpy(recs_seq + 3 * run_start, run.data(), run.size() * sizeof(HostRec), cudaMemcpyHostToDevice);
+    run.clear();
+    return e;
+  };
+  for (int i = 0; i < d->n_hitables; i++) {
+    const rt_hitable &h = d->hitables[i];
+    if (run.empty()) run_start = pos;
+    switch (h.type) {
+      case RT_HIT_SPHERE: {
+        HostRec r;
+        uint64_t rb;
+        memcpy(&rb, &h.radius, 8);
+        r.r[0] = make_float4(h.p[0][0], h.p[0][1], h.p[0][2], as_f(i));
+        r.r[1] = make_float4(as_fu((uint32_t)rb), as_fu((uint32_t)(rb >> 32)), 0.f, as_f(0));
+        r.r[2] = make_float4(0.f, 0.f, 0.f, as_fu(rec_word(K_SPHERE, 0, h.material)));
+        run.push_back(r);
+        pos += 1;
+        break;
+      }
+      case RT_HIT_TRIANGLE:
+        run.push_back(tri_rec(h.p[0], h.p[1], h.p[2], i, 0, rec_word(K_TRI, FLAG_BARY, h.material)));
+        pos += 1;
+        break;
+      case RT_HIT_PARALLELOGRAM:
+        run.push_back(tri_rec(h.p[0], h.p[1], h.p[2], i, 0, rec_word(K_QUAD0, 0, h.material)));
+        run.push_back(tri_rec(h.p[1], h.p[2], h.p[3], i, 1, rec_word(K_QUAD1, 0, h.material)));
+        pos += 2;
+        break;
+      case RT_HIT_SKY: {
+        HostRec r;
+        r.r[0] = make_float4(0.f, 0.f, 0.f, as_f(i));
+        r.r[1] = make_float4(0.f, 0.f, 0.f, as_f(0));
+        r.r[2] = make_float4(0.f, 0.f, 0.f, as_fu(rec_word(K_SKY, 0, h.material)));
+        run.push_back(r);
+        pos += 1;
+        break;
+      }
+      case RT_HIT_MESH: {
+        RT_CUDA(flush());
+        const rt_mesh &m = d->meshes[h.mesh];
+        int n = m.n_faces, stride = m.has_texcoord ? 15 : 9;
+        if (n > 0) {
+          size_t bytes = (size_t)n * stride * 4;
+          RT_CUDA(ctx->scratch[0].reserve(bytes));
+          RT_CUDA(cudaMemcpyAsync(ctx->scratch[0].p, m.h_faces, bytes, cudaMemcpyHostToDevice, st));
+          const uint32_t *perm = nullptr;
+          if (n > kRefLeafMin) {  // bvh.cuh:116-117: stable sort on positions_[0].x
+            RT_CUDA(ctx->scratch[1].reserve((size_t)n * 4));
+            RT_CUDA(ctx->scratch[2].reserve((size_t)n * 4));
+            RT_CUDA(ctx->scratch[3].reserve((size_t)n * 4));
+            RT_CUDA(ctx->scratch[4].reserve((size_t)n * 4));
+            k_face_keys<<<nblk(n), 256, 0, st>>>(ctx->scratch[0].as<float>(), stride, n, ctx->scratch[1].as<uint32_t>(),
+                                                 ctx->scratch[2].as<uint32_t>());
+            size_t tmp = 0;
+            cub::DeviceRadixSort::SortPairs(nullptr, tmp, ctx->scratch[1].as<uint32_t>(), ctx->scratch[3].as<uint32_t>(),
+                                            ctx->scratch[2].as<uint32_t>(), ctx->scratch[4].as<uint32_t>(), n, 0, 32, st);
+            RT_CUDA(ctx->scratch[5].reserve(tmp));
+            RT_CUDA(cub::DeviceRadixSort::SortPairs(ctx->scratch[5].p, tmp, ctx->scratch[1].as<uint32_t>(),
+                                                    ctx->scratch[3].as<uint32_t>(), ctx->scratch[2].as<uint32_t>(),
+                                                    ctx->scratch[4].as<uint32_t>(), n, 0, 32, st));
+            perm = ctx->scratch[4].as<uint32_t>();
+          }
+          k_face_records<<<nblk(n), 256, 0, st>>>(ctx->scratch[0].as<float>(), stride, perm, n, i,
+                                                  rec_word(K_TRI, 0, h.material), recs_seq + 3 * pos,
+                                                  uv_seq ? uv_seq + 6 * pos : nullptr);
+          RT_CUDA(cudaGetLastError());
+          RT_CUDA(cudaStreamSynchronize(st));  // scratch[0] is reused by the next mesh
+        }
+        pos += (size_t)n;
+        break;
+      }
+    }
+  }
+  RT_CUDA(flush());
+
+  // ---- build primitives -------------------------------------------------------------------------
+  int n_bp = 0;
+  DevBuf *S = ctx->scratch;
+  if (n_seq > 0) {
+    RT_CUDA(S[1].reserve((n_seq + 1) * 4));
+    RT_CUDA(S[2].reserve((n_seq + 1) * 4));
+    k_head_flags<<<nblk(n_seq), 256, 0, st>>>(recs_seq, (int)n_seq, S[1].as<uint32_t>());
+    size_t tmp = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp, S[1].as<uint32_t>(), S[2].as<uint32_t>(), (int)n_seq, st);
+    RT_CUDA(S[5].reserve(tmp));
+    RT_CUDA(cub::DeviceScan::ExclusiveSum(S[5].p, tmp, S[1].as<uint32_t>(), S[2].as<uint32_t>(), (int)n_seq, st));
+    uint32_t last_flag = 0, last_pos = 0;
+    RT_CUDA(cudaMemcpyAsync(&last_flag, S[1].as<uint32_t>() + n_seq - 1, 4, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(&last_pos, S[2].as<uint32_t>() + n_seq - 1, 4, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    n_bp = (int)(last_flag + last_pos);
+  }
+  size_t n_recs = 0;
+  int n_nodes = 0, max_depth = 0;
+  float sah = 0.f;
+  uint32_t root_words[2] = {0, LEAF_FLAG};
+  if (n_bp > 0) {
+    const char *env = getenv("RT_MAX_LEAF");
+    int max_leaf = env ? std::max(1, atoi(env)) : 4;
+    env = getenv("RT_SAH_CT");
+    float c_trav = env ? (float)atof(env) : 1.2f;
+    // S[3] bp_first, S[6] bp_lo, S[7] bp_hi, S[8] scene bounds + keys, S[9] vals ...
+    RT_CUDA(S[3].reserve((size_t)n_bp * 4));
+    k_scatter_heads<<<nblk(n_seq), 256, 0, st>>>(S[1].as<uint32_t>(), S[2].as<uint32_t>(), (int)n_seq,
+                                                 S[3].as<uint32_t>());
+    RT_CUDA(S[6].reserve((size_t)n_bp * 16));
+    RT_CUDA(S[7].reserve((size_t)n_bp * 16));
+    RT_CUDA(S[10].reserve(32));
+    uint32_t binit[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0, 0, 0};
+    RT_CUDA(cudaMemcpyAsync(S[10].p, binit, sizeof(binit), cudaMemcpyHostToDevice, st));
+    k_bp_bounds<<<nblk(n_bp), 256, 0, st>>>(recs_seq, S[3].as<uint32_t>(), n_bp, S[6].as<float4>(), S[7].as<float4>(),
+                                            S[10].as<uint32_t>());
+    // keys/vals double buffers: S[8] = keys in | keys out, S[9] = vals in | vals out
+    RT_CUDA(S[8].reserve((size_t)n_bp * 16));
+    RT_CUDA(S[9].reserve((size_t)n_bp * 8));
+    uint64_t *keys_in = S[8].as<uint64_t>(), *keys = keys_in + n_bp;
+    uint32_t *vals_in = S[9].as<uint32_t>(), *order = vals_in + n_bp;
+    k_morton<<<nblk(n_bp), 256, 0, st>>>(S[6].as<float4>(), S[7].as<float4>(), n_bp, S[10].as<uint32_t>(), keys_in,
+                                         vals_in);
+    size_t tmp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp, keys_in, keys, vals_in, order, n_bp, 0, 63, st);
+    RT_CUDA(S[5].reserve(tmp));
+    RT_CUDA(cub::DeviceRadixSort::SortPairs(S[5].p, tmp, keys_in, keys, vals_in, order, n_bp, 0, 63, st));
+    // record offsets of the sorted primitives: S[1] nrec, S[2] off (n_bp + 1)
+    RT_CUDA(S[1].reserve(((size_t)n_bp + 1) * 4));
+    RT_CUDA(S[2].reserve(((size_t)n_bp + 1) * 4));
+    RT_CUDA(cudaMemsetAsync(S[1].p, 0, ((size_t)n_bp + 1) * 4, st));
+    k_sorted_nrec<<<nblk(n_bp), 256, 0, st>>>(S[6].as<float4>(), order, n_bp, S[1].as<uint32_t>());
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp, S[1].as<uint32_t>(), S[2].as<uint32_t>(), n_bp + 1, st);
+    RT_CUDA(S[5].reserve(tmp));
+    RT_CUDA(cub::DeviceScan::ExclusiveSum(S[5].p, tmp, S[1].as<uint32_t>(), S[2].as<uint32_t>(), n_bp + 1, st));
+    uint32_t total = 0;
+    RT_CUDA(cudaMemcpyAsync(&total, S[2].as<uint32_t>() + n_bp, 4, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    n_recs = total;
+    n_nodes = 2 * n_bp - 1;
+    RT_CUDA(ctx->recs.reserve(n_recs * 48));
+    RT_CUDA(ctx->nodes.reserve((size_t)n_nodes * 32));
+    if (any_uv) RT_CUDA(ctx->face_uv.reserve(n_recs * 24));
+    // S[0] cost | depth, S[4] left | right | parent, S[11] range | visits
+    RT_CUDA(S[0].reserve((size_t)n_nodes * 8));
+    float *cost = S[0].as<float>();
+    int *depth = (int *)(cost + n_nodes);
+    k_emit<<<nblk(n_bp), 256, 0, st>>>(recs_seq, uv_seq, S[3].as<uint32_t>(), S[6].as<float4>(), S[7].as<float4>(),
+                                       order, S[2].as<uint32_t>(), n_bp, ctx->recs.as<float4>(),
+                                       any_uv ? ctx->face_uv.as<float>() : nullptr, ctx->nodes.as<float4>(), cost,
+                                       depth);
+    if (n_bp > 1) {
+      RT_CUDA(S[4].reserve(((size_t)n_bp * 2 + (size_t)n_nodes) * 4));
+      uint32_t *left = S[4].as<uint32_t>(), *right = left + n_bp, *parent = right + n_bp;
+      RT_CUDA(S[11].reserve((size_t)n_bp * 12));
+      uint2 *range = S[11].as<uint2>();
+      uint32_t *visits = (uint32_t *)(range + n_bp);
+      RT_CUDA(cudaMemsetAsync(visits, 0, (size_t)n_bp * 4, st));
+      k_hierarchy<<<nblk(n_bp - 1), 256, 0, st>>>(keys, n_bp, left, right, parent, range);
+      k_refit<<<nblk(n_bp), 256, 0, st>>>(left, right, parent, range, S[2].as<uint32_t>(), n_bp, max_leaf, c_trav,
+                                          visits, ctx->nodes.as<float4>(), cost, depth);
+    }
+    RT_CUDA(cudaGetLastError());
+    float4 root[2];
+    RT_CUDA(cudaMemcpyAsync(root, ctx->nodes.p, 32, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(&sah, cost, 4, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(&max_depth, depth, 4, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    memcpy(&root_words[0], &root[0].w, 4);
+    memcpy(&root_words[1], &root[1].w, 4);
+  }
+  RT_CUDA(cudaEventRecord(ctx->ev1, st));
+  RT_CUDA(cudaEventSynchronize(ctx->ev1));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+
+  DScene &s = ctx->scene;
+  s.nodes = ctx->nodes.as<float4>();
+  s.recs = ctx->recs.as<float4>();
+  s.recs_seq = recs_seq;
+  s.face_uv = any_uv ? ctx->face_uv.as<float>() : nullptr;
+  s.face_uv_seq = uv_seq;
+  s.mats = ctx->mats.as<DMaterial>();
+  s.textures = ctx->textures.as<DTexture>();
+  s.root_a = root_words[0];
+  s.root_b = root_words[1];
+  s.n_recs = (int)n_recs;
+  s.n_recs_seq = (int)n_seq;
+  s.n_nodes = n_nodes;
+  s.sky_obj = sky_obj;
+  s.sky_mat = sky_mat;
+  s.has_spheres = n_spheres > 0;
+  ctx->has_scene = true;
+
+  rt_build_stats &bs = ctx->build_stats;
+  bs.n_prims = n_bp;
+  bs.n_nodes = n_nodes;
+  bs.n_spheres = n_spheres;
+  bs.n_quads = n_quads;
+  bs.n_tris = n_tris;
+  bs.max_depth = max_depth;
+  bs.build_ms = ms;
+  bs.upload_ms = 0.f;
+  bs.sah_cost = sah;
+  if (stats) *stats = bs;
+  return RT_OK;
+}

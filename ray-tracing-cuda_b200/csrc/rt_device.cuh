@@ -1,0 +1,691 @@
+// rt_device.cuh — device-side data layout and arithmetic of the B200 path-tracing core.
+//
+// Everything that decides a hit or a colour is written in the reference's expression order with
+// one IEEE operation per source operation: this translation unit set is compiled with
+// --fmad=false, so `a*b+c` is FMUL+FADD exactly like the reference built with --fmad=false (and
+// like oracle/rt_oracle.cpp built with -ffp-contract=off).  Box culling, which only has to be
+// conservative, is free to use explicit __fmaf_rn.
+//
+// glm 0.9.9.8 definitions the reference relies on (third_party/glm/glm/detail/func_geometric.inl):
+//   dot :47-55   cross :65-77   normalize :80-89 (v * inversesqrt, func_exponential.inl:134-139)
+//   reflect :102-109   refract :111-123
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+#include "../../include/rtcore.h"
+
+namespace rtc {
+
+// ------------------------------------------------------------------------------------------------
+// vec3 in glm's expression order
+// ------------------------------------------------------------------------------------------------
+struct V3 {
+  float x, y, z;
+};
+__host__ __device__ __forceinline__ V3 mk(float x, float y, float z) { return V3{x, y, z}; }
+__host__ __device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__host__ __device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__host__ __device__ __forceinline__ V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
+__host__ __device__ __forceinline__ V3 operator*(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__host__ __device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+__host__ __device__ __forceinline__ V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+__host__ __device__ __forceinline__ float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__host__ __device__ __forceinline__ V3 cross(V3 x, V3 y) {
+  return mk(x.y * y.z - y.y * x.z, x.z * y.x - y.z * x.x, x.x * y.y - y.x * x.y);
+}
+__host__ __device__ __forceinline__ float length(V3 v) { return sqrtf(dot(v, v)); }
+__host__ __device__ __forceinline__ V3 normalize(V3 v) { return v * (1.0f / sqrtf(dot(v, v))); }
+__host__ __device__ __forceinline__ V3 reflect(V3 I, V3 N) { return I - N * dot(N, I) * 2.0f; }
+__host__ __device__ __forceinline__ V3 refract(V3 I, V3 N, float eta) {
+  float const d = dot(N, I);
+  float const k = 1.0f - eta * eta * (1.0f - d * d);
+  return (k >= 0.0f) ? (eta * I - (eta * d + sqrtf(k)) * N) : mk(0.f, 0.f, 0.f);
+}
+__host__ __device__ __forceinline__ V3 xyz(float4 a) { return mk(a.x, a.y, a.z); }
+
+// ------------------------------------------------------------------------------------------------
+// Records (48 B = 3 x float4): the type-tagged SoA replacement of the virtual Hitable objects.
+//   r0 = { a.xyz , obj  }   r1 = { b.xyz , sub }   r2 = { c.xyz , kind | flags | material << 4 }
+// kind TRI   : a = v0, b = v1 - v0, c = v2 - v0                 (Triangle, Face<>: utils.cu:54-55)
+// kind QUAD0 : first triangle (p0,p1,p2) of a Parallelogram; the next record is its QUAD1
+// kind QUAD1 : second triangle (p1,p2,p3)                        (parallelogram.cu:25-41)
+// kind SPHERE: a = centre, b.x/b.y = bit halves of the double radius (sphere.cuh:20)
+// kind SKY   : no geometry; only present in the sequential list     (sky.cu:18-27)
+// ------------------------------------------------------------------------------------------------
+enum : uint32_t { K_TRI = 0, K_QUAD0 = 1, K_QUAD1 = 2, K_SPHERE = 3, K_SKY = 4 };
+constexpr uint32_t KIND_BITS = 4, KIND_MASK = 7;
+constexpr uint32_t FLAG_BARY = 8;  // top-level Triangle: HitRecord::u,v are the barycentrics (triangle.cu:11-19)
+constexpr uint32_t LEAF_FLAG = 0x80000000u;
+constexpr int REC_NONE = -1, REC_SKY = -2;
+constexpr int STACK_SIZE = 64;
+
+struct DMaterial {  // 32 B, two float4 loads
+  float4 color_fuzz;  // albedo / attenuation / emission, Metal fuzz
+  int32_t type;       // RT_MAT_*
+  int32_t texture;    // -1: constant colour
+  float eta_in;       // (float)ior / 1.0f   inner -> outer   dielectric.cu:27-28
+  float eta_out;      // 1.0f / (float)ior   outer -> inner   dielectric.cu:36-37
+};
+
+struct DTexture {
+  const uint8_t *rgba;
+  int32_t height, width;
+  int64_t pitch;
+};
+
+struct DScene {
+  const float4 *nodes;     // 32-byte nodes: {lo.xyz, a}, {hi.xyz, b}
+  const float4 *recs;      // records in BVH (Morton) order, 3 float4 each
+  const float4 *recs_seq;  // records in list order (Append order; faces in post-sort order; incl. SKY)
+  const float *face_uv;    // per BVH-order record: 6 floats (Face<true> texcoords), or null
+  const float *face_uv_seq;
+  const DMaterial *mats;
+  const DTexture *textures;
+  uint32_t root_a, root_b;  // the root's (a, b) words
+  int32_t n_recs, n_recs_seq, n_nodes;
+  int32_t sky_obj, sky_mat;  // first Sky in the list, or -1
+  int32_t has_spheres;
+};
+
+struct DCamera {  // camera.cuh:12-14
+  V3 position, llc, horizontal, vertical, u, v;
+  int32_t is_defocus;
+  float lens_radius;
+};
+
+// Closest-hit result of a query (superset of HitRecord, hitable.cuh:13-17)
+struct Hit {
+  double t;
+  int32_t rec;   // record index (BVH order in mode 0, list order in mode 1), REC_SKY, REC_NONE
+  int32_t seq;   // 1: rec indexes recs_seq
+};
+
+// ------------------------------------------------------------------------------------------------
+// Philox4x32-10 keyed (seed) with counter (pixel, sample, dimension, iteration)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                              uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0;
+    c1 = lo1;
+    c2 = n2;
+    c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  out[0] = c0;
+  out[1] = c1;
+  out[2] = c2;
+  out[3] = c3;
+}
+// curand_uniform's mapping to (0, 1] (curand_kernel.h _curand_uniform)
+__device__ __forceinline__ float u01(uint32_t x) {
+  return __uint2float_rn(x) * 2.3283064365386963e-10f + 1.16415321826934814453125e-10f;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Ray with the float thresholds of the reference's double range test
+// ------------------------------------------------------------------------------------------------
+struct RayQ {
+  V3 o, d;
+};
+
+struct Range {
+  double t_from, t_to;  // as passed to Hit()
+  float tf_f;           // smallest float >= t_from : (double)t >= t_from  <=>  t >= tf_f
+};
+__host__ __device__ __forceinline__ float float_ge(double x) {  // smallest float >= x
+#ifdef __CUDA_ARCH__
+  return __double2float_ru(x);
+#else
+  float f = (float)x;
+  if ((double)f < x) f = nextafterf(f, INFINITY);
+  return f;
+#endif
+}
+__device__ __forceinline__ float float_le(double x) { return __double2float_rd(x); }  // largest float <= x
+
+constexpr float DET_EPS_F = 1.00000001168609742308035492897e-7f;  // smallest float >= 1e-7 (utils.cu:53,60)
+static_assert((double)DET_EPS_F >= 1e-7, "DET_EPS_F must round up");
+
+// utils.cu:49-85 TriangleHit, decision part.  Returns true when u, v pass and t >= tf_f; the
+// caller applies the upper bound.  a = v0, e1 = v1 - v0, e2 = v2 - v0.
+__device__ __forceinline__ bool tri_test(V3 a, V3 e1, V3 e2, const RayQ &r, float tf_f, float *out_t, float *out_u,
+                                         float *out_v) {
+  V3 pvec = cross(r.d, e2);
+  float det = dot(e1, pvec);
+  if (fabsf(det) < DET_EPS_F) return false;
+  float invDet = 1 / det;
+  V3 tvec = r.o - a;
+  float u = dot(tvec, pvec) * invDet;
+  if (u < 0 || u > 1) return false;
+  V3 qvec = cross(tvec, e1);
+  float v = dot(r.d, qvec) * invDet;
+  if (v < 0 || u + v > 1) return false;
+  float t = dot(e2, qvec) * invDet;
+  if (!(t >= tf_f)) return false;
+  *out_t = t;
+  *out_u = u;
+  *out_v = v;
+  return true;
+}
+
+__device__ __forceinline__ double rec_radius(float4 r1) {
+  return __hiloint2double(__float_as_int(r1.y), __float_as_int(r1.x));
+}
+
+// sphere.cu:11-44 Sphere::Hit, decision part: the root the reference would return for an
+// unbounded t_to (near root if >= t_from, else far root), or false.
+__device__ __forceinline__ bool sphere_test(V3 c, double radius, const RayQ &r, double t_from, double *out_t) {
+  double len_d = (double)length(r.d);
+  double a = len_d * len_d;
+  V3 oc = r.o - c;
+  double b = (double)(2 * dot(r.d, oc));
+  double len_oc = (double)length(oc);
+  double cc = len_oc * len_oc - radius * radius;
+  double disc = b * b - 4 * a * cc;
+  if (disc < 0) return false;
+  double sq = sqrt(disc);
+  double t = (-b - sq) / (2 * a);
+  if (t_from <= t) {
+    *out_t = t;
+    return true;
+  }
+  t = (-b + sq) / (2 * a);
+  if (t_from <= t) {
+    *out_t = t;
+    return true;
+  }
+  return false;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Closest-hit bookkeeping with the reference's tie rules made order independent:
+//   smaller t wins; equal t: the lower list index wins (HitableList::Hit replaces only on
+//   hr.t < t_to, hitable_list.cu:14-21); inside one mesh the higher post-sort face index wins
+//   (leaf loop t <= t_to, bvh.cuh:127-134; right child wins, :152-156).
+// ------------------------------------------------------------------------------------------------
+struct Best {
+  double t;    // current closest t (HitRecord::t is a double)
+  float t_f;   // largest float <= t: a float candidate passes `t <= t_to` iff t <= t_f
+  int32_t rec;
+  int32_t obj, sub;
+};
+
+__device__ __forceinline__ void best_init(Best &b, double t_to) {
+  b.t = t_to;
+  b.t_f = float_le(t_to);
+  b.rec = REC_NONE;
+  b.obj = 0x7fffffff;
+  b.sub = -1;
+}
+__device__ __forceinline__ bool best_offer(Best &b, double t, int32_t rec, int32_t obj, int32_t sub) {
+  // precondition: t <= b.t
+  if (t == b.t && b.rec != REC_NONE) {
+    if (!(obj < b.obj || (obj == b.obj && sub > b.sub))) return false;
+  }
+  b.t = t;
+  b.rec = rec;
+  b.obj = obj;
+  b.sub = sub;
+  return true;
+}
+
+// One record against the ray.  Returns the number of records consumed (2 for a quad).
+// `ambiguous` is raised in the one situation where Parallelogram::Hit's "first triangle that
+// hits wins" (parallelogram.cu:25-41) depends on the t_to it was called with: both triangles
+// hit and the second is closer.  The caller then re-runs the ray through the sequential scan.
+__device__ __forceinline__ int rec_test(const float4 *__restrict__ recs, int k, const RayQ &r, const Range &rg, Best &b,
+                                        bool &ambiguous) {
+  float4 r0 = __ldg(recs + 3 * (size_t)k), r1 = __ldg(recs + 3 * (size_t)k + 1), r2 = __ldg(recs + 3 * (size_t)k + 2);
+  uint32_t kind = __float_as_uint(r2.w) & KIND_MASK;
+  if (kind == K_TRI) {
+    float t, u, v;
+    if (tri_test(xyz(r0), xyz(r1), xyz(r2), r, rg.tf_f, &t, &u, &v) && t <= b.t_f) {
+      if (best_offer(b, (double)t, k, __float_as_int(r0.w), __float_as_int(r1.w))) b.t_f = t;
+    }
+    return 1;
+  }
+  if (kind == K_QUAD0) {
+    float t0, t1, u, v;
+    bool h0 = tri_test(xyz(r0), xyz(r1), xyz(r2), r, rg.tf_f, &t0, &u, &v);
+    float4 s0 = __ldg(recs + 3 * (size_t)k + 3), s1 = __ldg(recs + 3 * (size_t)k + 4), s2 = __ldg(recs + 3 * (size_t)k + 5);
+    bool h1 = tri_test(xyz(s0), xyz(s1), xyz(s2), r, rg.tf_f, &t1, &u, &v);
+    if (h0) {
+      if (h1 && t1 < t0) ambiguous = true;
+      if (t0 <= b.t_f) {
+        if (best_offer(b, (double)t0, k, __float_as_int(r0.w), 0)) b.t_f = t0;
+      }
+    } else if (h1 && t1 <= b.t_f) {
+      if (best_offer(b, (double)t1, k + 1, __float_as_int(s0.w), 1)) b.t_f = t1;
+    }
+    return 2;
+  }
+  if (kind == K_SPHERE) {
+    double t;
+    if (sphere_test(xyz(r0), rec_radius(r1), r, rg.t_from, &t) && t <= b.t) {
+      if (best_offer(b, t, k, __float_as_int(r0.w), 0)) b.t_f = float_le(t);
+    }
+    return 1;
+  }
+  return 1;  // K_QUAD1 reached on its own never happens (leaves keep pairs together); K_SKY is not in the BVH
+}
+
+// ------------------------------------------------------------------------------------------------
+// HitableList::Hit restated as the reference executes it: a sequential scan in Append order
+// (hitable_list.cu:7-25), meshes scanned face by face in post-sort order (the exact-visibility
+// form of BVHNode::Hit).  Used by mode 1 of rt_trace_closest and as the resolver of the rare
+// order-dependent cases of the BVH traversal.
+// ------------------------------------------------------------------------------------------------
+static __device__ __noinline__ Hit world_hit_seq(const DScene &s, const RayQ &r, double t_from, double t_to) {
+  bool ok = false;
+  double T = t_to;
+  int best_rec = REC_NONE;
+  int cur_obj = -1;
+  bool obj_hit = false;
+  double obj_t = 0, obj_tto = T;
+  int obj_rec = REC_NONE;
+  float tf_f = float_ge(t_from);
+  const float4 *recs = s.recs_seq;
+  auto commit = [&]() {
+    if (obj_hit) {
+      if (!ok) {
+        best_rec = obj_rec;
+        T = fmin(T, obj_t);
+        ok = true;
+      } else if (obj_t < T) {
+        T = obj_t;
+        best_rec = obj_rec;
+      }
+    }
+  };
+  for (int k = 0; k < s.n_recs_seq; k++) {
+    float4 r0 = recs[3 * (size_t)k], r1 = recs[3 * (size_t)k + 1], r2 = recs[3 * (size_t)k + 2];
+    int obj = __float_as_int(r0.w);
+    uint32_t kind = __float_as_uint(r2.w) & KIND_MASK;
+    if (obj != cur_obj) {
+      commit();
+      cur_obj = obj;
+      obj_hit = false;
+      obj_tto = T;
+    }
+    if (kind == K_TRI) {
+      float t, u, v;
+      if (tri_test(xyz(r0), xyz(r1), xyz(r2), r, tf_f, &t, &u, &v) && (double)t <= obj_tto) {
+        obj_tto = t;
+        obj_t = t;
+        obj_rec = k;
+        obj_hit = true;
+      }
+    } else if (kind == K_QUAD0) {
+      float t, u, v;
+      if (tri_test(xyz(r0), xyz(r1), xyz(r2), r, tf_f, &t, &u, &v) && (double)t <= obj_tto) {
+        obj_t = t;
+        obj_rec = k;
+        obj_hit = true;
+      } else {
+        float4 s0 = recs[3 * (size_t)k + 3], s1 = recs[3 * (size_t)k + 4], s2 = recs[3 * (size_t)k + 5];
+        if (tri_test(xyz(s0), xyz(s1), xyz(s2), r, tf_f, &t, &u, &v) && (double)t <= obj_tto) {
+          obj_t = t;
+          obj_rec = k + 1;
+          obj_hit = true;
+        }
+      }
+      k++;  // the QUAD1 record
+    } else if (kind == K_SPHERE) {
+      double t;
+      if (sphere_test(xyz(r0), rec_radius(r1), r, t_from, &t) && t <= obj_tto) {
+        obj_t = t;
+        obj_rec = k;
+        obj_hit = true;
+      }
+    } else if (kind == K_SKY) {
+      double t = 1e9;
+      if (t_from <= t && t <= obj_tto) {
+        obj_t = t;
+        obj_rec = k;
+        obj_hit = true;
+      }
+    }
+  }
+  commit();
+  Hit h;
+  h.t = ok ? T : 0.0;
+  h.rec = best_rec;
+  h.seq = 1;
+  return h;
+}
+
+// ------------------------------------------------------------------------------------------------
+// BVH traversal (product path).  32-byte nodes, children tested before descent, near child first,
+// far child's (a, b) words pushed on a short per-thread stack.  Boxes were padded at build time
+// and the cull bound is widened, so that culling never removes a record the scan would accept.
+// ------------------------------------------------------------------------------------------------
+struct TravStats {
+  uint32_t nodes, prims;
+};
+
+template <bool STATS>
+__device__ __forceinline__ Hit world_hit_bvh(const DScene &s, const RayQ &r, double t_from, double t_to,
+                                             TravStats *st) {
+  Range rg;
+  rg.t_from = t_from;
+  rg.t_to = t_to;
+  rg.tf_f = float_ge(t_from);
+  Best b;
+  best_init(b, t_to);
+  if (s.sky_obj >= 0) {  // sky.cu:18-27: always a candidate at t = 1e9
+    double t = 1e9;
+    if (t_from <= t && t <= t_to) {
+      b.t = t;
+      b.t_f = 1e9f;
+      b.rec = REC_SKY;
+      b.obj = s.sky_obj;
+      b.sub = 0;
+    }
+  }
+  bool ambiguous = false, overflow = false;
+  if (s.n_recs > 0) {
+    const float idx = 1.0f / r.d.x, idy = 1.0f / r.d.y, idz = 1.0f / r.d.z;
+    const float t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
+    uint2 stack[STACK_SIZE];
+    int sp = 0;
+    uint32_t ca = s.root_a, cb = s.root_b;
+    const float4 *__restrict__ nodes = s.nodes;
+    for (;;) {
+      if (cb & LEAF_FLAG) {
+        int k = (int)ca, end = (int)(ca + (cb & ~LEAF_FLAG));
+        while (k < end) {
+          if (STATS) st->prims++;
+          k += rec_test(s.recs, k, r, rg, b, ambiguous);
+        }
+      } else {
+        if (STATS) st->nodes += 2;
+        float4 l0 = __ldg(nodes + 2 * (size_t)ca), l1 = __ldg(nodes + 2 * (size_t)ca + 1);
+        float4 r0 = __ldg(nodes + 2 * (size_t)cb), r1 = __ldg(nodes + 2 * (size_t)cb + 1);
+        // widened upper bound: never cull a box whose entry is within rounding of the best t
+        float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
+        float ax = (l0.x - r.o.x) * idx, bx = (l1.x - r.o.x) * idx;
+        float ay = (l0.y - r.o.y) * idy, by = (l1.y - r.o.y) * idy;
+        float az = (l0.z - r.o.z) * idz, bz = (l1.z - r.o.z) * idz;
+        float ln = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_lo));
+        float lf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
+        ax = (r0.x - r.o.x) * idx, bx = (r1.x - r.o.x) * idx;
+        ay = (r0.y - r.o.y) * idy, by = (r1.y - r.o.y) * idy;
+        az = (r0.z - r.o.z) * idz, bz = (r1.z - r.o.z) * idz;
+        float rn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_lo));
+        float rf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
+        // entry <= exit with a relative guard band on the exit
+        bool hl = ln <= lf + fabsf(lf) * 1e-5f, hr = rn <= rf + fabsf(rf) * 1e-5f;
+        uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
+        uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
+        if (hl && hr) {
+          bool left_first = ln <= rn;
+          if (sp < STACK_SIZE) {
+            stack[sp++] = left_first ? make_uint2(ra, rb) : make_uint2(la, lb);
+          } else {
+            overflow = true;
+          }
+          ca = left_first ? la : ra;
+          cb = left_first ? lb : rb;
+          continue;
+        }
+        if (hl) {
+          ca = la;
+          cb = lb;
+          continue;
+        }
+        if (hr) {
+          ca = ra;
+          cb = rb;
+          continue;
+        }
+      }
+      if (sp == 0) break;
+      uint2 e = stack[--sp];
+      ca = e.x;
+      cb = e.y;
+    }
+  }
+  if (ambiguous || overflow) return world_hit_seq(s, r, t_from, t_to);
+  Hit h;
+  h.t = b.rec == REC_NONE ? 0.0 : b.t;
+  h.rec = b.rec;
+  h.seq = 0;
+  return h;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Surface data of an accepted hit (what HitRecord carries): normal, u, v, material
+// ------------------------------------------------------------------------------------------------
+struct Surface {
+  V3 normal;
+  float u, v;  // HitRecord::u,v narrowed to float
+  int32_t material, obj, sub;
+  uint32_t kind;
+};
+
+// sphere.cu:52-64 GetUV
+__device__ __forceinline__ void sphere_uv(V3 p, float *u, float *v) {
+  float pi = 3.14159265358979323846264338327950288f;
+  float theta = acosf(-p.y);
+  float phi = atan2f(-p.z, p.x) + pi;
+  *u = (float)((double)(phi / (2 * pi)));
+  *v = (float)((double)(theta / pi));
+}
+
+// need_uv: only textured materials read u, v; callers that do not need them skip the arithmetic.
+__device__ __forceinline__ Surface surface_at(const DScene &s, const RayQ &r, const Hit &h, bool need_uv) {
+  Surface sf;
+  sf.normal = mk(0.f, 0.f, 0.f);
+  sf.u = sf.v = 0.f;
+  sf.sub = 0;
+  if (h.rec == REC_SKY) {
+    sf.material = s.sky_mat;
+    sf.obj = s.sky_obj;
+    sf.kind = K_SKY;
+    return sf;
+  }
+  const float4 *recs = h.seq ? s.recs_seq : s.recs;
+  float4 r0 = __ldg(recs + 3 * (size_t)h.rec), r1 = __ldg(recs + 3 * (size_t)h.rec + 1),
+         r2 = __ldg(recs + 3 * (size_t)h.rec + 2);
+  uint32_t w = __float_as_uint(r2.w);
+  sf.kind = w & KIND_MASK;
+  sf.material = (int32_t)(w >> KIND_BITS);
+  sf.obj = __float_as_int(r0.w);
+  sf.sub = __float_as_int(r1.w);
+  if (sf.kind == K_SKY) return sf;
+  if (sf.kind == K_SPHERE) {
+    V3 c = xyz(r0);
+    V3 p = r.o + float(h.t) * r.d;
+    sf.normal = normalize(p - c);
+    if (need_uv) sphere_uv(sf.normal, &sf.u, &sf.v);
+    return sf;
+  }
+  V3 e1 = xyz(r1), e2 = xyz(r2);
+  V3 n = normalize(cross(e1, e2));
+  sf.normal = dot(r.d, n) < 0 ? n : -n;
+  if (need_uv) {
+    // re-run the decision arithmetic for u, v (same operations -> same bits)
+    float t, u, v;
+    tri_test(xyz(r0), e1, e2, r, -CUDART_INF_F, &t, &u, &v);
+    float a = (float)(1 - (double)u - (double)v), b = u, c = v;
+    if (sf.kind == K_QUAD0) {  // parallelogram.cu:26-29
+      sf.u = 0.f * a + 1.f * b + 0.f * c;
+      sf.v = 1.f * a + 1.f * b + 0.f * c;
+    } else if (sf.kind == K_QUAD1) {  // parallelogram.cu:35-38
+      sf.u = 1.f * a + 0.f * b + 1.f * c;
+      sf.v = 1.f * a + 0.f * b + 0.f * c;
+    } else {
+      const float *uvs = h.seq ? s.face_uv_seq : s.face_uv;
+      if (w & FLAG_BARY) {  // Triangle::Hit keeps the barycentrics (triangle.cu:11-19)
+        sf.u = u;
+        sf.v = v;
+      } else if (uvs) {  // Face<true>::Hit, bvh.cuh:41-45 (Face<false> leaves u,v unset: reported 0)
+        const float *q = uvs + 6 * (size_t)h.rec;
+        sf.u = q[0] * a + q[2] * b + q[4] * c;
+        sf.v = q[1] * a + q[3] * b + q[5] * c;
+      }
+    }
+  }
+  return sf;
+}
+
+// ------------------------------------------------------------------------------------------------
+// textures and materials
+// ------------------------------------------------------------------------------------------------
+// image_texture.cu:9-15 over the texture object of :17-38 (normalized coords, point filter, wrap,
+// uchar4 -> x/255), restated on raw memory so that the result does not depend on texture hardware.
+__device__ __forceinline__ V3 image_value(const DTexture &tx, float u_in, float v_in) {
+  double v = 1.0 - (double)v_in;
+  float fu = u_in, fv = (float)v;
+  float x = fu - floorf(fu), y = fv - floorf(fv);
+  int ix = (int)floorf(x * (float)tx.width), iy = (int)floorf(y * (float)tx.height);
+  if (ix >= tx.width) ix = tx.width - 1;
+  if (iy >= tx.height) iy = tx.height - 1;
+  if (ix < 0) ix = 0;
+  if (iy < 0) iy = 0;
+  uchar4 px = *reinterpret_cast<const uchar4 *>(tx.rgba + (size_t)iy * tx.pitch + (size_t)ix * 4);
+  return mk(px.x / 255.0f, px.y / 255.0f, px.z / 255.0f);
+}
+__device__ __forceinline__ V3 texture_value(const DScene &s, const DMaterial &m, float u, float v) {
+  if (m.texture < 0) return xyz(m.color_fuzz);  // constant_texture.cu:11-14
+  return image_value(s.textures[m.texture], u, v);
+}
+
+struct PathKey {
+  uint32_t pixel, sample, k0, k1;
+};
+constexpr int MAX_REJECT_ITER = 64;
+
+// lambertian.cu:19-31 SphericalRand / metal.cu:27-36 RandomInUnitSphere on the keyed Philox
+// stream: dimension 1 + depth, one block per rejection iteration, at most MAX_REJECT_ITER.
+__device__ __forceinline__ V3 ball_rejection(const PathKey &pk, int depth, float *out_l) {
+  float x = 0, y = 0, z = 0, l = 0;
+  for (int it = 0; it < MAX_REJECT_ITER; it++) {
+    uint32_t o[4];
+    philox4x32_10(pk.pixel, pk.sample, (uint32_t)(1 + depth), (uint32_t)it, pk.k0, pk.k1, o);
+    x = u01(o[0]) * 2.0f + -1.0f;
+    y = u01(o[1]) * 2.0f + -1.0f;
+    z = u01(o[2]) * 2.0f + -1.0f;
+    l = sqrtf(x * x + y * y + z * z);
+    if (!(l > 1)) break;
+  }
+  *out_l = l;
+  return mk(x, y, z);
+}
+
+__device__ __forceinline__ bool material_needs_uv(const DMaterial &m) { return m.texture >= 0; }
+
+// Material::Scatter (lambertian.cu:33-43, metal.cu:12-25, dielectric.cu:16-44, diffuse_light.cu:5-9,
+// sky.cu:3-7).  Returns false when the path ends here.  The scattered ray goes through Ray::Ray,
+// which normalizes (ray.cu:8-11).
+__device__ __forceinline__ bool scatter(const DScene &s, const DMaterial &m, const RayQ &ray, float t, const Surface &sf,
+                                        const PathKey &pk, int depth, V3 *att, RayQ *out) {
+  switch (m.type) {
+    case RT_MAT_LAMBERTIAN: {
+      if (dot(ray.d, sf.normal) >= 0) return false;
+      V3 p = ray.o + t * ray.d;
+      V3 albedo = texture_value(s, m, sf.u, sf.v);
+      float l;
+      V3 r = ball_rejection(pk, depth, &l);
+      r.x /= l;
+      r.y /= l;
+      r.z /= l;
+      V3 next_dir = normalize(r + sf.normal);
+      *att = albedo;
+      out->o = p;
+      out->d = normalize(next_dir);
+      return true;
+    }
+    case RT_MAT_METAL: {
+      if (dot(ray.d, sf.normal) >= 0) return false;
+      V3 p = ray.o + t * ray.d;
+      *att = xyz(m.color_fuzz);
+      V3 reflected = reflect(ray.d, sf.normal);
+      float fuzz = m.color_fuzz.w;
+      out->o = p;
+      if (fuzz > 0) {
+        float l;
+        V3 r = ball_rejection(pk, depth, &l);
+        out->d = normalize(reflected + fuzz * r);
+      } else {
+        out->d = normalize(reflected);
+      }
+      return true;
+    }
+    case RT_MAT_DIELECTRIC: {
+      V3 p = ray.o + t * ray.d;
+      V3 d;
+      if (dot(ray.d, sf.normal) >= 0)
+        d = refract(ray.d, -sf.normal, m.eta_in);
+      else
+        d = refract(ray.d, sf.normal, m.eta_out);
+      if (d.x == 0 && d.y == 0 && d.z == 0) return false;
+      if (isnan(d.x) || isnan(d.y) || isnan(d.z)) return false;
+      *att = xyz(m.color_fuzz);
+      out->o = p;
+      out->d = normalize(d);
+      return true;
+    }
+    default:
+      return false;
+  }
+}
+
+// Material::Emit (diffuse_light.cu:11-13, sky.cu:9-14, material.cu:3-6)
+__device__ __forceinline__ V3 emit(const DScene &s, const DMaterial &m, float u, float v, V3 p) {
+  switch (m.type) {
+    case RT_MAT_DIFFUSE_LIGHT:
+      return texture_value(s, m, u, v);
+    case RT_MAT_SKY: {
+      V3 dir = normalize(p);
+      float t = (float)(0.5 * ((double)dir.y + 1.0));
+      return (1.0f - t) * mk(1.0f, 1.0f, 1.0f) + t * mk(0.5f, 0.7f, 1.0f);
+    }
+    default:
+      return mk(0.f, 0.f, 0.f);
+  }
+}
+
+// camera.cu:57-77 RayAt; x, y in [-1, 1].  (DiskRand samples the square [0, lens_radius]^2.)
+__device__ __forceinline__ RayQ camera_ray_at(const DCamera &c, double x, double y, float lens_u, float lens_v) {
+  x = (x + 1) / 2;
+  y = (y + 1) / 2;
+  V3 target = c.llc + static_cast<float>(x) * c.horizontal + static_cast<float>(y) * c.vertical;
+  V3 origin;
+  if (c.is_defocus) {
+    origin = c.position + c.u * lens_u + c.v * lens_v;
+  } else {
+    origin = c.position;
+  }
+  RayQ r;
+  r.o = origin;
+  r.d = normalize(normalize(target - origin));
+  return r;
+}
+
+// ray_tracing.cu:68-74: camera sample `sample` of pixel (i, j) from Philox block (pixel, sample, 0, 0)
+__device__ __forceinline__ RayQ camera_sample(const DCamera &cam, int i, int j, int height, int width,
+                                              const PathKey &pk) {
+  uint32_t o[4];
+  philox4x32_10(pk.pixel, pk.sample, 0u, 0u, pk.k0, pk.k1, o);
+  double x = ((double)u01(o[0]) + double(j)) / double(width);
+  double y = ((double)u01(o[1]) + double(height - i)) / double(height);
+  x = 2 * x - 1;
+  y = 2 * y - 1;
+  float lu = 0, lv = 0;
+  if (cam.is_defocus) {
+    lu = u01(o[2]) * cam.lens_radius;
+    lv = u01(o[3]) * cam.lens_radius;
+  }
+  return camera_ray_at(cam, x, y, lu, lv);
+}
+
+}  // namespace rtc

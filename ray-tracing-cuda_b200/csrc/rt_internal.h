@@ -1,0 +1,69 @@
+// rt_internal.h — host-side context of librtcore.so (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "rt_device.cuh"
+
+namespace rtc {
+
+void set_error(const std::string &msg);
+int cuda_fail(cudaError_t e, const char *what);
+
+#define RT_CUDA(call)                                    \
+  do {                                                   \
+    cudaError_t e_ = (call);                             \
+    if (e_ != cudaSuccess) return rtc::cuda_fail(e_, #call); \
+  } while (0)
+
+// A device allocation that grows but never shrinks (buffers are reused across commits/renders).
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <typename T>
+  T *as() const {
+    return reinterpret_cast<T *>(p);
+  }
+};
+
+struct RenderCounters {  // device-side counters of one rt_render call
+  unsigned long long samples, rays, rays_ref, nodes, prims, seq_fallbacks;
+};
+
+}  // namespace rtc
+
+struct rt_ctx {
+  int device = 0;
+  bool has_scene = false, has_camera = false;
+  rtc::DScene scene{};
+  rtc::DCamera camera{};
+  rt_camera camera_host{};
+  // scene storage
+  rtc::DevBuf nodes, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;
+  std::vector<void *> tex_allocs;
+  // build scratch
+  rtc::DevBuf scratch[12];
+  // render scratch
+  rtc::DevBuf counters, accum_tmp, rgb_tmp, rgb8_tmp, rays_tmp, hits_tmp;
+  rtc::DevBuf wf[16];  // wavefront path state
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+  rt_build_stats build_stats{};
+  // nccl (loaded lazily)
+  void *nccl_comm = nullptr;
+};

@@ -1,0 +1,591 @@
+// rt_render.cu — the render hot path: closest-hit queries, the fused persistent-path kernel, the
+// wavefront pipeline (logic/shade -> extend) and the resolve kernel.
+//
+// Replaces, in the reference: PathTracing (ray_tracing.cu:56-85), Trace (ray_tracing.cu:12-54),
+// HitableList::Hit (hitable_list.cu:7-25) and everything they call, plus the post-processing tail
+// (ray_tracing.cu:78-83, utils.cu:126-129).
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "rt_internal.h"
+
+namespace rtc {
+
+struct RenderArgs {
+  int32_t height, width;
+  int32_t spp_begin, spp_end;
+  int32_t max_depth;
+  uint32_t k0, k1;
+};
+
+// ---- parity hook: HitableList::Hit on explicit rays ------------------------------------------------
+__global__ void __launch_bounds__(128) k_trace_closest(DScene s, const float *__restrict__ rays, int64_t n,
+                                                       double t_from, double t_to, int mode, rt_hit *out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  RayQ r;
+  r.o = mk(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]);
+  r.d = mk(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]);
+  Hit h = mode == 1 ? world_hit_seq(s, r, t_from, t_to) : world_hit_bvh<false>(s, r, t_from, t_to, nullptr);
+  rt_hit o;
+  if (h.rec == REC_NONE) {
+    o.t = 0;
+    o.obj = -1;
+    o.sub = -1;
+    o.u = o.v = 0.f;
+    o.normal[0] = o.normal[1] = o.normal[2] = 0.f;
+    o.material = -1;
+  } else {
+    Surface sf = surface_at(s, r, h, true);
+    o.t = h.t;
+    o.obj = sf.obj;
+    o.sub = sf.sub;
+    o.u = sf.u;
+    o.v = sf.v;
+    o.normal[0] = sf.normal.x;
+    o.normal[1] = sf.normal.y;
+    o.normal[2] = sf.normal.z;
+    o.material = sf.material;
+  }
+  out[i] = o;
+}
+
+// Pixel-centre primary rays: ray_tracing.cu:68-74 with both jitters = 0.5.
+__global__ void k_primary_rays(DCamera cam, int height, int width, float *rays) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= height * width) return;
+  int i = idx / width, j = idx % width;
+  double x = ((double)0.5f + double(j)) / double(width);
+  double y = ((double)0.5f + double(height - i)) / double(height);
+  x = 2 * x - 1;
+  y = 2 * y - 1;
+  RayQ r = camera_ray_at(cam, x, y, 0.5f * cam.lens_radius, 0.5f * cam.lens_radius);
+  float *o = rays + 6 * (size_t)idx;
+  o[0] = r.o.x;
+  o[1] = r.o.y;
+  o[2] = r.o.z;
+  o[3] = r.d.x;
+  o[4] = r.d.y;
+  o[5] = r.d.z;
+}
+
+// One bounce of Trace (ray_tracing.cu:20-43) after the closest-hit query, in forward form:
+// returns true when the path continues with `ray`/`T` updated, else adds the path's radiance.
+__device__ __forceinline__ bool shade_hit(const DScene &s, RayQ &ray, const Hit &h, const PathKey &pk, int depth, V3 &T,
+                                          V3 &color) {
+  int mat_id;
+  bool need_uv;
+  {
+    // material first: only textured materials need u, v
+    if (h.rec == REC_SKY) {
+      mat_id = s.sky_mat;
+    } else {
+      const float4 *recs = h.seq ? s.recs_seq : s.recs;
+      mat_id = (int)(__float_as_uint(__ldg(recs + 3 * (size_t)h.rec + 2).w) >> KIND_BITS);
+    }
+  }
+  DMaterial m;
+  {
+    const float4 *mp = reinterpret_cast<const float4 *>(s.mats + mat_id);
+    float4 a = __ldg(mp), b = __ldg(mp + 1);
+    m.color_fuzz = a;
+    m.type = __float_as_int(b.x);
+    m.texture = __float_as_int(b.y);
+    m.eta_in = b.z;
+    m.eta_out = b.w;
+  }
+  need_uv = material_needs_uv(m);
+  float t = float(h.t);
+  if (m.type == RT_MAT_SKY || m.type == RT_MAT_DIFFUSE_LIGHT) {
+    // Scatter returns false (sky.cu:3-7, diffuse_light.cu:5-9): result = emitted
+    float u = 0.f, v = 0.f;
+    if (need_uv) {
+      Surface sf = surface_at(s, ray, h, true);
+      u = sf.u;
+      v = sf.v;
+    }
+    V3 p = ray.o + t * ray.d;
+    color = color + T * emit(s, m, u, v, p);
+    return false;
+  }
+  Surface sf = surface_at(s, ray, h, need_uv);
+  V3 att;
+  RayQ out;
+  if (!scatter(s, m, ray, t, sf, pk, depth, &att, &out)) return false;  // Emit() of these materials is 0
+  T = T * att;
+  ray = out;
+  return true;
+}
+
+__device__ __forceinline__ void flush_counters(RenderCounters *ctr, unsigned long long samples,
+                                               unsigned long long rays, unsigned long long rays_ref,
+                                               unsigned long long nodes, unsigned long long prims) {
+  for (int o = 16; o > 0; o >>= 1) {
+    samples += __shfl_xor_sync(0xffffffffu, samples, o);
+    rays += __shfl_xor_sync(0xffffffffu, rays, o);
+    rays_ref += __shfl_xor_sync(0xffffffffu, rays_ref, o);
+    nodes += __shfl_xor_sync(0xffffffffu, nodes, o);
+    prims += __shfl_xor_sync(0xffffffffu, prims, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(&ctr->samples, samples);
+    atomicAdd(&ctr->rays, rays);
+    atomicAdd(&ctr->rays_ref, rays_ref);
+    if (nodes) atomicAdd(&ctr->nodes, nodes);
+    if (prims) atomicAdd(&ctr->prims, prims);
+  }
+}
+
+// ---- fused kernel: one thread per pixel, paths regenerated in registers ---------------------------
+// Each lane runs its pixel's samples in increasing order and starts the next sample the moment the
+// current path ends, so a warp stays full until its pixels run out of samples.  No queue traffic.
+template <bool STATS>
+__global__ void __launch_bounds__(128) k_render_fused(DScene s, DCamera cam, RenderArgs a, float *__restrict__ accum,
+                                                      RenderCounters *ctr) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+  const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = i < a.height && j < a.width;
+  const int idx = i * a.width + j;
+  PathKey pk;
+  pk.pixel = (uint32_t)idx;
+  pk.k0 = a.k0;
+  pk.k1 = a.k1;
+  int k = inside ? a.spp_begin : a.spp_end;
+  V3 color = mk(0.f, 0.f, 0.f), T = mk(1.f, 1.f, 1.f);
+  RayQ ray;
+  ray.o = ray.d = mk(0.f, 0.f, 0.f);
+  int depth = 0;
+  bool need_new = true;
+  unsigned long long n_samples = 0, n_rays = 0, n_rays_ref = 0;
+  TravStats ts;
+  ts.nodes = ts.prims = 0;
+  unsigned long long n_nodes = 0, n_prims = 0;
+  for (;;) {
+    if (need_new) {
+      if (k >= a.spp_end) break;
+      pk.sample = (uint32_t)k;
+      ray = camera_sample(cam, i, j, a.height, a.width, pk);
+      T = mk(1.f, 1.f, 1.f);
+      depth = 0;
+      need_new = false;
+      n_samples++;
+    }
+    n_rays_ref++;
+    bool alive = depth < a.max_depth;  // ray_tracing.cu:23: the query at depth == limit yields 0
+    if (alive) {
+      Hit h = world_hit_bvh<STATS>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
+      n_rays++;
+      if (STATS) {
+        n_nodes += ts.nodes;
+        n_prims += ts.prims;
+        ts.nodes = ts.prims = 0;
+      }
+      alive = h.rec != REC_NONE && shade_hit(s, ray, h, pk, depth, T, color);
+    }
+    if (alive) {
+      depth++;
+    } else {
+      k++;
+      need_new = true;
+    }
+  }
+  if (inside) {
+    accum[3 * (size_t)idx + 0] += color.x;
+    accum[3 * (size_t)idx + 1] += color.y;
+    accum[3 * (size_t)idx + 2] += color.z;
+  }
+  flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims);
+}
+
+
+// ---- wavefront pipeline ------------------------------------------------------------------------------
+// One path slot per pixel, paths regenerated in place (sample k+1 starts in the slot the moment
+// sample k ends), so the pool stays full until pixels run out of samples and every pixel sums its
+// samples in increasing order — the image is bit-identical to the fused kernel's.
+//   logic  : shade the slot's hit (Material::Scatter/Emit), regenerate (Camera::RayAt), enqueue
+//   extend : closest-hit query for every queued slot
+// Path state is SoA, float4 per field: 16-byte coalesced accesses.
+struct WfState {
+  float4 *ray_o;   // o.xyz, w = hit t (float)
+  float4 *ray_d;   // d.xyz, w = hit record (encoded)
+  float4 *thr;     // T.xyz, w = depth | flags
+  float4 *color;   // colour sum of the pixel, w = current sample index
+  uint32_t *queue[2];
+  uint32_t *count;  // [2] queue lengths, ping-pong
+};
+constexpr int WF_DONE = 1 << 30, WF_NEW = 1 << 29;
+
+__device__ __forceinline__ int hit_encode(const Hit &h) { return (h.rec < 0) ? h.rec : (h.seq ? (h.rec | 0x40000000) : h.rec); }
+__device__ __forceinline__ Hit hit_decode(int enc, float t) {
+  Hit h;
+  h.t = (double)t;
+  if (enc < 0) {
+    h.rec = enc;
+    h.seq = 0;
+  } else {
+    h.rec = enc & 0x3fffffff;
+    h.seq = (enc >> 30) & 1;
+  }
+  return h;
+}
+
+// Warp-aggregated append of `slot` to a queue.
+__device__ __forceinline__ void queue_push(bool pred, uint32_t slot, uint32_t *queue, uint32_t *count) {
+  unsigned m = __ballot_sync(0xffffffffu, pred);
+  if (m == 0) return;
+  int lane = threadIdx.x & 31;
+  int leader = __ffs(m) - 1;
+  uint32_t base = 0;
+  if (lane == leader) base = atomicAdd(count, (uint32_t)__popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (pred) queue[base + __popc(m & ((1u << lane) - 1))] = slot;
+}
+
+template <bool FIRST>
+__global__ void __launch_bounds__(256) k_wf_logic(DScene s, DCamera cam, RenderArgs a, WfState w, int qi,
+                                                  float *__restrict__ accum, RenderCounters *ctr) {
+  const int n_slots = a.height * a.width;
+  const uint32_t n_in = FIRST ? (uint32_t)n_slots : w.count[qi];
+  unsigned long long n_samples = 0, n_rays_ref = 0;
+  for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < ((n_in + 31u) & ~31u); q += gridDim.x * blockDim.x) {
+    bool valid = q < n_in;
+    uint32_t slot = valid ? (FIRST ? q : w.queue[qi][q]) : 0;
+    bool push = false;
+    if (valid) {
+      const int i = slot / a.width, j = slot % a.width;
+      PathKey pk;
+      pk.pixel = slot;
+      pk.k0 = a.k0;
+      pk.k1 = a.k1;
+      V3 color, T;
+      RayQ ray;
+      int k, depth;
+      bool need_new;
+      if (FIRST) {
+        color = mk(0.f, 0.f, 0.f);
+        T = mk(1.f, 1.f, 1.f);
+        k = a.spp_begin;
+        depth = 0;
+        need_new = true;
+        ray.o = ray.d = mk(0.f, 0.f, 0.f);
+      } else {
+        float4 ro = w.ray_o[slot], rd = w.ray_d[slot], th = w.thr[slot], co = w.color[slot];
+        ray.o = xyz(ro);
+        ray.d = xyz(rd);
+        T = xyz(th);
+        color = xyz(co);
+        depth = __float_as_int(th.w);
+        k = __float_as_int(co.w);
+        pk.sample = (uint32_t)k;
+        Hit h = hit_decode(__float_as_int(rd.w), ro.w);
+        bool alive = h.rec != REC_NONE && shade_hit(s, ray, h, pk, depth, T, color);
+        if (alive) {
+          depth++;
+          need_new = false;
+        } else {
+          k++;
+          need_new = true;
+        }
+      }
+      // next query of this slot (a path at depth == limit contributes 0: ray_tracing.cu:23-26)
+      for (;;) {
+        if (need_new) {
+          if (k >= a.spp_end) break;
+          pk.sample = (uint32_t)k;
+          ray = camera_sample(cam, i, j, a.height, a.width, pk);
+          T = mk(1.f, 1.f, 1.f);
+          depth = 0;
+          need_new = false;
+          n_samples++;
+        }
+        n_rays_ref++;
+        if (depth < a.max_depth) {
+          push = true;
+          break;
+        }
+        k++;
+        need_new = true;
+      }
+      if (push) {
+        w.ray_o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, 0.f);
+        w.ray_d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
+        w.thr[slot] = make_float4(T.x, T.y, T.z, __int_as_float(depth));
+        w.color[slot] = make_float4(color.x, color.y, color.z, __int_as_float(k));
+      } else {
+        accum[3 * (size_t)slot + 0] += color.x;
+        accum[3 * (size_t)slot + 1] += color.y;
+        accum[3 * (size_t)slot + 2] += color.z;
+      }
+    }
+    queue_push(push, slot, w.queue[qi ^ 1], w.count + (qi ^ 1));
+  }
+  flush_counters(ctr, n_samples, 0, n_rays_ref, 0, 0);
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(128) k_wf_extend(DScene s, WfState w, int qi, RenderCounters *ctr) {
+  const uint32_t n_in = w.count[qi];
+  unsigned long long n_rays = 0, n_nodes = 0, n_prims = 0;
+  TravStats ts;
+  ts.nodes = ts.prims = 0;
+  for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < n_in; q += gridDim.x * blockDim.x) {
+    uint32_t slot = w.queue[qi][q];
+    float4 ro = w.ray_o[slot], rd = w.ray_d[slot];
+    RayQ ray;
+    ray.o = xyz(ro);
+    ray.d = xyz(rd);
+    Hit h = world_hit_bvh<STATS>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
+    n_rays++;
+    // only the two .w words change: t and the record
+    reinterpret_cast<float *>(w.ray_o + slot)[3] = float(h.t);
+    reinterpret_cast<int *>(w.ray_d + slot)[3] = hit_encode(h);
+  }
+  if (STATS) {
+    n_nodes = ts.nodes;
+    n_prims = ts.prims;
+  }
+  flush_counters(ctr, 0, n_rays, 0, n_nodes, n_prims);
+}
+
+__global__ void k_wf_reset(uint32_t *count, int which) { count[which] = 0; }
+
+// ---- resolve: ray_tracing.cu:78-83 + WriteImage's *255 truncation (utils.cu:87-96) ---------------
+__global__ void k_resolve(const float *__restrict__ accum, int64_t n, int spp_total, float *rgb, uint8_t *rgb8) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float c = accum[i] / float(spp_total);
+  c = fminf(fmaxf(c, 0.f), 1.f);  // glm::clamp = min(max(x, lo), hi)
+  c = sqrtf(c);
+  if (rgb) rgb[i] = c;
+  if (rgb8) rgb8[i] = (uint8_t)(c * 255);
+}
+
+}  // namespace rtc
+
+// =================================================================================================
+// C-ABI
+// =================================================================================================
+using namespace rtc;
+
+namespace {
+inline int nblk(size_t n, int b) { return (int)((n + b - 1) / b); }
+
+int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
+  if (!ctx) {
+    set_error(std::string(who) + ": null context");
+    return RT_ERR_INVALID;
+  }
+  if (!ctx->has_scene) {
+    set_error(std::string(who) + ": no scene committed");
+    return RT_ERR_INVALID;
+  }
+  if (need_camera && !ctx->has_camera) {
+    set_error(std::string(who) + ": no camera set");
+    return RT_ERR_INVALID;
+  }
+  return RT_OK;
+}
+}  // namespace
+
+extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t n, double t_from, double t_to, int mode,
+                                       rt_hit *d_hits, void *stream) {
+  int rc = check_ready(ctx, false, "rt_trace_closest");
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode != 0 && mode != 1)) {
+    set_error("rt_trace_closest: bad argument");
+    return RT_ERR_INVALID;
+  }
+  if (n == 0) return RT_OK;
+  RT_CUDA(cudaSetDevice(ctx->device));
+  k_trace_closest<<<nblk((size_t)n, 128), 128, 0, (cudaStream_t)stream>>>(ctx->scene, d_rays, n, t_from, t_to, mode,
+                                                                          d_hits);
+  RT_CUDA(cudaGetLastError());
+  return RT_OK;
+}
+
+extern "C" int rt_trace_closest_host(rt_ctx *ctx, const float *h_rays, int64_t n, double t_from, double t_to, int mode,
+                                     rt_hit *h_hits) {
+  int rc = check_ready(ctx, false, "rt_trace_closest");
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!h_rays || !h_hits))) {
+    set_error("rt_trace_closest: bad argument");
+    return RT_ERR_INVALID;
+  }
+  if (n == 0) return RT_OK;
+  RT_CUDA(cudaSetDevice(ctx->device));
+  RT_CUDA(ctx->rays_tmp.reserve((size_t)n * 24));
+  RT_CUDA(ctx->hits_tmp.reserve((size_t)n * sizeof(rt_hit)));
+  RT_CUDA(cudaMemcpy(ctx->rays_tmp.p, h_rays, (size_t)n * 24, cudaMemcpyHostToDevice));
+  rc = rt_trace_closest_device(ctx, ctx->rays_tmp.as<float>(), n, t_from, t_to, mode, ctx->hits_tmp.as<rt_hit>(), nullptr);
+  if (rc) return rc;
+  RT_CUDA(cudaMemcpy(h_hits, ctx->hits_tmp.p, (size_t)n * sizeof(rt_hit), cudaMemcpyDeviceToHost));
+  return RT_OK;
+}
+
+extern "C" int rt_primary_rays_host(rt_ctx *ctx, int height, int width, float *h_rays) {
+  if (!ctx || !ctx->has_camera || height <= 0 || width <= 0 || !h_rays) {
+    set_error("rt_primary_rays_host: bad argument or no camera");
+    return RT_ERR_INVALID;
+  }
+  RT_CUDA(cudaSetDevice(ctx->device));
+  size_t n = (size_t)height * width;
+  RT_CUDA(ctx->rays_tmp.reserve(n * 24));
+  k_primary_rays<<<nblk(n, 256), 256>>>(ctx->camera, height, width, ctx->rays_tmp.as<float>());
+  RT_CUDA(cudaGetLastError());
+  RT_CUDA(cudaMemcpy(h_rays, ctx->rays_tmp.p, n * 24, cudaMemcpyDeviceToHost));
+  return RT_OK;
+}
+
+static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, float *d_accum, RenderCounters *ctr,
+                            cudaStream_t st, uint32_t *iterations, uint32_t *launches) {
+  size_t n = (size_t)a.height * a.width;
+  for (int i = 0; i < 4; i++) RT_CUDA(ctx->wf[i].reserve(n * 16));
+  RT_CUDA(ctx->wf[4].reserve(n * 4));
+  RT_CUDA(ctx->wf[5].reserve(n * 4));
+  RT_CUDA(ctx->wf[6].reserve(64));
+  WfState w;
+  w.ray_o = ctx->wf[0].as<float4>();
+  w.ray_d = ctx->wf[1].as<float4>();
+  w.thr = ctx->wf[2].as<float4>();
+  w.color = ctx->wf[3].as<float4>();
+  w.queue[0] = ctx->wf[4].as<uint32_t>();
+  w.queue[1] = ctx->wf[5].as<uint32_t>();
+  w.count = ctx->wf[6].as<uint32_t>();
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+  RT_CUDA(cudaMemsetAsync(w.count, 0, 8, st));
+  // first logic pass reads no queue and fills queue 1
+  int qi = 0;
+  k_wf_logic<true><<<std::min(nblk(n, 256), sms * 8), 256, 0, st>>>(ctx->scene, ctx->camera, a, w, qi, d_accum, ctr);
+  *launches += 1;
+  qi ^= 1;
+  uint32_t live = 0;
+  for (;;) {
+    RT_CUDA(cudaMemcpyAsync(&live, w.count + qi, 4, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    if (live == 0) break;
+    int gb = std::min(nblk(live, 128), sms * 16);
+    if (stats_on)
+      k_wf_extend<true><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
+    else
+      k_wf_extend<false><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
+    k_wf_reset<<<1, 1, 0, st>>>(w.count, qi ^ 1);
+    k_wf_logic<false><<<std::min(nblk(live, 256), sms * 8), 256, 0, st>>>(ctx->scene, ctx->camera, a, w, qi, d_accum, ctr);
+    *launches += 3;
+    *iterations += 1;
+    qi ^= 1;
+  }
+  RT_CUDA(cudaGetLastError());
+  return RT_OK;
+}
+
+extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_rgb, rt_render_stats *stats,
+                         void *stream) {
+  int rc = check_ready(ctx, true, "rt_render");
+  if (rc) return rc;
+  if (!p || !d_accum_rgb || p->height <= 0 || p->width <= 0 || p->spp_count < 0 || p->spp_begin < 0 ||
+      p->max_depth < 0 || (int64_t)p->height * p->width > 0x3fffffff ||
+      (int64_t)p->spp_begin + p->spp_count > 0x7fffffff) {
+    set_error("rt_render: bad parameters");
+    return RT_ERR_INVALID;
+  }
+  RT_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  RenderArgs a;
+  a.height = p->height;
+  a.width = p->width;
+  a.spp_begin = p->spp_begin;
+  a.spp_end = p->spp_begin + p->spp_count;
+  a.max_depth = p->max_depth;
+  a.k0 = (uint32_t)p->seed;
+  a.k1 = (uint32_t)(p->seed >> 32);
+  size_t n = (size_t)p->height * p->width;
+  RT_CUDA(ctx->counters.reserve(sizeof(RenderCounters)));
+  RenderCounters *ctr = ctx->counters.as<RenderCounters>();
+  RT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(RenderCounters), st));
+  if (p->flags & RT_RENDER_CLEAR) RT_CUDA(cudaMemsetAsync(d_accum_rgb, 0, n * 12, st));
+  bool stats_on = (p->flags & RT_RENDER_PROFILE) != 0;
+  bool fused = (p->flags & RT_RENDER_FUSED) != 0;
+  if (!(p->flags & (RT_RENDER_FUSED | RT_RENDER_WAVEFRONT))) {
+    // default strategy: scenes whose nodes + records stay cache resident run fused (no queue traffic)
+    const char *env = getenv("RT_STRATEGY");
+    fused = env ? strcmp(env, "wavefront") != 0 : true;
+  }
+  uint32_t iterations = 0, launches = 0;
+  RT_CUDA(cudaEventRecord(ctx->ev0, st));
+  if (fused) {
+    dim3 grid((p->width + 15) / 16, (p->height + 7) / 8);
+    if (stats_on)
+      k_render_fused<true><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+    else
+      k_render_fused<false><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+    RT_CUDA(cudaGetLastError());
+    launches = 1;
+    iterations = 1;
+  } else {
+    rc = render_wavefront(ctx, a, stats_on, d_accum_rgb, ctr, st, &iterations, &launches);
+    if (rc) return rc;
+  }
+  RT_CUDA(cudaEventRecord(ctx->ev1, st));
+  if (stats) {
+    RenderCounters hc;
+    RT_CUDA(cudaMemcpyAsync(&hc, ctr, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaEventSynchronize(ctx->ev1));
+    RT_CUDA(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    memset(stats, 0, sizeof(*stats));
+    stats->samples = hc.samples;
+    stats->rays = hc.rays;
+    stats->rays_ref_equiv = hc.rays_ref;
+    stats->node_visits = hc.nodes;
+    stats->prim_tests = hc.prims;
+    stats->iterations = iterations;
+    stats->kernel_launches = launches;
+    stats->render_ms = ms;
+  }
+  return RT_OK;
+}
+
+extern "C" int rt_resolve(rt_ctx *ctx, const float *d_accum_rgb, int height, int width, int spp_total, float *d_rgb,
+                          uint8_t *d_rgb8, void *stream) {
+  if (!ctx || !d_accum_rgb || height <= 0 || width <= 0 || spp_total <= 0) {
+    set_error("rt_resolve: bad argument");
+    return RT_ERR_INVALID;
+  }
+  RT_CUDA(cudaSetDevice(ctx->device));
+  int64_t n = (int64_t)height * width * 3;
+  k_resolve<<<nblk((size_t)n, 256), 256, 0, (cudaStream_t)stream>>>(d_accum_rgb, n, spp_total, d_rgb, d_rgb8);
+  RT_CUDA(cudaGetLastError());
+  return RT_OK;
+}
+
+extern "C" int rt_render_host(rt_ctx *ctx, const rt_render_params *p, float *h_accum_rgb, float *h_rgb,
+                              rt_render_stats *stats) {
+  int rc = check_ready(ctx, true, "rt_render_host");
+  if (rc) return rc;
+  if (!p || p->height <= 0 || p->width <= 0) {
+    set_error("rt_render_host: bad parameters");
+    return RT_ERR_INVALID;
+  }
+  RT_CUDA(cudaSetDevice(ctx->device));
+  size_t n = (size_t)p->height * p->width * 3;
+  RT_CUDA(ctx->accum_tmp.reserve(n * 4));
+  rt_render_params q = *p;
+  q.flags |= RT_RENDER_CLEAR;
+  rc = rt_render(ctx, &q, ctx->accum_tmp.as<float>(), stats, nullptr);
+  if (rc) return rc;
+  if (h_accum_rgb) RT_CUDA(cudaMemcpy(h_accum_rgb, ctx->accum_tmp.p, n * 4, cudaMemcpyDeviceToHost));
+  if (h_rgb) {
+    RT_CUDA(ctx->rgb_tmp.reserve(n * 4));
+    rc = rt_resolve(ctx, ctx->accum_tmp.as<float>(), p->height, p->width, std::max(p->spp_count, 1),
+                    ctx->rgb_tmp.as<float>(), nullptr, nullptr);
+    if (rc) return rc;
+    RT_CUDA(cudaMemcpy(h_rgb, ctx->rgb_tmp.p, n * 4, cudaMemcpyDeviceToHost));
+  }
+  RT_CUDA(cudaDeviceSynchronize());
+  return RT_OK;
+}
