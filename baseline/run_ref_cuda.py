@@ -1,0 +1,101 @@
+"""Baseline A: the reference's own CUDA build (baseline/_ref/ref_cuda, built here from
+/root/reference by baseline/Makefile) on one B200, beside the new core on the same inputs.
+MEASUREMENT INFRASTRUCTURE — not product code.  Writes gpurun_out/ref_cuda_<tag>.json.
+
+For every scene: (1) throughput of the reference's PathTracing kernel, timed the reference's way (cudaEvent pair
+around the launch, utils.cu:155-170), best of `reps`; (2) primary-ray hit `t` of the reference's world->Hit vs the
+new core's rt_trace_closest: mismatching bit patterns (the reference default build contracts FMAs; the new core and
+the oracle are one-IEEE-op-per-source-op, so this number is reported, not asserted); (3) image rRMSE between the two
+renders at equal spp (different RNG streams: statistical)."""
+import argparse, importlib, json, os, subprocess, sys, tempfile
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+rt = importlib.import_module("ray-tracing-cuda_b200")
+BIN = os.path.join(ROOT, "baseline", "_ref", "ref_cuda")
+HIT = np.dtype([("t", "<f8"), ("u", "<f8"), ("v", "<f8"), ("normal", "<f4", 3), ("hit", "<i4")])
+
+
+def run_ref(scene, H, W, spp, reps, extra, timeout):
+    cmd = [BIN, scene, str(H), str(W), str(spp), str(reps)] + extra
+    try:
+        p = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+    except subprocess.TimeoutExpired:
+        return {"error": f"timeout {timeout}s"}
+    if p.returncode != 0:
+        return {"error": p.stderr[-400:]}
+    return json.loads(p.stdout.strip().splitlines()[-1])
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--tag", default="r1")
+    ap.add_argument("--scenes", default="spheres,cornell_box,bunny,birthday")
+    ap.add_argument("--image-spp", type=int, default=256)
+    ap.add_argument("--timeout", type=int, default=240)
+    a = ap.parse_args()
+    tmp = tempfile.mkdtemp()
+    ctx = rt.Context(0)
+    out = {}
+    # (scene, H, W, throughput spp, small image H, W)
+    cfg = {"spheres": (225, 400, 16, 90, 160), "cornell_box": (1024, 1024, 8, 128, 128), "bunny": (1080, 1920, 2, 90, 160),
+           "birthday": (1080, 1920, 8, 90, 160), "soup100k": (540, 960, 1, 54, 96)}
+    for name in a.scenes.split(","):
+        H, W, spp, h, w = cfg[name]
+        scene, cam = rt.scenes.by_name(name)
+        extra, ref_scene = [], name
+        if name == "bunny" or name.startswith("soup"):
+            fp = os.path.join(tmp, name + "_faces.bin")
+            scene.meshes[0].astype(np.float32).tofile(fp)
+            extra += ["--faces", fp]
+            if name.startswith("soup"):
+                ref_scene = "mesh"
+                extra += ["--camera"] + [str(float(x)) for x in (*cam.position, *cam.look_at, cam.fov, cam.aspect)]
+        if name == "birthday":
+            tex = scene.textures[0]
+            fp = os.path.join(tmp, "tex.bin")
+            np.ascontiguousarray(tex).tofile(fp)
+            extra += ["--tex", fp, str(tex.shape[0]), str(tex.shape[1])]
+        camera = rt.core.camera_look_at(cam)
+        ctx.commit(scene)
+        ctx.set_camera(camera)
+        res = {}
+        # (1) throughput at the config's resolution
+        res["ref_throughput"] = run_ref(ref_scene, H, W, spp, 3, extra, a.timeout)
+        _, _, st = ctx.render_host(H, W, spp, seed=1)
+        best = min(ctx.render_host(H, W, spp, seed=1)[2].render_ms for _ in range(3))
+        res["new_throughput"] = {"ms_best": best, "msamples_per_s": H * W * spp / best / 1e3, "spp": spp}
+        if "msamples_per_s" in res["ref_throughput"]:
+            res["speedup_vs_ref_cuda"] = res["new_throughput"]["msamples_per_s"] / res["ref_throughput"]["msamples_per_s"]
+        # (2) primary hits and (3) image at small resolution
+        rays = ctx.primary_rays(h, w)
+        rp, hp, ip = (os.path.join(tmp, f"{name}_{x}.bin") for x in ("rays", "hits", "img"))
+        rays.tofile(rp)
+        r = run_ref(ref_scene, h, w, a.image_spp, 1, extra + ["--rays", rp, hp, "--image", ip], a.timeout)
+        res["ref_image_run"] = r
+        if "error" not in r:
+            ref_hits = np.fromfile(hp, dtype=HIT)
+            mine = ctx.trace_closest(rays)
+            hit_m = mine["obj"] >= 0
+            same_hit = (ref_hits["hit"] != 0) == hit_m
+            tb = ref_hits["t"].view(np.uint64) != mine["t"].view(np.uint64)
+            both = (ref_hits["hit"] != 0) & hit_m
+            rel = np.abs(ref_hits["t"][both] - mine["t"][both]) / np.maximum(np.abs(mine["t"][both]), 1e-30)
+            res["primary_hits"] = {"rays": int(len(rays)), "hit_flag_mismatch": int((~same_hit).sum()),
+                                   "t_bits_mismatch": int((tb & both).sum()), "max_rel_t_diff": float(rel.max() if len(rel) else 0)}
+            ref_img = np.fromfile(ip, dtype=np.float32).reshape(h, w, 3) / a.image_spp
+            acc, _, _ = ctx.render_host(h, w, a.image_spp, seed=3)
+            img = acc / a.image_spp
+            acc2, _, _ = ctx.render_host(h, w, a.image_spp, seed=4)
+            img2 = acc2 / a.image_spp
+            rr = lambda x, y: float(np.sqrt(((x - y) ** 2).sum()) / np.sqrt((y ** 2).sum()))
+            res["image"] = {"spp": a.image_spp, "hw": [h, w], "rrmse_new_vs_ref": rr(img, ref_img),
+                            "rrmse_new_vs_new_other_seed": rr(img, img2), "mean_new": float(img.mean()), "mean_ref": float(ref_img.mean())}
+        out[name] = res
+        print(name, json.dumps(res), flush=True)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    json.dump(out, open(os.path.join(ROOT, "gpurun_out", f"ref_cuda_{a.tag}.json"), "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()

@@ -147,6 +147,9 @@ typedef struct rt_render_stats {
   uint32_t kernel_launches;
   float render_ms;        /* device time, CUDA events on `stream` */
   float extend_ms, shade_ms; /* per-stage device time when profiling is enabled, else 0 */
+  float reserved_;
+  uint64_t sched_iters;   /* vote kernel, RT_RENDER_PROFILE only: warp scheduling iterations ...      */
+  uint64_t sched_lanes;   /* ... and lanes that executed in them (sched_lanes / (32*sched_iters) = SIMT use) */
 } rt_render_stats;
 
 /* ---- entry points -------------------------------------------------------------------------- */
@@ -175,7 +178,9 @@ int rt_camera_look_at(const float position[3], const float look_at[3], const flo
 /* Parity hook: replaces HitableList::Hit (hitable_list.cu:7-25) on explicit rays.
  * rays = n x 6 floats (position xyz, direction xyz); the direction is used as stored (callers
  * pass Ray::direction_, i.e. already normalized by Ray::Ray, ray.cu:8-11).
- * mode 0: unified-BVH traversal (product path); mode 1: brute force over every primitive. */
+ * mode 0: unified-BVH traversal (product path); mode 1: sequential scan over every primitive in
+ * list order; modes 2..7: the traversal variants 0..5 of the render kernels (diagnostics: all modes
+ * must return identical hits). */
 int rt_trace_closest_host(rt_ctx *ctx, const float *h_rays, int64_t n, double t_from, double t_to,
                           int mode, rt_hit *h_hits);
 int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t n, double t_from, double t_to,

@@ -97,6 +97,9 @@ class RtRenderStats(C.Structure):
         ("render_ms", C.c_float),
         ("extend_ms", C.c_float),
         ("shade_ms", C.c_float),
+        ("reserved_", C.c_float),
+        ("sched_iters", C.c_uint64),
+        ("sched_lanes", C.c_uint64),
     ]
 
     def as_dict(self):

@@ -372,8 +372,8 @@ struct TravStats {
 };
 
 template <bool STATS>
-__device__ __forceinline__ Hit world_hit_bvh(const DScene &s, const RayQ &r, double t_from, double t_to,
-                                             TravStats *st) {
+__device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r, double t_from, double t_to,
+                                                  TravStats *st) {
   Range rg;
   rg.t_from = t_from;
   rg.t_to = t_to;
@@ -459,6 +459,269 @@ __device__ __forceinline__ Hit world_hit_bvh(const DScene &s, const RayQ &r, dou
   h.rec = b.rec;
   h.seq = 0;
   return h;
+}
+
+// "while-while" form of the same traversal (Aila & Laine 2009): every lane first walks inner nodes
+// until it holds a leaf, then the warp tests leaf records together, so node steps and record tests
+// are not interleaved across lanes.  SPEC: a lane that holds a leaf keeps walking (postponing the
+// leaf) until every lane of the warp holds one.  CULL: the far child is pushed with its entry
+// distance and dropped at pop time when the closest hit has moved in front of it.
+template <bool STATS, bool SPEC, bool CULL>
+__device__ __forceinline__ Hit world_hit_bvh_ww(const DScene &s, const RayQ &r, double t_from, double t_to,
+                                                TravStats *st) {
+  Range rg;
+  rg.t_from = t_from;
+  rg.t_to = t_to;
+  rg.tf_f = float_ge(t_from);
+  Best b;
+  best_init(b, t_to);
+  if (s.sky_obj >= 0) {  // sky.cu:18-27: always a candidate at t = 1e9
+    double t = 1e9;
+    if (t_from <= t && t <= t_to) {
+      b.t = t;
+      b.t_f = 1e9f;
+      b.rec = REC_SKY;
+      b.obj = s.sky_obj;
+      b.sub = 0;
+    }
+  }
+  bool ambiguous = false, overflow = false;
+  if (s.n_recs > 0) {
+    const float idx = 1.0f / r.d.x, idy = 1.0f / r.d.y, idz = 1.0f / r.d.z;
+    const float t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
+    uint2 stack[STACK_SIZE];
+    float stack_t[CULL ? STACK_SIZE : 1];
+    int sp = 0;
+    uint32_t ca = s.root_a, cb = s.root_b;
+    const float4 *__restrict__ nodes = s.nodes;
+    bool done = false;
+    // pops the next node to visit into (ca, cb); false when the stack is exhausted
+    auto pop = [&]() -> bool {
+      while (sp > 0) {
+        --sp;
+        if (CULL) {
+          float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
+          if (stack_t[sp] > t_hi + fabsf(t_hi) * 1e-5f) continue;
+        }
+        uint2 e = stack[sp];
+        ca = e.x;
+        cb = e.y;
+        return true;
+      }
+      return false;
+    };
+    while (!done) {
+      uint32_t leaf_a = 0, leaf_b = 0;  // leaf_b == 0: no leaf held
+      for (;;) {
+        if (cb & LEAF_FLAG) {
+          if (leaf_b) break;  // SPEC: second leaf; (ca, cb) keeps it for the next round
+          leaf_a = ca;
+          leaf_b = cb;
+          if (!pop()) {
+            done = true;
+            break;
+          }
+          if (!SPEC) break;
+        } else {
+          if (STATS) st->nodes += 2;
+          float4 l0 = __ldg(nodes + 2 * (size_t)ca), l1 = __ldg(nodes + 2 * (size_t)ca + 1);
+          float4 r0 = __ldg(nodes + 2 * (size_t)cb), r1 = __ldg(nodes + 2 * (size_t)cb + 1);
+          float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
+          float ax = (l0.x - r.o.x) * idx, bx = (l1.x - r.o.x) * idx;
+          float ay = (l0.y - r.o.y) * idy, by = (l1.y - r.o.y) * idy;
+          float az = (l0.z - r.o.z) * idz, bz = (l1.z - r.o.z) * idz;
+          float ln = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_lo));
+          float lf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
+          ax = (r0.x - r.o.x) * idx, bx = (r1.x - r.o.x) * idx;
+          ay = (r0.y - r.o.y) * idy, by = (r1.y - r.o.y) * idy;
+          az = (r0.z - r.o.z) * idz, bz = (r1.z - r.o.z) * idz;
+          float rn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_lo));
+          float rf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
+          bool hl = ln <= lf + fabsf(lf) * 1e-5f, hr = rn <= rf + fabsf(rf) * 1e-5f;
+          uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
+          uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
+          if (hl && hr) {
+            bool left_first = ln <= rn;
+            if (sp < STACK_SIZE) {
+              stack[sp] = left_first ? make_uint2(ra, rb) : make_uint2(la, lb);
+              if (CULL) stack_t[sp] = left_first ? rn : ln;
+              sp++;
+            } else {
+              overflow = true;
+            }
+            ca = left_first ? la : ra;
+            cb = left_first ? lb : rb;
+          } else if (hl) {
+            ca = la;
+            cb = lb;
+          } else if (hr) {
+            ca = ra;
+            cb = rb;
+          } else if (!pop()) {
+            done = true;
+            break;
+          }
+        }
+        if (SPEC) {
+          // stop walking once every lane of the warp holds a leaf (or is finished)
+          if (!__any_sync(__activemask(), leaf_b == 0)) break;
+        }
+      }
+      if (leaf_b) {
+        int k = (int)leaf_a, end = (int)(leaf_a + (leaf_b & ~LEAF_FLAG));
+        while (k < end) {
+          if (STATS) st->prims++;
+          k += rec_test(s.recs, k, r, rg, b, ambiguous);
+        }
+      }
+    }
+  }
+  if (ambiguous || overflow) return world_hit_seq(s, r, t_from, t_to);
+  Hit h;
+  h.t = b.rec == REC_NONE ? 0.0 : b.t;
+  h.rec = b.rec;
+  h.seq = 0;
+  return h;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Resumable form of the same traversal: one call = one node step or one record test.  The render
+// kernel k_render_vote keeps a Trav per lane and lets the WARP decide each iteration which kind of
+// step to execute (the kind most lanes are waiting for), so that node steps, record tests and
+// shading are never interleaved lane by lane.  Visit order, culling and tie rules are those of
+// world_hit_bvh_ifif: identical hits.
+// ------------------------------------------------------------------------------------------------
+enum : int { ST_GEN = 0, ST_NODE = 1, ST_LEAF = 2, ST_SHADE = 3, ST_DONE = 4 };
+
+struct Trav {
+  RayQ r;
+  float idx, idy, idz, t_lo;
+  Best b;
+  uint32_t ca, cb;  // ST_NODE: the (a, b) words of an inner node; ST_LEAF: next record, end record
+  int sp;
+  bool ambiguous, overflow;
+};
+
+__device__ __forceinline__ int trav_set(Trav &tv, uint32_t a, uint32_t b) {
+  if (b & LEAF_FLAG) {
+    tv.ca = a;
+    tv.cb = a + (b & ~LEAF_FLAG);
+    return ST_LEAF;
+  }
+  tv.ca = a;
+  tv.cb = b;
+  return ST_NODE;
+}
+__device__ __forceinline__ int trav_pop(Trav &tv, const uint2 *stack) {
+  if (tv.sp == 0) return ST_SHADE;
+  uint2 e = stack[--tv.sp];
+  return trav_set(tv, e.x, e.y);
+}
+// Starts a query on tv.r; returns the first state.
+__device__ __forceinline__ int trav_begin(const DScene &s, Trav &tv, const Range &rg) {
+  best_init(tv.b, rg.t_to);
+  if (s.sky_obj >= 0) {  // sky.cu:18-27
+    double t = 1e9;
+    if (rg.t_from <= t && t <= rg.t_to) {
+      tv.b.t = t;
+      tv.b.t_f = 1e9f;
+      tv.b.rec = REC_SKY;
+      tv.b.obj = s.sky_obj;
+      tv.b.sub = 0;
+    }
+  }
+  tv.ambiguous = tv.overflow = false;
+  tv.sp = 0;
+  if (s.n_recs <= 0) return ST_SHADE;
+  tv.idx = 1.0f / tv.r.d.x;
+  tv.idy = 1.0f / tv.r.d.y;
+  tv.idz = 1.0f / tv.r.d.z;
+  tv.t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
+  return trav_set(tv, s.root_a, s.root_b);
+}
+__device__ __forceinline__ int trav_node_step(const DScene &s, Trav &tv, uint2 *stack) {
+  const float4 *__restrict__ nodes = s.nodes;
+  const RayQ &r = tv.r;
+  float4 l0 = __ldg(nodes + 2 * (size_t)tv.ca), l1 = __ldg(nodes + 2 * (size_t)tv.ca + 1);
+  float4 r0 = __ldg(nodes + 2 * (size_t)tv.cb), r1 = __ldg(nodes + 2 * (size_t)tv.cb + 1);
+  float t_hi = tv.b.t_f + fabsf(tv.b.t_f) * 1e-5f;
+  float ax = (l0.x - r.o.x) * tv.idx, bx = (l1.x - r.o.x) * tv.idx;
+  float ay = (l0.y - r.o.y) * tv.idy, by = (l1.y - r.o.y) * tv.idy;
+  float az = (l0.z - r.o.z) * tv.idz, bz = (l1.z - r.o.z) * tv.idz;
+  float ln = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tv.t_lo));
+  float lf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
+  ax = (r0.x - r.o.x) * tv.idx, bx = (r1.x - r.o.x) * tv.idx;
+  ay = (r0.y - r.o.y) * tv.idy, by = (r1.y - r.o.y) * tv.idy;
+  az = (r0.z - r.o.z) * tv.idz, bz = (r1.z - r.o.z) * tv.idz;
+  float rn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tv.t_lo));
+  float rf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
+  bool hl = ln <= lf + fabsf(lf) * 1e-5f, hr = rn <= rf + fabsf(rf) * 1e-5f;
+  uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
+  uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
+  if (hl && hr) {
+    bool left_first = ln <= rn;
+    if (tv.sp < STACK_SIZE) {
+      stack[tv.sp++] = left_first ? make_uint2(ra, rb) : make_uint2(la, lb);
+    } else {
+      tv.overflow = true;
+    }
+    return trav_set(tv, left_first ? la : ra, left_first ? lb : rb);
+  }
+  if (hl) return trav_set(tv, la, lb);
+  if (hr) return trav_set(tv, ra, rb);
+  return trav_pop(tv, stack);
+}
+__device__ __forceinline__ int trav_leaf_step(const DScene &s, Trav &tv, const Range &rg, const uint2 *stack) {
+  int k = (int)tv.ca;
+  k += rec_test(s.recs, k, tv.r, rg, tv.b, tv.ambiguous);
+  tv.ca = (uint32_t)k;
+  if (k >= (int)tv.cb) return trav_pop(tv, stack);
+  return ST_LEAF;
+}
+__device__ __forceinline__ Hit trav_finish(const DScene &s, const Trav &tv, const Range &rg) {
+  if (tv.ambiguous || tv.overflow) return world_hit_seq(s, tv.r, rg.t_from, rg.t_to);
+  Hit h;
+  h.t = tv.b.rec == REC_NONE ? 0.0 : tv.b.t;
+  h.rec = tv.b.rec;
+  h.seq = 0;
+  return h;
+}
+// Per-lane driver of the step functions (parity hook / reference for the voting kernel).
+template <bool STATS>
+__device__ __forceinline__ Hit world_hit_bvh_steps(const DScene &s, const RayQ &r, double t_from, double t_to,
+                                                   TravStats *st) {
+  Range rg;
+  rg.t_from = t_from;
+  rg.t_to = t_to;
+  rg.tf_f = float_ge(t_from);
+  Trav tv;
+  tv.r = r;
+  uint2 stack[STACK_SIZE];
+  int state = trav_begin(s, tv, rg);
+  while (state != ST_SHADE) {
+    if (state == ST_NODE) {
+      if (STATS) st->nodes += 2;
+      state = trav_node_step(s, tv, stack);
+    } else {
+      if (STATS) st->prims++;
+      state = trav_leaf_step(s, tv, rg, stack);
+    }
+  }
+  return trav_finish(s, tv, rg);
+}
+
+// Traversal variants (selected per launch; all return identical hits):
+//   0 if-if (round-1 first kernel)   1 while-while   2 while-while + speculative leaf postponement
+//   3 = 1 + pop-time culling         4 = 2 + pop-time culling         5 = resumable steps (vote kernel)
+template <bool STATS, int TRAV>
+__device__ __forceinline__ Hit world_hit_bvh(const DScene &s, const RayQ &r, double t_from, double t_to,
+                                             TravStats *st) {
+  if (TRAV == 0) return world_hit_bvh_ifif<STATS>(s, r, t_from, t_to, st);
+  if (TRAV == 1) return world_hit_bvh_ww<STATS, false, false>(s, r, t_from, t_to, st);
+  if (TRAV == 2) return world_hit_bvh_ww<STATS, true, false>(s, r, t_from, t_to, st);
+  if (TRAV == 3) return world_hit_bvh_ww<STATS, false, true>(s, r, t_from, t_to, st);
+  if (TRAV == 5) return world_hit_bvh_steps<STATS>(s, r, t_from, t_to, st);
+  return world_hit_bvh_ww<STATS, true, true>(s, r, t_from, t_to, st);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -43,7 +43,7 @@ struct DevBuf {
 };
 
 struct RenderCounters {  // device-side counters of one rt_render call
-  unsigned long long samples, rays, rays_ref, nodes, prims, seq_fallbacks;
+  unsigned long long samples, rays, rays_ref, nodes, prims, seq_fallbacks, sched_iters, sched_lanes;
 };
 
 }  // namespace rtc

@@ -11,6 +11,10 @@
 
 #include "rt_internal.h"
 
+#ifndef RT_DEFAULT_TRAV
+#define RT_DEFAULT_TRAV 0  // traversal loop of the parity hook and the wavefront extend kernel
+#endif
+
 namespace rtc {
 
 struct RenderArgs {
@@ -28,7 +32,17 @@ __global__ void __launch_bounds__(128) k_trace_closest(DScene s, const float *__
   RayQ r;
   r.o = mk(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]);
   r.d = mk(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]);
-  Hit h = mode == 1 ? world_hit_seq(s, r, t_from, t_to) : world_hit_bvh<false>(s, r, t_from, t_to, nullptr);
+  Hit h;
+  switch (mode) {
+    case 1: h = world_hit_seq(s, r, t_from, t_to); break;
+    case 2: h = world_hit_bvh<false, 0>(s, r, t_from, t_to, nullptr); break;
+    case 3: h = world_hit_bvh<false, 1>(s, r, t_from, t_to, nullptr); break;
+    case 4: h = world_hit_bvh<false, 2>(s, r, t_from, t_to, nullptr); break;
+    case 5: h = world_hit_bvh<false, 3>(s, r, t_from, t_to, nullptr); break;
+    case 6: h = world_hit_bvh<false, 4>(s, r, t_from, t_to, nullptr); break;
+    case 7: h = world_hit_bvh<false, 5>(s, r, t_from, t_to, nullptr); break;
+    default: h = world_hit_bvh<false, RT_DEFAULT_TRAV>(s, r, t_from, t_to, nullptr); break;
+  }
   rt_hit o;
   if (h.rec == REC_NONE) {
     o.t = 0;
@@ -141,7 +155,7 @@ __device__ __forceinline__ void flush_counters(RenderCounters *ctr, unsigned lon
 // ---- fused kernel: one thread per pixel, paths regenerated in registers ---------------------------
 // Each lane runs its pixel's samples in increasing order and starts the next sample the moment the
 // current path ends, so a warp stays full until its pixels run out of samples.  No queue traffic.
-template <bool STATS>
+template <bool STATS, int TRAV>
 __global__ void __launch_bounds__(128) k_render_fused(DScene s, DCamera cam, RenderArgs a, float *__restrict__ accum,
                                                       RenderCounters *ctr) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -176,7 +190,7 @@ __global__ void __launch_bounds__(128) k_render_fused(DScene s, DCamera cam, Ren
     n_rays_ref++;
     bool alive = depth < a.max_depth;  // ray_tracing.cu:23: the query at depth == limit yields 0
     if (alive) {
-      Hit h = world_hit_bvh<STATS>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
+      Hit h = world_hit_bvh<STATS, TRAV>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
       n_rays++;
       if (STATS) {
         n_nodes += ts.nodes;
@@ -200,6 +214,119 @@ __global__ void __launch_bounds__(128) k_render_fused(DScene s, DCamera cam, Ren
   flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims);
 }
 
+
+// ---- vote kernel: the fused kernel as a warp-scheduled state machine ------------------------------
+// Same work as k_render_fused (one lane per pixel, samples in increasing order, paths regenerated in
+// registers) but every lane carries an explicit state — GEN (needs a camera sample), NODE (inner-node
+// step pending), LEAF (record test pending), SHADE (query finished) — and each iteration the warp
+// executes ONE kind of step: the kind most of its lanes are waiting for.  Lanes in other states keep
+// their state and wait, so their number grows until they are the majority.  This sorts the work of
+// a warp by kind in time instead of in memory (no queues): node steps, record tests and shading each
+// run with most lanes active instead of the 8 of 32 measured for the lane-by-lane loop
+// (profiles/r01_a_cornell_fused_ncu_summary.txt).  Image and counters are identical to the fused kernel.
+template <bool STATS>
+__global__ void __launch_bounds__(128) k_render_vote(DScene s, DCamera cam, RenderArgs a, float *__restrict__ accum,
+                                                     RenderCounters *ctr) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+  const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = i < a.height && j < a.width;
+  const int idx = i * a.width + j;
+  PathKey pk;
+  pk.pixel = (uint32_t)idx;
+  pk.sample = 0;
+  pk.k0 = a.k0;
+  pk.k1 = a.k1;
+  int k = a.spp_begin;
+  V3 color = mk(0.f, 0.f, 0.f), T = mk(1.f, 1.f, 1.f);
+  int depth = 0;
+  int state = inside ? ST_GEN : ST_DONE;
+  Range rg;
+  rg.t_from = 1e-3;
+  rg.t_to = (double)CUDART_INF_F;
+  rg.tf_f = float_ge(1e-3);
+  Trav tv;
+  tv.r.o = tv.r.d = mk(0.f, 0.f, 0.f);
+  tv.sp = 0;
+  uint2 stack[STACK_SIZE];
+  unsigned long long n_samples = 0, n_rays = 0, n_rays_ref = 0, n_nodes = 0, n_prims = 0, n_iters = 0, n_lanes = 0;
+  // next closest-hit query of the current path, or the end of the path at the depth limit
+  // (ray_tracing.cu:23: the query at depth == limit yields 0 and is skipped)
+  auto start_query = [&]() {
+    n_rays_ref++;
+    if (depth < a.max_depth) {
+      n_rays++;
+      state = trav_begin(s, tv, rg);
+    } else {
+      k++;
+      state = ST_GEN;
+    }
+  };
+  for (;;) {
+    const unsigned mN = __ballot_sync(0xffffffffu, state == ST_NODE);
+    const unsigned mL = __ballot_sync(0xffffffffu, state == ST_LEAF);
+    const unsigned mS = __ballot_sync(0xffffffffu, state == ST_SHADE);
+    const unsigned mG = __ballot_sync(0xffffffffu, state == ST_GEN);
+    if ((mN | mL | mS | mG) == 0u) break;
+    int pick = ST_NODE, best = __popc(mN);
+    int c = __popc(mL);
+    if (c > best) {
+      pick = ST_LEAF;
+      best = c;
+    }
+    c = __popc(mS);
+    if (c > best) {
+      pick = ST_SHADE;
+      best = c;
+    }
+    c = __popc(mG);
+    if (c > best) {
+      pick = ST_GEN;
+      best = c;
+    }
+    if (STATS && lane == 0) {
+      n_iters++;
+      n_lanes += best;
+    }
+    if (state != pick) continue;
+    if (pick == ST_NODE) {
+      if (STATS) n_nodes += 2;
+      state = trav_node_step(s, tv, stack);
+    } else if (pick == ST_LEAF) {
+      if (STATS) n_prims++;
+      state = trav_leaf_step(s, tv, rg, stack);
+    } else if (pick == ST_SHADE) {
+      Hit h = trav_finish(s, tv, rg);
+      bool alive = h.rec != REC_NONE && shade_hit(s, tv.r, h, pk, depth, T, color);
+      if (alive) {
+        depth++;
+        start_query();
+      } else {
+        k++;
+        state = ST_GEN;
+      }
+    } else {  // ST_GEN
+      if (k >= a.spp_end) {
+        accum[3 * (size_t)idx + 0] += color.x;
+        accum[3 * (size_t)idx + 1] += color.y;
+        accum[3 * (size_t)idx + 2] += color.z;
+        state = ST_DONE;
+      } else {
+        pk.sample = (uint32_t)k;
+        tv.r = camera_sample(cam, i, j, a.height, a.width, pk);
+        T = mk(1.f, 1.f, 1.f);
+        depth = 0;
+        n_samples++;
+        start_query();
+      }
+    }
+  }
+  flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims);
+  if (STATS && lane == 0) {
+    atomicAdd(&ctr->sched_iters, n_iters);
+    atomicAdd(&ctr->sched_lanes, n_lanes);
+  }
+}
 
 // ---- wavefront pipeline ------------------------------------------------------------------------------
 // One path slot per pixel, paths regenerated in place (sample k+1 starts in the slot the moment
@@ -325,7 +452,7 @@ __global__ void __launch_bounds__(256) k_wf_logic(DScene s, DCamera cam, RenderA
   flush_counters(ctr, n_samples, 0, n_rays_ref, 0, 0);
 }
 
-template <bool STATS>
+template <bool STATS, int TRAV>
 __global__ void __launch_bounds__(128) k_wf_extend(DScene s, WfState w, int qi, RenderCounters *ctr) {
   const uint32_t n_in = w.count[qi];
   unsigned long long n_rays = 0, n_nodes = 0, n_prims = 0;
@@ -337,7 +464,7 @@ __global__ void __launch_bounds__(128) k_wf_extend(DScene s, WfState w, int qi, 
     RayQ ray;
     ray.o = xyz(ro);
     ray.d = xyz(rd);
-    Hit h = world_hit_bvh<STATS>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
+    Hit h = world_hit_bvh<STATS, TRAV>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
     n_rays++;
     // only the two .w words change: t and the record
     reinterpret_cast<float *>(w.ray_o + slot)[3] = float(h.t);
@@ -373,6 +500,17 @@ using namespace rtc;
 namespace {
 inline int nblk(size_t n, int b) { return (int)((n + b - 1) / b); }
 
+// Traversal variant of the render kernels: RT_TRAV=0..4 overrides the default (diagnostics).
+// Default (measured, profiles/r01_b_sweep_variants.txt): scenes of a few thousand records are
+// dominated by incoherent bounce rays in a cache-resident tree, where the while-while loop wins;
+// large meshes, dominated by coherent primary rays / long traversals, run the if-if loop faster.
+int trav_variant(const rt_ctx *ctx) {
+  const char *e = getenv("RT_TRAV");
+  int dflt = ctx->scene.n_recs <= 4096 ? 1 : 0;
+  int v = e ? atoi(e) : dflt;
+  return (v < 0 || v > 5) ? dflt : v;
+}
+
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
   if (!ctx) {
     set_error(std::string(who) + ": null context");
@@ -394,7 +532,7 @@ extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t
                                        rt_hit *d_hits, void *stream) {
   int rc = check_ready(ctx, false, "rt_trace_closest");
   if (rc) return rc;
-  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode != 0 && mode != 1)) {
+  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 7)) {
     set_error("rt_trace_closest: bad argument");
     return RT_ERR_INVALID;
   }
@@ -469,9 +607,9 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, flo
     if (live == 0) break;
     int gb = std::min(nblk(live, 128), sms * 16);
     if (stats_on)
-      k_wf_extend<true><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
+      k_wf_extend<true, RT_DEFAULT_TRAV><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
     else
-      k_wf_extend<false><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
+      k_wf_extend<false, RT_DEFAULT_TRAV><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
     k_wf_reset<<<1, 1, 0, st>>>(w.count, qi ^ 1);
     k_wf_logic<false><<<std::min(nblk(live, 256), sms * 8), 256, 0, st>>>(ctx->scene, ctx->camera, a, w, qi, d_accum, ctr);
     *launches += 3;
@@ -518,10 +656,29 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
   RT_CUDA(cudaEventRecord(ctx->ev0, st));
   if (fused) {
     dim3 grid((p->width + 15) / 16, (p->height + 7) / 8);
-    if (stats_on)
-      k_render_fused<true><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
-    else
-      k_render_fused<false><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+    int trav = trav_variant(ctx);
+#define RT_FUSED_CASE(T)                                                                               \
+  case T:                                                                                              \
+    if (stats_on)                                                                                      \
+      k_render_fused<true, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);     \
+    else                                                                                               \
+      k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);    \
+    break;
+    switch (trav) {
+      case 5:
+        if (stats_on)
+          k_render_vote<true><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+        else
+          k_render_vote<false><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+        break;
+      RT_FUSED_CASE(0)
+      RT_FUSED_CASE(1)
+      RT_FUSED_CASE(2)
+      RT_FUSED_CASE(3)
+      default:
+      RT_FUSED_CASE(4)
+    }
+#undef RT_FUSED_CASE
     RT_CUDA(cudaGetLastError());
     launches = 1;
     iterations = 1;
@@ -546,6 +703,8 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     stats->iterations = iterations;
     stats->kernel_launches = launches;
     stats->render_ms = ms;
+    stats->sched_iters = hc.sched_iters;
+    stats->sched_lanes = hc.sched_lanes;
   }
   return RT_OK;
 }

@@ -97,6 +97,19 @@ def test_sequential_scan_mode_bit_exact(ctx, name):
     assert len(ck.hits_equal(got, want, _fields(name))) == 0
 
 
+@pytest.mark.parametrize("name", ["cornell_box", "spheres", "bunny9k", "soup100k"])
+def test_traversal_variants_identical(ctx, name):
+    """Every traversal variant of the render kernels (modes 2..6) returns the oracle's hits."""
+    s, cam, o = _setup(ctx, name)
+    lo, hi = _BOX[name]
+    rr = np.concatenate([ctx.primary_rays(54, 96), ck.random_rays(30000, 21, lo, hi)])
+    want = o.trace(rr, quirks=0)
+    for mode in (2, 3, 4, 5, 6, 7):
+        got = ctx.trace_closest(rr, mode=mode)
+        bad = ck.hits_equal(got, want, _fields(name))
+        assert len(bad) == 0, (mode, len(bad), got[bad[:3]], want[bad[:3]])
+
+
 def test_mixed_scene_all_primitive_types(ctx):
     rng = np.random.RandomState(3)
     mats = [scenes._mat(abi.RT_MAT_LAMBERTIAN, (0.5, 0.5, 0.5)), scenes._mat(abi.RT_MAT_METAL, (0.7, 0.6, 0.5), fuzz=0.3),
@@ -171,6 +184,19 @@ def test_render_bit_exact_vs_oracle(ctx, name, hw, spp):
     ctx.render_device(d.data_ptr(), H, W, spp - spp // 2, spp // 2, seed=1234)
     torch.cuda.synchronize()
     assert (d.cpu().numpy().view(np.uint32) == a.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("name,hw,spp", [("cornell_box", (72, 128), 8), ("spheres", (54, 96), 8), ("bunny9k", (54, 96), 4)])
+def test_render_kernel_variants_bit_exact(ctx, name, hw, spp, monkeypatch):
+    """Every fused-kernel variant (RT_TRAV 0..5; 5 = warp-scheduled vote kernel) renders the oracle's image."""
+    s, cam, o = _setup(ctx, name)
+    H, W = hw
+    want, cnt = o.render_product(H, W, 0, spp, 99)
+    for trav in range(6):
+        monkeypatch.setenv("RT_TRAV", str(trav))
+        got, _, st = ctx.render_host(H, W, spp, seed=99, flags=abi.RT_RENDER_FUSED)
+        assert (got.view(np.uint32) == want.view(np.uint32)).all(), trav
+        assert (st.samples, st.rays, st.rays_ref_equiv) == tuple(int(x) for x in cnt), trav
 
 
 def test_render_textured_sphere_close(ctx):

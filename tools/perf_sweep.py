@@ -1,0 +1,62 @@
+"""Kernel-variant sweep on one GPU (diagnostics, not the bench): Msamples/s of rt_render per scene and
+RT_TRAV variant, plus node/record visits per ray from the stats build.
+usage: python tools/perf_sweep.py [--trav 0,1,2,3,4] [--scenes cornell_box,spheres,bunny,birthday,soup1m]"""
+import argparse, importlib, json, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+import torch
+rt = importlib.import_module("ray-tracing-cuda_b200")
+
+CASES = {"cornell_box": (1024, 1024, 64), "spheres": (720, 1280, 32), "bunny": (1080, 1920, 16),
+         "birthday": (1080, 1920, 32), "soup1m": (1080, 1920, 4), "soup100k": (1080, 1920, 8)}
+
+def scene_of(name):
+    if name.startswith("soup"):
+        n = {"soup1m": 1000000, "soup100k": 100000, "soup10m": 10000000}[name]
+        return rt.scenes.soup(n)
+    return rt.scenes.by_name(name)
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--trav", default="0,1,2,3,4")
+    ap.add_argument("--scenes", default="cornell_box,spheres,bunny,birthday,soup1m")
+    ap.add_argument("--strategy", default="fused")
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--env", default="", help="extra VAR=a|b|c axis")
+    a = ap.parse_args()
+    ctx = rt.Context(0)
+    flags = rt.abi.RT_RENDER_FUSED if a.strategy == "fused" else rt.abi.RT_RENDER_WAVEFRONT
+    extra = [None]
+    if a.env:
+        var, vals = a.env.split("=")
+        extra = [(var, v) for v in vals.split("|")]
+    res = {}
+    for name in a.scenes.split(","):
+        H, W, spp = CASES[name]
+        scene, cam = scene_of(name)
+        ctx.set_camera(rt.core.camera_look_at(cam))
+        acc = torch.zeros(H, W, 3, device="cuda")
+        for ex in extra:
+            if ex:
+                os.environ[ex[0]] = ex[1]
+            bs = ctx.commit(scene)
+            for tv in a.trav.split(","):
+                os.environ["RT_TRAV"] = tv
+                st = ctx.render_device(acc.data_ptr(), H, W, 1, 0, seed=1, flags=flags | rt.abi.RT_RENDER_CLEAR | rt.abi.RT_RENDER_PROFILE)
+                nodes, prims, rays1 = st.node_visits, st.prim_tests, st.rays
+                simt = st.sched_lanes / max(32 * st.sched_iters, 1)
+                best = 1e30
+                for _ in range(a.reps):
+                    st = ctx.render_device(acc.data_ptr(), H, W, spp, 0, seed=1, flags=flags | rt.abi.RT_RENDER_CLEAR)
+                    best = min(best, st.render_ms)
+                key = f"{name} trav={tv}" + (f" {ex[0]}={ex[1]}" if ex else "")
+                res[key] = dict(msamples=H * W * spp / best / 1e3, mrays=st.rays / best / 1e3, ms=best,
+                                nodes_per_ray=nodes / max(rays1, 1), recs_per_ray=prims / max(rays1, 1),
+                                build_ms=bs.build_ms, nodes=bs.n_nodes, depth=bs.max_depth, simt=simt)
+                r = res[key]
+                print(f"{key:40s} {r['msamples']:9.1f} Msamp/s {r['mrays']:9.1f} Mrays/s {r['ms']:8.2f} ms  nodes/ray {r['nodes_per_ray']:.1f} recs/ray {r['recs_per_ray']:.1f}  build {r['build_ms']:.2f} ms depth {r['depth']} simt {r['simt']:.2f}", flush=True)
+    print(json.dumps(res))
+
+if __name__ == "__main__":
+    main()
