@@ -445,7 +445,7 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
         if (n > 0) {
           size_t bytes = (size_t)n * stride * 4;
           RT_CUDA(ctx->scratch[0].reserve(bytes));
-          RT_CUDA(cudaMemcpyAsync(ctx->scratch[0].p, m.h_faces, bytes, cudaMemcpyHostToDevice, st));
+          RT_CUDA(cudaMemcpyAsync(ctx->scratch[0].p, m.h_faces, bytes, cudaMemcpyDefault, st));
           const uint32_t *perm = nullptr;
           if (n > kRefLeafMin) {  // bvh.cuh:116-117: stable sort on positions_[0].x
             RT_CUDA(ctx->scratch[1].reserve((size_t)n * 4));

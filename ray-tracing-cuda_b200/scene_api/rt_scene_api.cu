@@ -1,0 +1,543 @@
+// rt_scene_api.cu — drivers of the scene API: Main / DistributedMain (utils.cu:132-242), the flattening of
+// the device-resident object list into the C-ABI's scene description, and the small utilities of utils.cu
+// (CudaRandomInit :43-47, WriteImage :87-96, GatherImageData :115-130, BaseName/ParentPath :26-41).
+//
+// All rendering goes through librtcore.so (include/rtcore.h); nothing here traces a ray.
+#include "rt_scene_api.cuh"
+
+#include <unistd.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <map>
+#include <thread>
+
+#include "../../include/rtcore.h"
+
+#define RTAPI_CUDA(call)                                                     \
+  do {                                                                       \
+    cudaError_t e_ = (call);                                                 \
+    CHECK(e_ == cudaSuccess) << #call << ": " << cudaGetErrorString(e_);     \
+  } while (0)
+#define RTAPI_RT(call)                                                       \
+  do {                                                                       \
+    int rc_ = (call);                                                        \
+    CHECK(rc_ == RT_OK) << #call << ": " << rt_last_error_string();          \
+  } while (0)
+
+// ---- small utilities ---------------------------------------------------------------------------------
+std::string BaseName(const std::string &path) {
+  size_t k = path.find_last_of("/\\");
+  return k == std::string::npos ? path : path.substr(k + 1);
+}
+
+std::string ParentPath(const std::string &path) {
+  // the reference ignores a trailing separator and returns "" when there is no parent (utils.cu:33-41)
+  if (path.size() < 2) return "";
+  size_t k = path.find_last_of("/\\", path.size() - 2);
+  return k == std::string::npos ? "" : path.substr(0, k);
+}
+
+__global__ void CudaRandomInit(uint64_t seed, curandState *state, int n) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < n) curand_init(seed, idx, 0, &state[idx]);
+}
+
+cudaTextureObject_t ImageTexture::CreateCudaTextureObj(uint8_t *dev_buffer, int height, int width,
+                                                       uint64_t pitch_in_bytes) {
+  cudaResourceDesc res;
+  memset(&res, 0, sizeof(res));
+  res.resType = cudaResourceTypePitch2D;
+  res.res.pitch2D.devPtr = dev_buffer;
+  res.res.pitch2D.desc = cudaCreateChannelDesc<uchar4>();
+  res.res.pitch2D.width = width;
+  res.res.pitch2D.height = height;
+  res.res.pitch2D.pitchInBytes = pitch_in_bytes;
+  cudaTextureDesc tex;
+  memset(&tex, 0, sizeof(tex));  // point filter, wrap addressing, as the zeroed descriptor of the reference
+  tex.readMode = cudaReadModeNormalizedFloat;
+  tex.normalizedCoords = 1;
+  cudaTextureObject_t obj = 0;
+  RTAPI_CUDA(cudaCreateTextureObject(&obj, &res, &tex, nullptr));
+  return obj;
+}
+
+void WriteImage(const std::vector<glm::vec3> &pixels, int height, int width, const std::string &path) {
+  std::vector<uint8_t> rgb8((size_t)height * width * 3);
+  for (size_t i = 0; i < (size_t)height * width; i++)
+    for (int c = 0; c < 3; c++) rgb8[3 * i + c] = (uint8_t)(pixels[i][c] * 255);  // utils.cu:90-93: truncation
+  LOG(INFO) << "Writing image to \"" << path << "\"";
+  bool ppm = path.size() > 4 && path.compare(path.size() - 4, 4, ".ppm") == 0;
+  RTAPI_RT(ppm ? rt_write_ppm(path.c_str(), width, height, rgb8.data())
+               : rt_write_jpeg(path.c_str(), width, height, rgb8.data(), 100));
+}
+
+// ---- flattening: device object list -> rt_hitable / rt_material records -------------------------------
+namespace {
+
+struct FlatRec {
+  rt_hitable h;           // material = -1 here; resolved on the host from material_ptr
+  rt_material m;          // description of *material_ptr (texture = -1, or -2 when tex_obj is an image)
+  unsigned long long material_ptr, tex_obj, faces_ptr;
+  int32_t n_faces, has_uv;
+};
+
+__device__ void DescribeTexture(const Texture *t, FlatRec *out) {
+  if (t && t->rt_kind() == rtapi::kTexImage) {
+    out->m.texture = -2;
+    out->tex_obj = (unsigned long long)static_cast<const ImageTexture *>(t)->image_texture();
+  } else if (t && t->rt_kind() == rtapi::kTexConstant) {
+    glm::vec3 c = static_cast<const ConstantTexture *>(t)->color();
+    out->m.color[0] = c.x, out->m.color[1] = c.y, out->m.color[2] = c.z;
+  }
+}
+
+__device__ void DescribeMaterial(Material *mp, FlatRec *out) {
+  out->material_ptr = (unsigned long long)mp;
+  out->tex_obj = 0;
+  rt_material &m = out->m;
+  m.type = -1;
+  m.texture = -1;
+  m.color[0] = m.color[1] = m.color[2] = 0.f;
+  m.fuzz = 0.f;
+  m.ior = 0.0;
+  if (!mp) return;
+  switch (mp->rt_kind()) {
+    case rtapi::kMatLambertian:
+      m.type = RT_MAT_LAMBERTIAN;
+      DescribeTexture(static_cast<Lambertian *>(mp)->texture_ptr(), out);
+      break;
+    case rtapi::kMatMetal: {
+      m.type = RT_MAT_METAL;
+      glm::vec3 c = static_cast<Metal *>(mp)->albedo();
+      m.color[0] = c.x, m.color[1] = c.y, m.color[2] = c.z;
+      m.fuzz = static_cast<Metal *>(mp)->fuzz();
+      break;
+    }
+    case rtapi::kMatDielectric: {
+      m.type = RT_MAT_DIELECTRIC;
+      glm::vec3 c = static_cast<Dielectric *>(mp)->attenuation();
+      m.color[0] = c.x, m.color[1] = c.y, m.color[2] = c.z;
+      m.ior = static_cast<Dielectric *>(mp)->refractive_index();
+      break;
+    }
+    case rtapi::kMatDiffuseLight:
+      m.type = RT_MAT_DIFFUSE_LIGHT;
+      DescribeTexture(static_cast<DiffuseLight *>(mp)->texture_ptr(), out);
+      break;
+    case rtapi::kMatSky:
+      m.type = RT_MAT_SKY;
+      break;
+    default:
+      break;
+  }
+}
+
+__device__ void ClearRec(FlatRec *r, int type, int group) {
+  memset(r, 0, sizeof(*r));
+  r->h.type = type;
+  r->h.material = -1;
+  r->h.mesh = -1;
+  r->h.group = group;
+}
+__device__ void PutPoint(float *dst, glm::vec3 p) { dst[0] = p.x, dst[1] = p.y, dst[2] = p.z; }
+
+__device__ void PutParallelogram(const Parallelogram &pg, int group, FlatRec *out) {
+  ClearRec(out, RT_HIT_PARALLELOGRAM, group);
+  for (int k = 0; k < 4; k++) PutPoint(out->h.p[k], pg.point(k));
+  DescribeMaterial(pg.material_ptr(), out);
+}
+
+// Number of flat records under one Hitable (nested lists included), and the records themselves.
+__device__ int CountFlat(const Hitable *h) {
+  if (!h) return 0;
+  switch (h->rt_kind()) {
+    case rtapi::kHitList: {
+      const HitableList *l = static_cast<const HitableList *>(h);
+      int n = 0;
+      for (int i = 0; i < l->list_len(); i++) n += CountFlat(l->at(i));
+      return n;
+    }
+    case rtapi::kHitParallelepiped:
+      return static_cast<const Parallelepiped *>(h)->face_count();
+    case rtapi::kHitSphere:
+    case rtapi::kHitTriangle:
+    case rtapi::kHitParallelogram:
+    case rtapi::kHitSky:
+    case rtapi::kHitMesh:
+    case rtapi::kHitMeshUV:
+      return 1;
+    default:
+      return 0;  // AABB and unknown objects are not renderable
+  }
+}
+
+__device__ int EmitFlat(Hitable *h, int group, FlatRec *out) {
+  if (!h) return 0;
+  switch (h->rt_kind()) {
+    case rtapi::kHitList: {
+      HitableList *l = static_cast<HitableList *>(h);
+      int n = 0;
+      for (int i = 0; i < l->list_len(); i++) n += EmitFlat(l->at(i), group, out + n);
+      return n;
+    }
+    case rtapi::kHitParallelepiped: {
+      const Parallelepiped *pp = static_cast<const Parallelepiped *>(h);
+      for (int i = 0; i < pp->face_count(); i++) PutParallelogram(pp->face(i), group, out + i);
+      return pp->face_count();
+    }
+    case rtapi::kHitSphere: {
+      const Sphere *s = static_cast<const Sphere *>(h);
+      ClearRec(out, RT_HIT_SPHERE, -1);
+      PutPoint(out->h.p[0], s->position());
+      out->h.radius = s->radius();
+      DescribeMaterial(s->material_ptr(), out);
+      return 1;
+    }
+    case rtapi::kHitTriangle: {
+      const Triangle *t = static_cast<const Triangle *>(h);
+      ClearRec(out, RT_HIT_TRIANGLE, -1);
+      for (int k = 0; k < 3; k++) PutPoint(out->h.p[k], t->point(k));
+      DescribeMaterial(t->material_ptr(), out);
+      return 1;
+    }
+    case rtapi::kHitParallelogram:
+      PutParallelogram(*static_cast<const Parallelogram *>(h), -1, out);
+      return 1;
+    case rtapi::kHitSky:
+      ClearRec(out, RT_HIT_SKY, -1);
+      DescribeMaterial(static_cast<Sky *>(h)->material_ptr(), out);
+      return 1;
+    case rtapi::kHitMesh: {
+      const BVH<Face<false>, AABB> *b = static_cast<const BVH<Face<false>, AABB> *>(h);
+      ClearRec(out, RT_HIT_MESH, -1);
+      DescribeMaterial(b->material_ptr(), out);
+      out->faces_ptr = (unsigned long long)b->objs();
+      out->n_faces = b->size();
+      out->has_uv = 0;
+      return 1;
+    }
+    case rtapi::kHitMeshUV: {
+      const BVH<Face<true>, AABB> *b = static_cast<const BVH<Face<true>, AABB> *>(h);
+      ClearRec(out, RT_HIT_MESH, -1);
+      DescribeMaterial(b->material_ptr(), out);
+      out->faces_ptr = (unsigned long long)b->objs();
+      out->n_faces = b->size();
+      out->has_uv = 1;
+      return 1;
+    }
+    default:
+      return 0;
+  }
+}
+
+// pass 1: one thread per top-level entry counts its flat records; pass 2 writes them at the scanned offsets
+__global__ void FlattenCount(const HitableList *world, int *counts, int *list_len) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) *list_len = world->list_len();
+  if (i < world->list_len()) counts[i] = CountFlat(world->at(i));
+}
+__global__ void FlattenEmit(const HitableList *world, const int *offsets, FlatRec *out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= world->list_len()) return;
+  // a top-level Parallelepiped gets its own group id (its index in the list)
+  int group = world->at(i) && world->at(i)->rt_kind() == rtapi::kHitParallelepiped ? i : -1;
+  EmitFlat(world->at(i), group, out + offsets[i]);
+}
+
+}  // namespace
+
+// ---- host side: commit the flattened world to the core -------------------------------------------------
+namespace {
+
+struct Options {
+  int height, width, spp, max_depth;
+  uint64_t seed;
+  std::string out, stats;
+};
+
+int EnvInt(const char *name, int dflt) {
+  const char *v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+
+Options ReadOptions(int height, int width, int spp) {
+  Options o;
+  o.height = EnvInt("RT_HEIGHT", height);
+  o.width = EnvInt("RT_WIDTH", width);
+  o.spp = EnvInt("RT_SPP", spp);
+  o.max_depth = EnvInt("RT_MAX_DEPTH", 10);  // TRACE_DEPTH_LIMIT, ray_tracing.cu:10
+  const char *s = getenv("RT_SEED");
+  o.seed = s && *s ? strtoull(s, nullptr, 10) : 1;
+  const char *out = getenv("RT_OUT");
+  o.out = out && *out ? out : "image.jpeg";  // utils.cu:178
+  const char *st = getenv("RT_STATS");
+  o.stats = st ? st : "";
+  return o;
+}
+
+// Walks *d_world on the device, then describes it to the core.  Returns the build statistics.
+rt_build_stats CommitWorld(rt_ctx *ctx, HitableList *d_world, Camera *d_camera) {
+  int *d_counts = nullptr, *d_offsets = nullptr;
+  RTAPI_CUDA(cudaMalloc(&d_counts, sizeof(int) * (HitableList::kMaxHitables + 1)));
+  RTAPI_CUDA(cudaMalloc(&d_offsets, sizeof(int) * HitableList::kMaxHitables));
+  RTAPI_CUDA(cudaMemset(d_counts, 0, sizeof(int) * (HitableList::kMaxHitables + 1)));
+  FlattenCount<<<HitableList::kMaxHitables / 128, 128>>>(d_world, d_counts, d_counts + HitableList::kMaxHitables);
+  std::vector<int> counts(HitableList::kMaxHitables + 1);
+  RTAPI_CUDA(cudaMemcpy(counts.data(), d_counts, sizeof(int) * counts.size(), cudaMemcpyDeviceToHost));
+  int list_len = counts[HitableList::kMaxHitables];
+  CHECK(list_len >= 0 && list_len <= HitableList::kMaxHitables) << "HitableList overflow: " << list_len;
+  std::vector<int> offsets(HitableList::kMaxHitables, 0);
+  int total = 0;
+  for (int i = 0; i < list_len; i++) {
+    offsets[i] = total;
+    total += counts[i];
+  }
+  std::vector<FlatRec> flat((size_t)std::max(total, 1));
+  if (total > 0) {
+    FlatRec *d_flat = nullptr;
+    RTAPI_CUDA(cudaMalloc(&d_flat, sizeof(FlatRec) * total));
+    RTAPI_CUDA(cudaMemcpy(d_offsets, offsets.data(), sizeof(int) * offsets.size(), cudaMemcpyHostToDevice));
+    FlattenEmit<<<HitableList::kMaxHitables / 128, 128>>>(d_world, d_offsets, d_flat);
+    RTAPI_CUDA(cudaMemcpy(flat.data(), d_flat, sizeof(FlatRec) * total, cudaMemcpyDeviceToHost));
+    RTAPI_CUDA(cudaFree(d_flat));
+  }
+  RTAPI_CUDA(cudaFree(d_counts));
+  RTAPI_CUDA(cudaFree(d_offsets));
+
+  // materials deduplicated by object address, image textures by texture object
+  std::vector<rt_hitable> hitables;
+  std::vector<rt_material> materials;
+  std::vector<rt_mesh> meshes;
+  std::vector<rt_texture> textures;
+  std::vector<std::vector<uint8_t>> texels;
+  std::map<unsigned long long, int> material_ids, texture_ids;
+  for (int i = 0; i < total; i++) {
+    FlatRec &r = flat[i];
+    CHECK(r.m.type >= 0) << "hitable " << i << " has no (known) material";
+    auto it = material_ids.find(r.material_ptr);
+    if (it == material_ids.end()) {
+      rt_material m = r.m;
+      if (m.texture == -2) {
+        auto tt = texture_ids.find(r.tex_obj);
+        if (tt == texture_ids.end()) {
+          cudaResourceDesc res;
+          RTAPI_CUDA(cudaGetTextureObjectResourceDesc(&res, (cudaTextureObject_t)r.tex_obj));
+          CHECK(res.resType == cudaResourceTypePitch2D) << "ImageTexture must wrap a pitch2D resource (image_texture.cu:17-38)";
+          rt_texture t;
+          t.height = (int)res.res.pitch2D.height;
+          t.width = (int)res.res.pitch2D.width;
+          t.pitch_bytes = (int64_t)t.width * 4;
+          texels.emplace_back((size_t)t.pitch_bytes * t.height);
+          RTAPI_CUDA(cudaMemcpy2D(texels.back().data(), t.pitch_bytes, res.res.pitch2D.devPtr, res.res.pitch2D.pitchInBytes,
+                                  (size_t)t.width * 4, t.height, cudaMemcpyDeviceToHost));
+          t.h_rgba = nullptr;  // fixed up below (vector growth moves nothing, but keep it explicit)
+          tt = texture_ids.emplace(r.tex_obj, (int)textures.size()).first;
+          textures.push_back(t);
+        }
+        m.texture = tt->second;
+      }
+      it = material_ids.emplace(r.material_ptr, (int)materials.size()).first;
+      materials.push_back(m);
+    }
+    r.h.material = it->second;
+    if (r.h.type == RT_HIT_MESH) {
+      rt_mesh m;
+      m.h_faces = (const float *)r.faces_ptr;  // device memory: rt_scene_commit copies with cudaMemcpyDefault
+      m.n_faces = r.n_faces;
+      m.has_texcoord = r.has_uv;
+      r.h.mesh = (int)meshes.size();
+      meshes.push_back(m);
+    }
+    hitables.push_back(r.h);
+  }
+  for (size_t i = 0; i < textures.size(); i++) textures[i].h_rgba = texels[i].data();
+
+  rt_scene_desc d;
+  memset(&d, 0, sizeof(d));
+  d.hitables = hitables.data();
+  d.n_hitables = (int)hitables.size();
+  d.materials = materials.data();
+  d.n_materials = (int)materials.size();
+  d.meshes = meshes.data();
+  d.n_meshes = (int)meshes.size();
+  d.textures = textures.data();
+  d.n_textures = (int)textures.size();
+  rt_build_stats bs;
+  RTAPI_RT(rt_scene_commit(ctx, &d, &bs));
+
+  // the Camera record the callback placement-new'ed on the device
+  alignas(Camera) unsigned char raw[sizeof(Camera)];
+  RTAPI_CUDA(cudaMemcpy(raw, d_camera, sizeof(Camera), cudaMemcpyDeviceToHost));
+  const Camera &c = *reinterpret_cast<const Camera *>(raw);
+  rt_camera rc;
+  memset(&rc, 0, sizeof(rc));
+  auto put = [](float *dst, glm::vec3 v) { dst[0] = v.x, dst[1] = v.y, dst[2] = v.z; };
+  put(rc.position, c.position());
+  put(rc.lower_left_corner, c.lower_left_corner());
+  put(rc.horizontal, c.horizontal());
+  put(rc.vertical, c.vertical());
+  put(rc.u, c.u());
+  put(rc.v, c.v());
+  put(rc.w, c.w());
+  rc.is_defocus = c.is_defocus_camera() ? 1 : 0;
+  rc.lens_radius = c.lens_radius();
+  RTAPI_RT(rt_camera_set(ctx, &rc));
+  return bs;
+}
+
+void WriteStats(const Options &o, int rank, int world_size, const rt_build_stats &bs, const rt_render_stats &rs,
+                int local_spp, double total_ms) {
+  if (o.stats.empty()) return;
+  std::string path = o.stats;
+  if (world_size > 1) path += "." + std::to_string(rank);
+  std::ofstream f(path);
+  double samples = (double)o.height * o.width * local_spp;
+  f << "{\"rank\": " << rank << ", \"world_size\": " << world_size << ", \"height\": " << o.height
+    << ", \"width\": " << o.width << ", \"spp\": " << o.spp << ", \"local_spp\": " << local_spp
+    << ", \"max_depth\": " << o.max_depth << ", \"render_ms\": " << rs.render_ms << ", \"total_ms\": " << total_ms
+    << ", \"msamples_per_s\": " << (rs.render_ms > 0 ? samples / rs.render_ms / 1e3 : 0.0) << ", \"rays\": " << rs.rays
+    << ", \"rays_ref_equiv\": " << rs.rays_ref_equiv << ", \"build_ms\": " << bs.build_ms << ", \"prims\": " << bs.n_prims
+    << ", \"nodes\": " << bs.n_nodes << "}\n";
+}
+
+// NCCL rendezvous between the ranks of one box: rank 0 publishes the ncclUniqueId in /dev/shm.
+std::string RendezvousPath() {
+  const char *job = getenv("RT_JOB_ID");
+  if (!job || !*job) job = getenv("MASTER_PORT");
+  std::string key = job && *job ? std::string(job) : "ppid" + std::to_string((long)getppid());
+  return "/dev/shm/rtcore_nccl_" + key;
+}
+
+void BindNccl(rt_ctx *ctx, int rank, int world_size) {
+  char id[128];
+  std::string path = RendezvousPath();
+  if (rank == 0) {
+    RTAPI_RT(rt_nccl_unique_id(id));
+    std::string tmp = path + ".tmp";
+    {
+      std::ofstream f(tmp, std::ios::binary);
+      f.write(id, sizeof(id));
+    }
+    CHECK(rename(tmp.c_str(), path.c_str()) == 0) << "cannot publish " << path;
+  } else {
+    bool ok = false;
+    for (int tries = 0; tries < 6000 && !ok; tries++) {
+      std::ifstream f(path, std::ios::binary);
+      if (f.good() && f.read(id, sizeof(id)) && f.gcount() == (std::streamsize)sizeof(id)) ok = true;
+      else std::this_thread::sleep_for(std::chrono::milliseconds(10));
+    }
+    CHECK(ok) << "rank " << rank << ": no ncclUniqueId at " << path << " after 60 s";
+  }
+  RTAPI_RT(rt_nccl_init(ctx, id, world_size, rank));
+  if (rank == 0) unlink(path.c_str());  // every rank has joined once ncclCommInitRank returns
+}
+
+// The part of Main / DistributedMain after init_world: flatten, build, render, (reduce), resolve, write.
+void RenderWorld(curandState **d_states, Camera **d_camera, HitableList **d_world, glm::vec3 **d_image,
+                 nvstd::function<void(HitableList *, Camera *)> init_world, int height, int width, int spp,
+                 uint64_t curand_seed, bool distributed) {
+  auto t_start = std::chrono::steady_clock::now();
+  Options o = ReadOptions(height, width, spp);
+  int rank = 0, world_size = 1;
+  if (distributed) {
+    MPI_Comm_size(MPI_COMM_WORLD, &world_size);
+    MPI_Comm_rank(MPI_COMM_WORLD, &rank);
+  }
+  int device = 0;
+  RTAPI_CUDA(cudaGetDevice(&device));
+  const size_t n = (size_t)o.height * o.width;
+
+  // utils.cu:139-146 / :194-202: the caller's four device pointers, states seeded before init_world runs
+  RTAPI_CUDA(cudaMalloc(d_states, sizeof(curandState) * n));
+  RTAPI_CUDA(cudaMalloc(d_image, sizeof(glm::vec3) * n));
+  RTAPI_CUDA(cudaMalloc(d_world, sizeof(HitableList)));
+  RTAPI_CUDA(cudaMalloc(d_camera, sizeof(Camera)));
+  LOG(INFO) << "cuda memory allocated";
+  CudaRandomInit<<<(unsigned)((n + 63) / 64), 64>>>(curand_seed, *d_states, (int)n);
+  LOG(INFO) << "cuda random initialized";
+  init_world(*d_world, *d_camera);
+  RTAPI_CUDA(cudaDeviceSynchronize());
+  RTAPI_CUDA(cudaGetLastError());
+  LOG(INFO) << "world initialized";
+
+  rt_ctx *ctx = nullptr;
+  RTAPI_RT(rt_ctx_create(device, &ctx));
+  rt_build_stats bs = CommitWorld(ctx, *d_world, *d_camera);
+  LOG(INFO) << "scene committed: " << bs.n_prims << " primitives, " << bs.n_nodes << " BVH nodes, build " << bs.build_ms
+            << "ms";
+
+  int spp_begin = 0;
+  int local_spp = rt_get_workload(rank, world_size, o.spp, &spp_begin);
+  if (distributed) LOG(INFO) << "[" << rank << " / " << world_size << "] workload: " << local_spp;
+  if (world_size > 1) BindNccl(ctx, rank, world_size);
+
+  rt_render_params p;
+  p.height = o.height;
+  p.width = o.width;
+  p.spp_begin = spp_begin;
+  p.spp_count = local_spp;
+  p.max_depth = o.max_depth;
+  p.flags = RT_RENDER_CLEAR;
+  p.seed = o.seed;
+  rt_render_stats rs;
+  float *accum = reinterpret_cast<float *>(*d_image);
+  RTAPI_RT(rt_render(ctx, &p, accum, &rs, nullptr));
+  if (distributed)
+    LOG(INFO) << "[" << rank << " / " << world_size << "] Ray tracing finished in " << rs.render_ms << "ms.";
+  else
+    LOG(INFO) << "Ray tracing finished in " << rs.render_ms << "ms.";
+
+  // utils.cu:124 (MPI_Reduce of host copies) -> one ncclReduce of the device buffer
+  if (world_size > 1) RTAPI_RT(rt_reduce(ctx, nullptr, accum, (int64_t)n * 3, 0, nullptr));
+  if (rank == 0) {
+    // ray_tracing.cu:78-83 / utils.cu:126-129 on the device, then WriteImage's *255 truncation
+    uint8_t *d_rgb8 = nullptr;
+    RTAPI_CUDA(cudaMalloc(&d_rgb8, n * 3));
+    RTAPI_RT(rt_resolve(ctx, accum, o.height, o.width, std::max(o.spp, 1), distributed ? nullptr : accum, d_rgb8, nullptr));
+    std::vector<uint8_t> rgb8(n * 3);
+    RTAPI_CUDA(cudaMemcpy(rgb8.data(), d_rgb8, n * 3, cudaMemcpyDeviceToHost));
+    RTAPI_CUDA(cudaFree(d_rgb8));
+    LOG(INFO) << "Writing image to \"" << o.out << "\"";
+    bool ppm = o.out.size() > 4 && o.out.compare(o.out.size() - 4, 4, ".ppm") == 0;
+    RTAPI_RT(ppm ? rt_write_ppm(o.out.c_str(), o.width, o.height, rgb8.data())
+                 : rt_write_jpeg(o.out.c_str(), o.width, o.height, rgb8.data(), 100));
+  }
+  RTAPI_CUDA(cudaDeviceSynchronize());
+  double total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
+  WriteStats(o, rank, world_size, bs, rs, local_spp, total_ms);
+  if (world_size > 1) rt_nccl_destroy(ctx);
+  RTAPI_RT(rt_ctx_destroy(ctx));
+}
+
+}  // namespace
+
+// utils.cu:115-130: SUM of the ranks' images at rank 0, then /spp, clamp, sqrt.  Host-vector form kept for API
+// compatibility (the drivers above reduce on the device instead); only the single-rank case is supported here.
+__host__ void GatherImageData(int height, int width, const std::vector<glm::vec3> &send_buf, int spp,
+                              std::vector<glm::vec3> *out_image) {
+  int world_size = 1;
+  MPI_Comm_size(MPI_COMM_WORLD, &world_size);
+  CHECK(world_size == 1) << "GatherImageData on host vectors is single-rank; DistributedMain reduces on the device";
+  out_image->resize((size_t)height * width);
+  for (size_t i = 0; i < out_image->size(); i++) {
+    glm::vec3 c = send_buf[i] / float(spp);
+    c = glm::clamp(c, 0.f, 1.f);
+    (*out_image)[i] = glm::sqrt(c);
+  }
+}
+
+__host__ void Main(curandState **d_states, Camera **d_camera, HitableList **d_world, glm::vec3 **d_image,
+                   nvstd::function<void(HitableList *world, Camera *camera)> init_world, int height, int width,
+                   int spp) {
+  RenderWorld(d_states, d_camera, d_world, d_image, init_world, height, width, spp, 1024 /* utils.cu:146 */, false);
+}
+
+__host__ void DistributedMain(curandState **d_states, Camera **d_camera, HitableList **d_world, glm::vec3 **d_image,
+                              nvstd::function<void(HitableList *world, Camera *camera)> init_world, int height,
+                              int width, int spp) {
+  RenderWorld(d_states, d_camera, d_world, d_image, init_world, height, width, spp, 10086 /* utils.cu:202 */, true);
+}

@@ -1,0 +1,3 @@
+// Forwarding header for ray-tracing-cuda/textures/image_texture.cuh (see rt_scene_api.cuh).
+#pragma once
+#include "../rt_scene_api.cuh"
