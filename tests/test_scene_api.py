@@ -1,0 +1,116 @@
+"""The reference's own scenes/*.cu, compiled UNCHANGED against ray-tracing-cuda_b200/scene_api (binaries built
+here by `make -C ray-tracing-cuda_b200/scene_api`, they travel to the GPU box), run end to end:
+InitWorld on the device -> flatten -> rt_scene_commit -> rt_render -> resolve -> image file, and are compared
+with the same scene described through the Python bindings (bit-exact where the geometry is bit-reproducible)."""
+import importlib
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+API = os.path.join(ROOT, "ray-tracing-cuda_b200", "scene_api")
+BUILD = os.path.join(API, "build")
+SCENES = ["spheres", "cornell_box", "bunny", "birthday"]
+
+
+def _have_reference():
+    return os.path.exists("/root/reference/scenes/spheres.cu")
+
+
+@pytest.mark.skipif(not _have_reference(), reason="reference sources are only mounted in the authoring container")
+def test_reference_scenes_compile_unchanged():
+    """Acceptance test of the drop-in boundary: the four scene files build byte-for-byte unchanged."""
+    subprocess.run(["make", "-s", "-j4", "-C", API], check=True)
+    for s in SCENES:
+        assert os.path.exists(os.path.join(BUILD, s)), s
+    # nothing of the reference is compiled into them except scenes/<name>.cu itself
+    out = subprocess.run(["make", "-n", "-B", "-C", API], capture_output=True, text=True).stdout
+    assert "/root/reference/ray-tracing-cuda" not in out
+
+
+def test_rtrun_launcher_sets_ranks(tmp_path):
+    rtrun = os.path.join(BUILD, "rtrun")
+    if not os.path.exists(rtrun):
+        subprocess.run(["make", "-s", "-C", API, "build/rtrun"], check=True)
+    out = subprocess.run([rtrun, "-n", "3", "sh", "-c", "echo $RT_RANK/$RT_WORLD_SIZE/$RT_JOB_ID"], capture_output=True,
+                         text=True, check=True).stdout.split()
+    assert sorted(x.split("/")[0] for x in out) == ["0", "1", "2"]
+    assert {x.split("/")[1] for x in out} == {"3"} and len({x.split("/")[2] for x in out}) == 1
+    assert subprocess.run([rtrun, "-n", "2", "sh", "-c", "exit $RT_RANK"]).returncode == 1
+
+
+def _read_ppm(path):
+    with open(path, "rb") as f:
+        assert f.readline().strip() == b"P6"
+        w, h = map(int, f.readline().split())
+        assert f.readline().strip() == b"255"
+        return np.frombuffer(f.read(), np.uint8).reshape(h, w, 3)
+
+
+def _run_scene(name, tmp_path, H, W, spp, ranks=1):
+    rt = importlib.import_module("ray-tracing-cuda_b200")
+    res = tmp_path / "resources"
+    if not res.exists():
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import make_resources
+        make_resources.main(str(res), n_faces=9000, tex_hw=(64, 128))
+    out, stats = tmp_path / f"{name}.ppm", tmp_path / f"{name}.json"
+    env = dict(os.environ, RT_HEIGHT=str(H), RT_WIDTH=str(W), RT_SPP=str(spp), RT_OUT=str(out), RT_STATS=str(stats),
+               RT_SEED="5", RT_LOG="0")
+    cmd = [os.path.join(BUILD, name)]
+    if ranks > 1:
+        cmd = [os.path.join(BUILD, "rtrun"), "-n", str(ranks)] + cmd
+    p = subprocess.run(cmd, cwd=tmp_path, env=env, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-2000:]
+    st = json.load(open(str(stats) + (".0" if ranks > 1 else "")))
+    return rt, _read_ppm(out), st
+
+
+def _python_render(rt, scene, cam, H, W, spp):
+    ctx = rt.Context(0)
+    ctx.commit(scene)
+    ctx.set_camera(rt.core.camera_look_at(cam))
+    acc, rgb, st = ctx.render_host(H, W, spp, seed=5, want_rgb=True)
+    ctx.close()
+    return (rgb * np.float32(255)).astype(np.uint8), st
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", SCENES)
+def test_scene_binary_matches_python_api(name, tmp_path):
+    if not os.path.exists(os.path.join(BUILD, name)):
+        pytest.skip("scene binaries not built (needs the reference's scenes/*.cu at build time)")
+    H, W, spp = 90, 160, 8
+    rt, img, st = _run_scene(name, tmp_path, H, W, spp)
+    assert img.shape == (H, W, 3) and st["height"] == H and st["spp"] == spp and st["rays"] > H * W * spp
+    sc = rt.scenes
+    if name == "spheres":
+        # layout drawn from states[0] inside the user kernel; argument evaluation order is the compiler's
+        cands = [sc.spheres(10086, o)[:2] for o in ("ltr", "rtl")]
+    elif name == "cornell_box":
+        cands = [sc.cornell_box()]
+    elif name == "bunny":
+        cands = [sc.bunny(sc.bunny_mesh(9000))]
+    else:
+        from PIL import Image
+        tex = np.asarray(Image.open(tmp_path / "resources" / "earthmap.jpg").convert("RGBA"))
+        cands = [sc.birthday(tex)]
+    best = None
+    for scene, cam in cands:
+        want, pst = _python_render(rt, scene, cam, H, W, spp)
+        diff = np.abs(want.astype(int) - img.astype(int))
+        frac = float((diff.max(axis=2) > 0).mean())
+        if best is None or frac < best[0]:
+            best = (frac, float(diff.mean()), pst)
+    frac, mean_diff, pst = best
+    if name in ("spheres", "bunny"):
+        # geometry is bit-reproducible (float adds of curand draws / raw OBJ floats): identical images
+        assert frac == 0.0, (frac, mean_diff)
+        assert st["rays"] == pst.rays
+    else:
+        # rotateY goes through device cosf/sinf (cornell) and the JPEG decoder differs (birthday): statistical
+        assert mean_diff < 1.5 and frac < 0.6, (frac, mean_diff)
