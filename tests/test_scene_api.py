@@ -114,3 +114,20 @@ def test_scene_binary_matches_python_api(name, tmp_path):
     else:
         # rotateY goes through device cosf/sinf (cornell) and the JPEG decoder differs (birthday): statistical
         assert mean_diff < 1.5 and frac < 0.6, (frac, mean_diff)
+
+
+@pytest.mark.gpu
+def test_distributed_main_two_ranks_matches_one(tmp_path):
+    """DistributedMain under `rtrun -n 2` (sample partition + one ncclReduce) gives the 1-rank image: the Philox key
+    is (pixel, GLOBAL sample, bounce), so only the float summation order differs (<= 1 LSB of the 8-bit output)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    if not os.path.exists(os.path.join(BUILD, "spheres")):
+        pytest.skip("scene binaries not built")
+    H, W, spp = 90, 160, 9  # odd: ranks get 5 and 4 samples (GetWorkload, utils.cu:111-113)
+    _, one, st1 = _run_scene("spheres", tmp_path, H, W, spp, ranks=1)
+    _, two, st2 = _run_scene("spheres", tmp_path, H, W, spp, ranks=2)
+    assert st2["world_size"] == 2 and st2["local_spp"] == 5
+    d = np.abs(one.astype(int) - two.astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 0.05, (d.max(), (d > 0).mean())
