@@ -173,6 +173,33 @@ def cpu_baseline(name, H, W, spp, budget_s=12.0):
             "sample": f"full {W}x{H} frame at {spp_s} spp (of {spp}), {t:.1f} s"}
 
 
+def ref_cuda_baseline(name, H, W, scene, spp=16):
+    """The reference's own CUDA build on this GPU (baseline/_ref/ref_cuda, built from /root/reference by
+    baseline/Makefile): its PathTracing kernel timed its own way at `spp` samples (the kernel is linear in spp)."""
+    import tempfile
+    exe = os.path.join(ROOT, "baseline", "_ref", "ref_cuda")
+    if not os.path.exists(exe):
+        return {"unavailable": "baseline/_ref/ref_cuda not built"}
+    extra = []
+    tmp = tempfile.mkdtemp()
+    if name == "bunny":
+        fp = os.path.join(tmp, "faces.bin")
+        scene.meshes[0].astype(np.float32).tofile(fp)
+        extra = ["--faces", fp]
+        spp = 2
+    if name == "birthday":
+        fp = os.path.join(tmp, "tex.bin")
+        np.ascontiguousarray(scene.textures[0]).tofile(fp)
+        extra = ["--tex", fp, str(scene.textures[0].shape[0]), str(scene.textures[0].shape[1])]
+    try:
+        p = subprocess.run([exe, name, str(H), str(W), str(spp), "3"] + extra, capture_output=True, text=True, timeout=240)
+        r = json.loads(p.stdout.strip().splitlines()[-1])
+        return {"value": r["msamples_per_s"], "unit": "Msamples/s", "kind": "reference CUDA build, sm_100a, --fmad default",
+                "sample": f"full {W}x{H} frame at {spp} spp, best of 3, kernel-only (cudaEvents) as utils.cu:155-170", "ms": r["ms_best"]}
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": repr(e)[:200]}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -269,6 +296,10 @@ def main():
     # one more step with stats for ray counts and the kernel-only time
     st = ctx.render_device(accum.data_ptr(), H, W, count, begin, MAX_DEPTH, seed=1, flags=flags | rt.abi.RT_RENDER_CLEAR,
                            stream=sp)
+    # stats launch (counters of the same frame at reduced spp: per-ray figures are spp independent)
+    prof_spp = max(1, min(count, 4))
+    st_prof = ctx.render_device(accum.data_ptr(), H, W, prof_spp, begin, MAX_DEPTH, seed=1,
+                                flags=flags | rt.abi.RT_RENDER_CLEAR | rt.abi.RT_RENDER_PROFILE, stream=sp)
     ms_e2e = timed(step_e2e, max(1, min(args.steps, 3)), 1)
 
     rays = torch.tensor([float(st.rays), float(st.rays_ref_equiv)], device=dev, dtype=torch.float64)
@@ -284,22 +315,33 @@ def main():
     value = samples / ms / 1e3
     h2d = int(scene.hitables.nbytes + scene.materials.nbytes + sum(m.nbytes for m in scene.meshes) +
               sum(t.nbytes for t in scene.textures) + 96)
-    # roofline of the dominant kernel (the render kernel): algorithmic HBM bytes per launch =
-    # accumulation buffer read + write (24 B/pixel) + scene records + nodes read once
-    alg_bytes = H * W * 24 + build.n_prims * 48 + build.n_nodes * 32
     kern_ms = st.render_ms
-    achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": achieved / peaks["hbm_gbs"], "traffic": consts.get("dram_bytes_per_launch"),
-                "peak_source": f"{peak_kind} MEASURED_PEAKS.json hbm_gbs", "kernel": "k_render_fused" if st.kernel_launches == 1 else "k_wf_extend",
-                "kernel_ms": kern_ms,
-                "note": "scene is cache resident: the binding roofline is SM instruction issue, reported in `issue`"}
+    kernel = "k_render_fused" if st.kernel_launches == 1 else "k_wf_extend"
     sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
     props = torch.cuda.get_device_properties(local)
-    issue_peak = props.multi_processor_count * 4 * sm_mhz * 1e6  # warp instructions / s
-    wi = consts.get("warp_inst_per_sample", {}).get(args.workload)
-    issue = {"peak_warp_inst_per_s": issue_peak, "sm_mhz": sm_mhz,
-             "warp_inst_per_sample": wi, "frac": (samples / (kern_ms * 1e-3) / world * wi / issue_peak) if wi else None}
+    # Roofline of the dominant kernel.  The scene (nodes + records) is L1/L2 resident, so the bound is SM
+    # instruction issue: peak = SMs x 4 schedulers x f_clk warp-instructions/s at the
+    # clock sampled DURING the run.  Algorithmic work per launch (SURVEY §8d figures x the counters of a stats
+    # launch of the same frame): 23 flops per box test, 52 per ray-triangle record test, 23 per accepted hit,
+    # /1.3 (FMA-fused instruction count) + 12 control instructions per box test; one warp instruction = 32 lanes.
+    boxes, recs_tested = float(st_prof.node_visits), float(st_prof.prim_tests)
+    scale = float(count) / max(prof_spp, 1)  # the stats launch renders prof_spp samples per pixel
+    thread_inst = ((23.0 * boxes + 52.0 * recs_tested + 23.0 * float(st_prof.rays)) / 1.3 + 12.0 * boxes) * scale
+    issue_peak = props.multi_processor_count * 4 * sm_mhz * 1e6
+    achieved = thread_inst / 32.0 / (kern_ms * 1e-3)
+    alg_bytes = H * W * 24 + build.n_prims * 48 + build.n_nodes * 32  # accumulation r+w, scene read once
+    hbm_achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
+    roofline = {"bound": "issue", "achieved": achieved / 1e9, "peak": issue_peak / 1e9, "unit": "Gwarp-inst/s",
+                "frac": achieved / issue_peak, "traffic": consts.get("dram_bytes_per_launch", {}).get(args.workload),
+                "kernel": kernel, "kernel_ms": kern_ms, "sm_mhz": sm_mhz,
+                "peak_source": "148 SMs x 4 issue slots x sampled SM clock (B200_PROFILING.md / SURVEY 8d); not a tensor or HBM bound",
+                "algorithmic": {"box_tests_per_ray": boxes / max(float(st_prof.rays), 1.0),
+                                "record_tests_per_ray": recs_tested / max(float(st_prof.rays), 1.0),
+                                "thread_inst_per_ray": thread_inst / max(float(st.rays), 1.0)},
+                "hbm": {"bound": "hbm", "achieved": hbm_achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                        "frac": hbm_achieved / peaks["hbm_gbs"], "peak_source": f"{peak_kind} MEASURED_PEAKS.json hbm_gbs",
+                        "note": "scene is cache resident: HBM is not the binding resource"},
+                "measured_ncu": consts.get("ncu", {}).get(args.workload)}
     out = {"metric": "path Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
            "dtype": "f32", "data": "synthetic",
@@ -311,10 +353,11 @@ def main():
            "e2e": {"value": samples / ms_e2e / 1e3, "unit": "Msamples/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
                    "d2h_bytes_per_step": H * W * 12},
            "gpu_launches": int((st.kernel_launches + (1 if world > 1 else 0)) * args.steps),
-           "roofline": roofline, "issue": issue, "clocks": clocks,
+           "roofline": roofline, "clocks": clocks,
            "build": {"ms": build.build_ms, "max_depth": build.max_depth, "sah": build.sah_cost}}
     if not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(name, H, W, spp)
+        out["ref_cuda_baseline"] = ref_cuda_baseline(name, H, W, scene)
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

@@ -402,8 +402,9 @@ __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r
       if (cb & LEAF_FLAG) {
         int k = (int)ca, end = (int)(ca + (cb & ~LEAF_FLAG));
         while (k < end) {
-          if (STATS) st->prims++;
-          k += rec_test(s.recs, k, r, rg, b, ambiguous);
+          int used = rec_test(s.recs, k, r, rg, b, ambiguous);
+          if (STATS) st->prims += used;  // records tested (a parallelogram = 2 triangle records)
+          k += used;
         }
       } else {
         if (STATS) st->nodes += 2;
@@ -570,8 +571,9 @@ __device__ __forceinline__ Hit world_hit_bvh_ww(const DScene &s, const RayQ &r, 
       if (leaf_b) {
         int k = (int)leaf_a, end = (int)(leaf_a + (leaf_b & ~LEAF_FLAG));
         while (k < end) {
-          if (STATS) st->prims++;
-          k += rec_test(s.recs, k, r, rg, b, ambiguous);
+          int used = rec_test(s.recs, k, r, rg, b, ambiguous);
+          if (STATS) st->prims += used;  // records tested (a parallelogram = 2 triangle records)
+          k += used;
         }
       }
     }
@@ -703,7 +705,12 @@ __device__ __forceinline__ Hit world_hit_bvh_steps(const DScene &s, const RayQ &
       if (STATS) st->nodes += 2;
       state = trav_node_step(s, tv, stack);
     } else {
-      if (STATS) st->prims++;
+      if (STATS) {
+        uint32_t before = tv.ca;
+        state = trav_leaf_step(s, tv, rg, stack);
+        st->prims += state == ST_LEAF ? tv.ca - before : 1;
+        continue;
+      }
       state = trav_leaf_step(s, tv, rg, stack);
     }
   }
