@@ -155,8 +155,8 @@ __device__ __forceinline__ void flush_counters(RenderCounters *ctr, unsigned lon
 // ---- fused kernel: one thread per pixel, paths regenerated in registers ---------------------------
 // Each lane runs its pixel's samples in increasing order and starts the next sample the moment the
 // current path ends, so a warp stays full until its pixels run out of samples.  No queue traffic.
-template <bool STATS, int TRAV>
-__global__ void __launch_bounds__(128) k_render_fused(DScene s, DCamera cam, RenderArgs a, float *__restrict__ accum,
+template <bool STATS, int TRAV, int MINB = 5>
+__global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera cam, RenderArgs a, float *__restrict__ accum,
                                                       RenderCounters *ctr) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
@@ -318,6 +318,137 @@ __global__ void __launch_bounds__(128) k_render_vote(DScene s, DCamera cam, Rend
         depth = 0;
         n_samples++;
         start_query();
+      }
+    }
+  }
+  flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims);
+  if (STATS && lane == 0) {
+    atomicAdd(&ctr->sched_iters, n_iters);
+    atomicAdd(&ctr->sched_lanes, n_lanes);
+  }
+}
+
+// ---- pool kernel: K path slots per lane, warp-scheduled ------------------------------------------------
+// The vote kernel loses because a lane whose only path waits for a minority step idles.  Here every lane owns K
+// pixels (K path slots, state in per-thread local memory = L1), and each iteration the warp executes the step
+// kind for which the MOST LANES have a ready slot; a lane runs it on its first slot in that state.  Waiting slots
+// cost storage, not issue slots: a lane idles only when none of its K slots wants the chosen step.  Samples of a
+// pixel still run in increasing order in one slot, so the image is bit-identical to the fused kernel's.
+struct PathSlot {
+  V3 T, color;
+  int32_t depth, k;
+};
+
+template <bool STATS, int K>
+__global__ void __launch_bounds__(128) k_render_pool(DScene s, DCamera cam, RenderArgs a, float *__restrict__ accum,
+                                                     RenderCounters *ctr) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j0 = blockIdx.x * (16 * K) + (warp & 1) * 8 + (lane & 7);
+  const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+  Range rg;
+  rg.t_from = 1e-3;
+  rg.t_to = (double)CUDART_INF_F;
+  rg.tf_f = float_ge(1e-3);
+  Trav tv[K];
+  PathSlot ps[K];
+  uint2 stack[K][STACK_SIZE];
+  uint32_t mG = 0, mN = 0, mL = 0, mS = 0;  // bit q: slot q is in that state
+#pragma unroll
+  for (int q = 0; q < K; q++) {
+    ps[q].color = mk(0.f, 0.f, 0.f);
+    ps[q].T = mk(1.f, 1.f, 1.f);
+    ps[q].depth = 0;
+    ps[q].k = a.spp_begin;
+    tv[q].sp = 0;
+    if (i < a.height && j0 + 16 * q < a.width) mG |= 1u << q;
+  }
+  unsigned long long n_samples = 0, n_rays = 0, n_rays_ref = 0, n_nodes = 0, n_prims = 0, n_iters = 0, n_lanes = 0;
+  auto set_state = [&](int q, int state) {
+    const uint32_t bit = 1u << q;
+    mG &= ~bit, mN &= ~bit, mL &= ~bit, mS &= ~bit;
+    if (state == ST_GEN) mG |= bit;
+    else if (state == ST_NODE) mN |= bit;
+    else if (state == ST_LEAF) mL |= bit;
+    else if (state == ST_SHADE) mS |= bit;
+  };
+  auto start_query = [&](int q) {
+    n_rays_ref++;
+    if (ps[q].depth < a.max_depth) {
+      n_rays++;
+      set_state(q, trav_begin(s, tv[q], rg));
+    } else {
+      ps[q].k++;
+      set_state(q, ST_GEN);
+    }
+  };
+  for (;;) {
+    const unsigned bN = __ballot_sync(0xffffffffu, mN != 0), bL = __ballot_sync(0xffffffffu, mL != 0);
+    const unsigned bS = __ballot_sync(0xffffffffu, mS != 0), bG = __ballot_sync(0xffffffffu, mG != 0);
+    if ((bN | bL | bS | bG) == 0u) break;
+    int pick = ST_NODE, best = __popc(bN);
+    int c = __popc(bL);
+    if (c > best) pick = ST_LEAF, best = c;
+    c = __popc(bS);
+    if (c > best) pick = ST_SHADE, best = c;
+    c = __popc(bG);
+    if (c > best) pick = ST_GEN, best = c;
+    if (STATS && lane == 0) {
+      n_iters++;
+      n_lanes += best;
+    }
+    if (pick == ST_NODE) {
+      if (mN) {
+        const int q = __ffs(mN) - 1;
+        if (STATS) n_nodes += 2;
+        set_state(q, trav_node_step(s, tv[q], stack[q]));
+      }
+    } else if (pick == ST_LEAF) {
+      if (mL) {
+        const int q = __ffs(mL) - 1;
+        if (STATS) n_prims++;
+        set_state(q, trav_leaf_step(s, tv[q], rg, stack[q]));
+      }
+    } else if (pick == ST_SHADE) {
+      if (mS) {
+        const int q = __ffs(mS) - 1;
+        PathKey pk;
+        pk.pixel = (uint32_t)(i * a.width + j0 + 16 * q);
+        pk.sample = (uint32_t)ps[q].k;
+        pk.k0 = a.k0;
+        pk.k1 = a.k1;
+        Hit h = trav_finish(s, tv[q], rg);
+        V3 T = ps[q].T, color = ps[q].color;
+        bool alive = h.rec != REC_NONE && shade_hit(s, tv[q].r, h, pk, ps[q].depth, T, color);
+        ps[q].T = T;
+        ps[q].color = color;
+        if (alive) {
+          ps[q].depth++;
+          start_query(q);
+        } else {
+          ps[q].k++;
+          set_state(q, ST_GEN);
+        }
+      }
+    } else if (mG) {
+      const int q = __ffs(mG) - 1;
+      const int j = j0 + 16 * q;
+      const int idx = i * a.width + j;
+      if (ps[q].k >= a.spp_end) {
+        accum[3 * (size_t)idx + 0] += ps[q].color.x;
+        accum[3 * (size_t)idx + 1] += ps[q].color.y;
+        accum[3 * (size_t)idx + 2] += ps[q].color.z;
+        set_state(q, ST_DONE);
+      } else {
+        PathKey pk;
+        pk.pixel = (uint32_t)idx;
+        pk.sample = (uint32_t)ps[q].k;
+        pk.k0 = a.k0;
+        pk.k1 = a.k1;
+        tv[q].r = camera_sample(cam, i, j, a.height, a.width, pk);
+        ps[q].T = mk(1.f, 1.f, 1.f);
+        ps[q].depth = 0;
+        n_samples++;
+        start_query(q);
       }
     }
   }
@@ -508,7 +639,7 @@ int trav_variant(const rt_ctx *ctx) {
   const char *e = getenv("RT_TRAV");
   int dflt = ctx->scene.n_recs <= 4096 ? 1 : 0;
   int v = e ? atoi(e) : dflt;
-  return (v < 0 || v > 5) ? dflt : v;
+  return (v < 0 || v > 8) ? dflt : v;
 }
 
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
@@ -657,13 +788,35 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
   if (fused) {
     dim3 grid((p->width + 15) / 16, (p->height + 7) / 8);
     int trav = trav_variant(ctx);
+    // resident blocks per SM the kernel is compiled for (register budget): measured best per scene class
+    // (profiles/r01_d_occupancy_sweep.txt): 6 for small scenes, 8 for >= 500k records (latency bound), else 5
+    const char *mb = getenv("RT_MINB");
+    int minb = mb ? atoi(mb) : (ctx->scene.n_recs <= 4096 ? 6 : (ctx->scene.n_recs >= 500000 ? 8 : 5));
 #define RT_FUSED_CASE(T)                                                                               \
   case T:                                                                                              \
     if (stats_on)                                                                                      \
       k_render_fused<true, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);     \
+    else if (minb == 6 && T < 2)                                                                       \
+      k_render_fused<false, T < 2 ? T : 0, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr); \
+    else if (minb == 8 && T < 2)                                                                       \
+      k_render_fused<false, T < 2 ? T : 0, 8><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr); \
     else                                                                                               \
       k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);    \
     break;
+    if (trav >= 6) {  // pool kernel, K = trav - 4 slots per lane (6 -> 2, 7 -> 3, 8 -> 4)
+      const int K = trav - 4;
+      dim3 pgrid((p->width + 16 * K - 1) / (16 * K), (p->height + 7) / 8);
+      if (K == 2) {
+        if (stats_on) k_render_pool<true, 2><<<pgrid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+        else k_render_pool<false, 2><<<pgrid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+      } else if (K == 3) {
+        if (stats_on) k_render_pool<true, 3><<<pgrid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+        else k_render_pool<false, 3><<<pgrid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+      } else {
+        if (stats_on) k_render_pool<true, 4><<<pgrid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+        else k_render_pool<false, 4><<<pgrid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+      }
+    } else
     switch (trav) {
       case 5:
         if (stats_on)
