@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+#define RT_ABI_VERSION 2
 
 enum {
   RT_OK = 0,
@@ -135,6 +135,8 @@ typedef struct rt_build_stats {
   float build_ms;       /* device time of the BVH build (CUDA events) */
   float upload_ms;
   float sah_cost;
+  int32_t n_wide_nodes; /* 256-byte 8-wide nodes collapsed from the binary tree (the render kernels' tree) */
+  int32_t wide_depth;   /* levels of the wide tree */
 } rt_build_stats;
 
 typedef struct rt_render_stats {

@@ -82,6 +82,8 @@ class RtBuildStats(C.Structure):
         ("build_ms", C.c_float),
         ("upload_ms", C.c_float),
         ("sah_cost", C.c_float),
+        ("n_wide_nodes", C.c_int32),
+        ("wide_depth", C.c_int32),
     ]
 
 

@@ -53,7 +53,7 @@ def lib():
     L.rt_write_jpeg.argtypes = [C.c_char_p, C.c_int, C.c_int, vp, C.c_int]
     L.rt_write_ppm.argtypes = [C.c_char_p, C.c_int, C.c_int, vp]
     L.rt_write_pfm.argtypes = [C.c_char_p, C.c_int, C.c_int, vp]
-    if L.rt_abi_version() != 1:
+    if L.rt_abi_version() != 2:
         raise RtError("librtcore.so ABI version mismatch")
     _lib = L
     return L

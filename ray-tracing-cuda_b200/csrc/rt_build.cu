@@ -255,6 +255,84 @@ __global__ void k_refit(const uint32_t *left, const uint32_t *right, const uint3
   }
 }
 
+// ---- wide collapse: binary tree -> 8 children per node ---------------------------------------------
+// One thread per wide node of the current level.  Starting from the two children of its binary
+// node it keeps opening the inner child with the largest surface area until 8 slots are used or
+// only leaves are left (the greedy collapse of Wald et al. 2008 / Ylitie et al. 2017).  Inner
+// children get a wide-node index (atomic counter) and go to the next level's queue.  WRITE = false
+// only counts (sizes the node buffer).
+template <bool WRITE>
+__global__ void k_wide_expand(const float4 *__restrict__ nodes, const uint2 *__restrict__ in_q, int n_in, uint2 *out_q,
+                              uint32_t *counters /* [0] next-level queue length, [1] wide nodes allocated */,
+                              float4 *wnodes) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_in) return;
+  const uint32_t bn = in_q[t].x, wn = in_q[t].y;
+  uint32_t slot[WIDE];
+  int n;
+  {
+    uint32_t a = __float_as_uint(nodes[2 * (size_t)bn].w), b = __float_as_uint(nodes[2 * (size_t)bn + 1].w);
+    if (b & LEAF_FLAG) {  // the whole scene is one leaf
+      slot[0] = bn;
+      n = 1;
+    } else {
+      slot[0] = a;
+      slot[1] = b;
+      n = 2;
+    }
+  }
+  while (n < WIDE) {
+    int best = -1;
+    float best_area = -1.f;
+    for (int i = 0; i < n; i++) {
+      float4 lo = nodes[2 * (size_t)slot[i]], hi = nodes[2 * (size_t)slot[i] + 1];
+      if (__float_as_uint(hi.w) & LEAF_FLAG) continue;
+      float ar = half_area(lo, hi);
+      if (ar > best_area) {
+        best_area = ar;
+        best = i;
+      }
+    }
+    if (best < 0) break;
+    uint32_t a = __float_as_uint(nodes[2 * (size_t)slot[best]].w), b = __float_as_uint(nodes[2 * (size_t)slot[best] + 1].w);
+    slot[best] = a;
+    slot[n++] = b;
+  }
+  float *f = WRITE ? reinterpret_cast<float *>(wnodes + (size_t)WNODE_F4 * wn) : nullptr;
+  uint32_t *u = reinterpret_cast<uint32_t *>(f);
+  for (int i = 0; i < WIDE; i++) {
+    if (i >= n) {
+      if (WRITE) {
+        f[i] = f[8 + i] = f[16 + i] = CUDART_INF_F;
+        f[24 + i] = f[32 + i] = f[40 + i] = -CUDART_INF_F;
+        u[48 + i] = WREF_EMPTY;
+      }
+      continue;
+    }
+    float4 lo = nodes[2 * (size_t)slot[i]], hi = nodes[2 * (size_t)slot[i] + 1];
+    uint32_t a = __float_as_uint(lo.w), b = __float_as_uint(hi.w);
+    uint32_t ref;
+    if (b & LEAF_FLAG) {
+      ref = WLEAF | ((b & ~LEAF_FLAG) << WLEAF_COUNT_SHIFT) | a;
+    } else {
+      ref = atomicAdd(counters + 1, 1u);
+      uint32_t q = atomicAdd(counters + 0, 1u);
+      if (out_q) out_q[q] = make_uint2(slot[i], ref);
+    }
+    if (WRITE) {
+      f[i] = lo.x, f[8 + i] = lo.y, f[16 + i] = lo.z;
+      f[24 + i] = hi.x, f[32 + i] = hi.y, f[40 + i] = hi.z;
+      u[48 + i] = ref;
+    }
+  }
+  if (WRITE) {
+    u[56] = (1u << n) - 1u;
+    u[57] = (uint32_t)n;
+    u[58] = u[59] = 0;
+    u[60] = u[61] = u[62] = u[63] = 0;
+  }
+}
+
 }  // namespace rtc
 
 // =================================================================================================
@@ -494,12 +572,12 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
     n_bp = (int)(last_flag + last_pos);
   }
   size_t n_recs = 0;
-  int n_nodes = 0, max_depth = 0;
+  int n_nodes = 0, max_depth = 0, n_wnodes = 0, wide_depth = 0;
   float sah = 0.f;
   uint32_t root_words[2] = {0, LEAF_FLAG};
   if (n_bp > 0) {
     const char *env = getenv("RT_MAX_LEAF");
-    int max_leaf = env ? std::max(1, atoi(env)) : 4;
+    int max_leaf = env ? std::min(std::max(1, atoi(env)), WLEAF_MAX_COUNT) : 4;
     env = getenv("RT_SAH_CT");
     float c_trav = env ? (float)atof(env) : 1.2f;
     // S[3] bp_first, S[6] bp_lo, S[7] bp_hi, S[8] scene bounds + keys, S[9] vals ...
@@ -567,6 +645,44 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
     RT_CUDA(cudaStreamSynchronize(st));
     memcpy(&root_words[0], &root[0].w, 4);
     memcpy(&root_words[1], &root[1].w, 4);
+
+    // ---- wide collapse, level by level (bp_lo / bp_hi are dead: their storage holds the two queues) ----
+    if (n_recs > (size_t)WLEAF_FIRST_MASK) {
+      set_error("rt_scene_commit: too many records for the wide-node leaf encoding");
+      return RT_ERR_LIMIT;
+    }
+    uint32_t *cnt = S[10].as<uint32_t>();
+    for (int pass = 0; pass < 2; pass++) {
+      uint2 *in = S[6].as<uint2>(), *out = S[7].as<uint2>();
+      uint2 seed = make_uint2(0u, 0u);
+      uint32_t c[2] = {0u, 1u};
+      RT_CUDA(cudaMemcpyAsync(in, &seed, sizeof(seed), cudaMemcpyHostToDevice, st));
+      RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
+      int n_in = 1, levels = 0;
+      while (n_in > 0) {
+        if (pass == 0)
+          k_wide_expand<false><<<nblk(n_in), 256, 0, st>>>(ctx->nodes.as<float4>(), in, n_in, out, cnt, nullptr);
+        else
+          k_wide_expand<true><<<nblk(n_in), 256, 0, st>>>(ctx->nodes.as<float4>(), in, n_in, out, cnt,
+                                                          ctx->wnodes.as<float4>());
+        RT_CUDA(cudaMemcpyAsync(c, cnt, sizeof(c), cudaMemcpyDeviceToHost, st));
+        RT_CUDA(cudaStreamSynchronize(st));
+        n_in = (int)c[0];
+        c[0] = 0;
+        RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
+        std::swap(in, out);
+        levels++;
+      }
+      if (pass == 0) {
+        n_wnodes = (int)c[1];
+        RT_CUDA(ctx->wnodes.reserve((size_t)n_wnodes * WNODE_F4 * 16));
+      } else if ((int)c[1] != n_wnodes) {
+        set_error("rt_scene_commit: wide collapse passes disagree");
+        return RT_ERR_CUDA;
+      }
+      wide_depth = levels;
+    }
+    RT_CUDA(cudaGetLastError());
   }
   RT_CUDA(cudaEventRecord(ctx->ev1, st));
   RT_CUDA(cudaEventSynchronize(ctx->ev1));
@@ -575,6 +691,8 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
 
   DScene &s = ctx->scene;
   s.nodes = ctx->nodes.as<float4>();
+  s.wnodes = n_wnodes > 0 ? ctx->wnodes.as<float4>() : nullptr;
+  s.n_wnodes = n_wnodes;
   s.recs = ctx->recs.as<float4>();
   s.recs_seq = recs_seq;
   s.face_uv = any_uv ? ctx->face_uv.as<float>() : nullptr;
@@ -601,6 +719,8 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   bs.build_ms = ms;
   bs.upload_ms = 0.f;
   bs.sah_cost = sah;
+  bs.n_wide_nodes = n_wnodes;
+  bs.wide_depth = wide_depth;
   if (stats) *stats = bs;
   return RT_OK;
 }

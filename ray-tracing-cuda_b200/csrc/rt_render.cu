@@ -10,6 +10,7 @@
 #include <string>
 
 #include "rt_internal.h"
+#include "rt_wide.cuh"
 
 #ifndef RT_DEFAULT_TRAV
 #define RT_DEFAULT_TRAV 0  // traversal loop of the parity hook and the wavefront extend kernel
@@ -24,25 +25,8 @@ struct RenderArgs {
   uint32_t k0, k1;
 };
 
-// ---- parity hook: HitableList::Hit on explicit rays ------------------------------------------------
-__global__ void __launch_bounds__(128) k_trace_closest(DScene s, const float *__restrict__ rays, int64_t n,
-                                                       double t_from, double t_to, int mode, rt_hit *out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  RayQ r;
-  r.o = mk(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]);
-  r.d = mk(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]);
-  Hit h;
-  switch (mode) {
-    case 1: h = world_hit_seq(s, r, t_from, t_to); break;
-    case 2: h = world_hit_bvh<false, 0>(s, r, t_from, t_to, nullptr); break;
-    case 3: h = world_hit_bvh<false, 1>(s, r, t_from, t_to, nullptr); break;
-    case 4: h = world_hit_bvh<false, 2>(s, r, t_from, t_to, nullptr); break;
-    case 5: h = world_hit_bvh<false, 3>(s, r, t_from, t_to, nullptr); break;
-    case 6: h = world_hit_bvh<false, 4>(s, r, t_from, t_to, nullptr); break;
-    case 7: h = world_hit_bvh<false, 5>(s, r, t_from, t_to, nullptr); break;
-    default: h = world_hit_bvh<false, RT_DEFAULT_TRAV>(s, r, t_from, t_to, nullptr); break;
-  }
+// rt_hit of a query result (what HitRecord carries, hitable.cuh:13-17)
+__device__ __forceinline__ rt_hit make_rt_hit(const DScene &s, const RayQ &r, const Hit &h) {
   rt_hit o;
   if (h.rec == REC_NONE) {
     o.t = 0;
@@ -63,7 +47,53 @@ __global__ void __launch_bounds__(128) k_trace_closest(DScene s, const float *__
     o.normal[2] = sf.normal.z;
     o.material = sf.material;
   }
-  out[i] = o;
+  return o;
+}
+
+// Parity hook of the warp-synchronous traversals (every lane of a warp enters the query):
+// mode 8 wide tree, per-lane record tests; 9 wide tree + cooperative record tests; 10 binary tree + cooperative.
+__global__ void __launch_bounds__(128) k_trace_closest_warp(DScene s, const float *__restrict__ rays, int64_t n,
+                                                            double t_from, double t_to, int mode, rt_hit *out) {
+  __shared__ CoopWarp sm_all[4];
+  CoopWarp &sm = sm_all[threadIdx.x >> 5];
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool active = i < n;
+  RayQ r;
+  r.o = r.d = mk(0.f, 0.f, 1.f);
+  if (active) {
+    r.o = mk(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]);
+    r.d = mk(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]);
+  }
+  Hit h;
+  if (mode == 8)
+    h = world_hit_wide<false, false>(s, r, active, t_from, t_to, &sm, nullptr);
+  else if (mode == 9)
+    h = world_hit_wide<false, true>(s, r, active, t_from, t_to, &sm, nullptr);
+  else
+    h = world_hit_coop<false>(s, r, active, t_from, t_to, sm, nullptr);
+  if (active) out[i] = make_rt_hit(s, r, h);
+}
+
+// ---- parity hook: HitableList::Hit on explicit rays ------------------------------------------------
+__global__ void __launch_bounds__(128) k_trace_closest(DScene s, const float *__restrict__ rays, int64_t n,
+                                                       double t_from, double t_to, int mode, rt_hit *out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  RayQ r;
+  r.o = mk(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]);
+  r.d = mk(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]);
+  Hit h;
+  switch (mode) {
+    case 1: h = world_hit_seq(s, r, t_from, t_to); break;
+    case 2: h = world_hit_bvh<false, 0>(s, r, t_from, t_to, nullptr); break;
+    case 3: h = world_hit_bvh<false, 1>(s, r, t_from, t_to, nullptr); break;
+    case 4: h = world_hit_bvh<false, 2>(s, r, t_from, t_to, nullptr); break;
+    case 5: h = world_hit_bvh<false, 3>(s, r, t_from, t_to, nullptr); break;
+    case 6: h = world_hit_bvh<false, 4>(s, r, t_from, t_to, nullptr); break;
+    case 7: h = world_hit_bvh<false, 5>(s, r, t_from, t_to, nullptr); break;
+    default: h = world_hit_bvh<false, RT_DEFAULT_TRAV>(s, r, t_from, t_to, nullptr); break;
+  }
+  out[i] = make_rt_hit(s, r, h);
 }
 
 // Pixel-centre primary rays: ray_tracing.cu:68-74 with both jitters = 0.5.
@@ -214,6 +244,87 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
   flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims);
 }
 
+
+// ---- warp-synchronous kernel: the fused kernel over the wide tree / with cooperative record tests ----
+// Same path bookkeeping as k_render_fused (one lane per pixel, samples in increasing order, a path is
+// regenerated in registers when the previous one ends), but every lane of the warp enters every
+// closest-hit query — lanes whose path is at the depth limit or whose pixel is finished pass
+// active = false — so the query can pool the warp's record tests (rt_coop.cuh).
+//   MODE 0: binary tree + cooperative record tests      (RT_TRAV=9)
+//   MODE 1: 8-wide tree, per-lane record tests          (RT_TRAV=10)
+//   MODE 2: 8-wide tree + cooperative record tests      (RT_TRAV=11)
+// Image and counters are bit-identical to k_render_fused.
+template <bool STATS, int MODE, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_render_warp(DScene s, DCamera cam, RenderArgs a,
+                                                           float *__restrict__ accum, RenderCounters *ctr) {
+  constexpr unsigned FULL = 0xffffffffu;
+  __shared__ CoopWarp sm_all[MODE == 1 ? 1 : 4];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  CoopWarp &sm = sm_all[MODE == 1 ? 0 : warp];
+  const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+  const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = i < a.height && j < a.width;
+  const int idx = i * a.width + j;
+  PathKey pk;
+  pk.pixel = (uint32_t)idx;
+  pk.k0 = a.k0;
+  pk.k1 = a.k1;
+  int k = a.spp_begin;
+  V3 color = mk(0.f, 0.f, 0.f), T = mk(1.f, 1.f, 1.f);
+  RayQ ray;
+  ray.o = mk(0.f, 0.f, 0.f);
+  ray.d = mk(0.f, 0.f, 1.f);
+  int depth = 0;
+  bool need_new = true, finished = !inside;
+  unsigned long long n_samples = 0, n_rays = 0, n_rays_ref = 0, n_nodes = 0, n_prims = 0;
+  TravStats ts;
+  ts.nodes = ts.prims = 0;
+  for (;;) {
+    if (need_new && !finished) {
+      if (k >= a.spp_end) {
+        finished = true;
+      } else {
+        pk.sample = (uint32_t)k;
+        ray = camera_sample(cam, i, j, a.height, a.width, pk);
+        T = mk(1.f, 1.f, 1.f);
+        depth = 0;
+        need_new = false;
+        n_samples++;
+      }
+    }
+    if (__all_sync(FULL, finished)) break;
+    const bool query = !finished && depth < a.max_depth;  // ray_tracing.cu:23: the query at depth == limit yields 0
+    if (!finished) n_rays_ref++;
+    Hit h;
+    if (MODE == 0)
+      h = world_hit_coop<STATS>(s, ray, query, 1e-3, (double)CUDART_INF_F, sm, &ts);
+    else
+      h = world_hit_wide<STATS, MODE == 2>(s, ray, query, 1e-3, (double)CUDART_INF_F, &sm, &ts);
+    bool alive = false;
+    if (query) {
+      n_rays++;
+      alive = h.rec != REC_NONE && shade_hit(s, ray, h, pk, depth, T, color);
+    }
+    if (!finished) {
+      if (alive) {
+        depth++;
+      } else {
+        k++;
+        need_new = true;
+      }
+    }
+  }
+  if (STATS) {
+    n_nodes = ts.nodes;
+    n_prims = ts.prims;
+  }
+  if (inside) {
+    accum[3 * (size_t)idx + 0] += color.x;
+    accum[3 * (size_t)idx + 1] += color.y;
+    accum[3 * (size_t)idx + 2] += color.z;
+  }
+  flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims);
+}
 
 // ---- vote kernel: the fused kernel as a warp-scheduled state machine ------------------------------
 // Same work as k_render_fused (one lane per pixel, samples in increasing order, paths regenerated in
@@ -639,7 +750,7 @@ int trav_variant(const rt_ctx *ctx) {
   const char *e = getenv("RT_TRAV");
   int dflt = ctx->scene.n_recs <= 4096 ? 1 : 0;
   int v = e ? atoi(e) : dflt;
-  return (v < 0 || v > 8) ? dflt : v;
+  return (v < 0 || v > 11) ? dflt : v;
 }
 
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
@@ -663,14 +774,18 @@ extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t
                                        rt_hit *d_hits, void *stream) {
   int rc = check_ready(ctx, false, "rt_trace_closest");
   if (rc) return rc;
-  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 7)) {
+  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 10)) {
     set_error("rt_trace_closest: bad argument");
     return RT_ERR_INVALID;
   }
   if (n == 0) return RT_OK;
   RT_CUDA(cudaSetDevice(ctx->device));
-  k_trace_closest<<<nblk((size_t)n, 128), 128, 0, (cudaStream_t)stream>>>(ctx->scene, d_rays, n, t_from, t_to, mode,
-                                                                          d_hits);
+  if (mode >= 8)
+    k_trace_closest_warp<<<nblk((size_t)n, 128), 128, 0, (cudaStream_t)stream>>>(ctx->scene, d_rays, n, t_from, t_to,
+                                                                                 mode, d_hits);
+  else
+    k_trace_closest<<<nblk((size_t)n, 128), 128, 0, (cudaStream_t)stream>>>(ctx->scene, d_rays, n, t_from, t_to, mode,
+                                                                            d_hits);
   RT_CUDA(cudaGetLastError());
   return RT_OK;
 }
@@ -803,7 +918,25 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     else                                                                                               \
       k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);    \
     break;
-    if (trav >= 6) {  // pool kernel, K = trav - 4 slots per lane (6 -> 2, 7 -> 3, 8 -> 4)
+    if (trav >= 9) {  // warp-synchronous kernel: 9 binary + coop, 10 wide, 11 wide + coop
+#define RT_WARP_CASE(M)                                                                                          \
+  if (stats_on)                                                                                                  \
+    k_render_warp<true, M, 5><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);               \
+  else if (minb == 6)                                                                                            \
+    k_render_warp<false, M, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);              \
+  else if (minb == 8)                                                                                            \
+    k_render_warp<false, M, 8><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);              \
+  else                                                                                                           \
+    k_render_warp<false, M, 5><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+      if (trav == 9) {
+        RT_WARP_CASE(0)
+      } else if (trav == 10) {
+        RT_WARP_CASE(1)
+      } else {
+        RT_WARP_CASE(2)
+      }
+#undef RT_WARP_CASE
+    } else if (trav >= 6) {  // pool kernel, K = trav - 4 slots per lane (6 -> 2, 7 -> 3, 8 -> 4)
       const int K = trav - 4;
       dim3 pgrid((p->width + 16 * K - 1) / (16 * K), (p->height + 7) / 8);
       if (K == 2) {
