@@ -382,6 +382,33 @@ static __device__ __noinline__ Hit world_hit_seq(const DScene &s, const RayQ &r,
 // far child's (a, b) words pushed on a short per-thread stack.  Boxes were padded at build time
 // and the cull bound is widened, so that culling never removes a record the scan would accept.
 // ------------------------------------------------------------------------------------------------
+// 1/d for the slab tests, clamped to +-1e18: with an infinite reciprocal (d = +-0) the FFMA form turns a
+// plane on the far side into inf - inf = NaN, and fmaxf(near, NaN) would return the NEAR plane as the exit.
+// A finite stand-in keeps every plane distance finite and ordered (|t| >= 1e18 * |plane - o|: still far
+// outside any scene unless the origin lies within rounding of the plane, where either answer is accepted
+// by the padded box).
+__device__ __forceinline__ float slab_rcp(float d) { return fmaxf(fminf(1.0f / d, 1e18f), -1e18f); }
+
+// Slab test of the two children of a binary node: entry / exit distances of the left (ln, lf) and right
+// (rn, rf) box, clamped to [t_lo, t_hi].  Culling only has to be conservative, so the plane distances are
+// one FFMA each, fma(plane, 1/d, -(o/d)): the rounding of that form is bounded by
+// 3e-8 * (t + |plane| / |d|), which the builder's relative box padding (2e-5 * |coordinate|, rt_build.cu
+// k_bp_bounds) and the relative guard bands on t (1e-5) cover.  1/d comes from slab_rcp (finite).
+__device__ __forceinline__ void slab2(const float4 &l0, const float4 &l1, const float4 &r0, const float4 &r1, float idx,
+                                      float idy, float idz, float nox, float noy, float noz, float t_lo, float t_hi,
+                                      float &ln, float &lf, float &rn, float &rf) {
+  float ax = __fmaf_rn(l0.x, idx, nox), bx = __fmaf_rn(l1.x, idx, nox);
+  float ay = __fmaf_rn(l0.y, idy, noy), by = __fmaf_rn(l1.y, idy, noy);
+  float az = __fmaf_rn(l0.z, idz, noz), bz = __fmaf_rn(l1.z, idz, noz);
+  ln = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_lo));
+  lf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
+  ax = __fmaf_rn(r0.x, idx, nox), bx = __fmaf_rn(r1.x, idx, nox);
+  ay = __fmaf_rn(r0.y, idy, noy), by = __fmaf_rn(r1.y, idy, noy);
+  az = __fmaf_rn(r0.z, idz, noz), bz = __fmaf_rn(r1.z, idz, noz);
+  rn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_lo));
+  rf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
+}
+
 struct TravStats {
   uint32_t nodes, prims;
 };
@@ -407,7 +434,8 @@ __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r
   }
   bool ambiguous = false, overflow = false;
   if (s.n_recs > 0) {
-    const float idx = 1.0f / r.d.x, idy = 1.0f / r.d.y, idz = 1.0f / r.d.z;
+    const float idx = slab_rcp(r.d.x), idy = slab_rcp(r.d.y), idz = slab_rcp(r.d.z);
+    const float nox = -(r.o.x * idx), noy = -(r.o.y * idy), noz = -(r.o.z * idz);
     const float t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
     uint2 stack[STACK_SIZE];
     int sp = 0;
@@ -427,18 +455,10 @@ __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r
         float4 r0 = __ldg(nodes + 2 * (size_t)cb), r1 = __ldg(nodes + 2 * (size_t)cb + 1);
         // widened upper bound: never cull a box whose entry is within rounding of the best t
         float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
-        float ax = (l0.x - r.o.x) * idx, bx = (l1.x - r.o.x) * idx;
-        float ay = (l0.y - r.o.y) * idy, by = (l1.y - r.o.y) * idy;
-        float az = (l0.z - r.o.z) * idz, bz = (l1.z - r.o.z) * idz;
-        float ln = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_lo));
-        float lf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
-        ax = (r0.x - r.o.x) * idx, bx = (r1.x - r.o.x) * idx;
-        ay = (r0.y - r.o.y) * idy, by = (r1.y - r.o.y) * idy;
-        az = (r0.z - r.o.z) * idz, bz = (r1.z - r.o.z) * idz;
-        float rn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_lo));
-        float rf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
-        // entry <= exit with a relative guard band on the exit
-        bool hl = ln <= lf + fabsf(lf) * 1e-5f, hr = rn <= rf + fabsf(rf) * 1e-5f;
+        float ln, lf, rn, rf;
+        slab2(l0, l1, r0, r1, idx, idy, idz, nox, noy, noz, t_lo, t_hi, ln, lf, rn, rf);
+        // entry <= exit with a relative guard band on the exit (an exit < 0 never passes: entry >= t_lo > 0)
+        bool hl = ln <= lf * 1.00001f, hr = rn <= rf * 1.00001f;
         uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
         uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
         if (hl && hr) {
@@ -503,7 +523,8 @@ __device__ __forceinline__ Hit world_hit_bvh_ww(const DScene &s, const RayQ &r, 
   }
   bool ambiguous = false, overflow = false;
   if (s.n_recs > 0) {
-    const float idx = 1.0f / r.d.x, idy = 1.0f / r.d.y, idz = 1.0f / r.d.z;
+    const float idx = slab_rcp(r.d.x), idy = slab_rcp(r.d.y), idz = slab_rcp(r.d.z);
+    const float nox = -(r.o.x * idx), noy = -(r.o.y * idy), noz = -(r.o.z * idz);
     const float t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
     uint2 stack[STACK_SIZE];
     float stack_t[CULL ? STACK_SIZE : 1];
@@ -543,17 +564,9 @@ __device__ __forceinline__ Hit world_hit_bvh_ww(const DScene &s, const RayQ &r, 
           float4 l0 = __ldg(nodes + 2 * (size_t)ca), l1 = __ldg(nodes + 2 * (size_t)ca + 1);
           float4 r0 = __ldg(nodes + 2 * (size_t)cb), r1 = __ldg(nodes + 2 * (size_t)cb + 1);
           float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
-          float ax = (l0.x - r.o.x) * idx, bx = (l1.x - r.o.x) * idx;
-          float ay = (l0.y - r.o.y) * idy, by = (l1.y - r.o.y) * idy;
-          float az = (l0.z - r.o.z) * idz, bz = (l1.z - r.o.z) * idz;
-          float ln = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_lo));
-          float lf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
-          ax = (r0.x - r.o.x) * idx, bx = (r1.x - r.o.x) * idx;
-          ay = (r0.y - r.o.y) * idy, by = (r1.y - r.o.y) * idy;
-          az = (r0.z - r.o.z) * idz, bz = (r1.z - r.o.z) * idz;
-          float rn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_lo));
-          float rf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
-          bool hl = ln <= lf + fabsf(lf) * 1e-5f, hr = rn <= rf + fabsf(rf) * 1e-5f;
+          float ln, lf, rn, rf;
+          slab2(l0, l1, r0, r1, idx, idy, idz, nox, noy, noz, t_lo, t_hi, ln, lf, rn, rf);
+          bool hl = ln <= lf * 1.00001f, hr = rn <= rf * 1.00001f;
           uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
           uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
           if (hl && hr) {

@@ -10,7 +10,7 @@
 #include <string>
 
 #include "rt_internal.h"
-#include "rt_wide.cuh"
+#include "rt_walk.cuh"
 
 #ifndef RT_DEFAULT_TRAV
 #define RT_DEFAULT_TRAV 0  // traversal loop of the parity hook and the wavefront extend kernel
@@ -324,6 +324,105 @@ __global__ void __launch_bounds__(128, MINB) k_render_warp(DScene s, DCamera cam
     accum[3 * (size_t)idx + 2] += color.z;
   }
   flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims);
+}
+
+// ---- persistent kernel: no reconvergence at the query boundary -----------------------------------------
+// One loop iteration = one traversal ROUND of every lane (walk to a leaf, test the leaf).  A lane whose query
+// ended in the previous round first shades its hit, scatters or regenerates, and starts its next query —
+// then joins the round with the others.  Lanes never wait for the longest query of the warp; only the
+// shade block runs with the few lanes that need it.  Samples of a pixel still run in increasing order in
+// one lane: image and counters are bit-identical to k_render_fused.   (RT_TRAV=12 binary tree, 13 8-wide tree)
+template <bool STATS, class W, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_render_persist(DScene s, DCamera cam, RenderArgs a,
+                                                              float *__restrict__ accum, RenderCounters *ctr) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+  const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = i < a.height && j < a.width;
+  const int idx = i * a.width + j;
+  PathKey pk;
+  pk.pixel = (uint32_t)idx;
+  pk.sample = 0;
+  pk.k0 = a.k0;
+  pk.k1 = a.k1;
+  int k = a.spp_begin;
+  V3 color = mk(0.f, 0.f, 0.f), T = mk(1.f, 1.f, 1.f);
+  RayQ ray;
+  ray.o = mk(0.f, 0.f, 0.f);
+  ray.d = mk(0.f, 0.f, 1.f);
+  int depth = 0;
+  bool need_new = true, finished = !inside, have_query = false, ambiguous = false;
+  Range rg;
+  rg.t_from = 1e-3;
+  rg.t_to = (double)CUDART_INF_F;
+  rg.tf_f = float_ge(1e-3);
+  Best b;
+  best_init(b, rg.t_to);
+  W w;
+  w.begin(s, ray, rg);
+  w.done = true;
+  uint2 stack[W::kStack];
+  unsigned long long n_samples = 0, n_rays = 0, n_rays_ref = 0;
+  TravStats ts;
+  ts.nodes = ts.prims = 0;
+  for (;;) {
+    if (w.done) {  // between two queries of this lane
+      if (have_query) {
+        Hit h;
+        if (ambiguous || w.overflow) {
+          h = world_hit_seq(s, ray, rg.t_from, rg.t_to);
+        } else {
+          h.t = b.rec == REC_NONE ? 0.0 : b.t;
+          h.rec = b.rec;
+          h.seq = 0;
+        }
+        n_rays++;
+        const bool alive = h.rec != REC_NONE && shade_hit(s, ray, h, pk, depth, T, color);
+        if (alive) {
+          depth++;
+        } else {
+          k++;
+          need_new = true;
+        }
+        have_query = false;
+      }
+      while (!finished) {
+        if (need_new) {
+          if (k >= a.spp_end) {
+            finished = true;
+            break;
+          }
+          pk.sample = (uint32_t)k;
+          ray = camera_sample(cam, i, j, a.height, a.width, pk);
+          T = mk(1.f, 1.f, 1.f);
+          depth = 0;
+          need_new = false;
+          n_samples++;
+        }
+        n_rays_ref++;
+        if (depth < a.max_depth) {  // ray_tracing.cu:23: the query at depth == limit yields 0
+          have_query = true;
+          ambiguous = false;
+          query_begin(s, rg, b);
+          w.begin(s, ray, rg);
+          break;
+        }
+        k++;
+        need_new = true;
+      }
+    }
+    if (finished) break;
+    int first = 0;
+    const int n = w.template walk<STATS>(s, ray, b, stack, &first, &ts);
+    if (STATS) ts.prims += n;
+    for (int q = first, end = first + n; q < end;) q += rec_test(s.recs, q, ray, rg, b, ambiguous);
+  }
+  if (inside) {
+    accum[3 * (size_t)idx + 0] += color.x;
+    accum[3 * (size_t)idx + 1] += color.y;
+    accum[3 * (size_t)idx + 2] += color.z;
+  }
+  flush_counters(ctr, n_samples, n_rays, n_rays_ref, STATS ? ts.nodes : 0, STATS ? ts.prims : 0);
 }
 
 // ---- vote kernel: the fused kernel as a warp-scheduled state machine ------------------------------
@@ -750,7 +849,7 @@ int trav_variant(const rt_ctx *ctx) {
   const char *e = getenv("RT_TRAV");
   int dflt = ctx->scene.n_recs <= 4096 ? 1 : 0;
   int v = e ? atoi(e) : dflt;
-  return (v < 0 || v > 11) ? dflt : v;
+  return (v < 0 || v > 13) ? dflt : v;
 }
 
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
@@ -918,7 +1017,25 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     else                                                                                               \
       k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);    \
     break;
-    if (trav >= 9) {  // warp-synchronous kernel: 9 binary + coop, 10 wide, 11 wide + coop
+    if (trav >= 12) {  // persistent kernel: 12 binary tree, 13 8-wide tree
+#define RT_PERSIST_CASE(WK)                                                                                      \
+  if (stats_on)                                                                                                  \
+    k_render_persist<true, WK, 5><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);           \
+  else if (minb == 6)                                                                                            \
+    k_render_persist<false, WK, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);          \
+  else if (minb == 8)                                                                                            \
+    k_render_persist<false, WK, 8><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);          \
+  else if (minb == 4)                                                                                            \
+    k_render_persist<false, WK, 4><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);          \
+  else                                                                                                           \
+    k_render_persist<false, WK, 5><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+      if (trav == 12) {
+        RT_PERSIST_CASE(BinWalker)
+      } else {
+        RT_PERSIST_CASE(WideWalker)
+      }
+#undef RT_PERSIST_CASE
+    } else if (trav >= 9) {  // warp-synchronous kernel: 9 binary + coop, 10 wide, 11 wide + coop
 #define RT_WARP_CASE(M)                                                                                          \
   if (stats_on)                                                                                                  \
     k_render_warp<true, M, 5><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);               \

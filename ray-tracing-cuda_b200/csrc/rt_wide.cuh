@@ -54,7 +54,7 @@ __device__ __forceinline__ Hit world_hit_wide(const DScene &s, const RayQ &r, bo
     sm->ray[4][lane] = r.d.y;
     sm->ray[5][lane] = r.d.z;
   }
-  const float idx = 1.0f / r.d.x, idy = 1.0f / r.d.y, idz = 1.0f / r.d.z;
+  const float idx = slab_rcp(r.d.x), idy = slab_rcp(r.d.y), idz = slab_rcp(r.d.z);
   const float nox = -(r.o.x * idx), noy = -(r.o.y * idy), noz = -(r.o.z * idz);
   // float4 offsets of this ray's near / far plane arrays inside a node
   const int nx = idx < 0.f ? 6 : 0, ny = idy < 0.f ? 8 : 2, nz = idz < 0.f ? 10 : 4;

@@ -208,6 +208,33 @@ def random_rays(n, seed, lo, hi, toward=None, spread=1.0):
     return np.concatenate([o, d], 1).astype(np.float32)
 
 
+def degenerate_rays(n, seed, lo, hi):
+    """Seeded rays that stress the slab tests: one or two direction components exactly +-0 (infinite
+    reciprocal), origins on a grid that includes the box planes lo / hi exactly, and tiny components."""
+    rng = np.random.RandomState(seed)
+    grid = np.linspace(lo, hi, 9).astype(np.float32)
+    o = grid[rng.randint(0, 9, (n, 3))].astype(np.float32)
+    jitter = rng.uniform(-1, 1, (n, 3)).astype(np.float32) * np.float32((hi - lo) * 0.3)
+    o = np.where(rng.rand(n, 3) < 0.5, o, o + jitter).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    kind = rng.randint(0, 4, n)
+    for i in range(n):
+        ax = rng.permutation(3)
+        if kind[i] == 0:    # one component exactly 0
+            d[i, ax[0]] = 0.0
+        elif kind[i] == 1:  # axis parallel, either sign, -0 included
+            d[i, ax[0]] = 0.0
+            d[i, ax[1]] = -0.0
+        elif kind[i] == 2:  # one component far below the others
+            d[i, ax[0]] = np.float32(1e-30) * np.float32(rng.choice([-1, 1]))
+        else:               # denormal component
+            d[i, ax[0]] = np.float32(1e-42)
+    dot = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]).astype(np.float32) + (d[:, 2] * d[:, 2]).astype(np.float32)
+    inv = (np.float32(1) / np.sqrt(dot.astype(np.float32))).astype(np.float32)
+    d = (d * inv[:, None]).astype(np.float32)
+    return np.concatenate([o, d], 1).astype(np.float32)
+
+
 def hits_equal(a, b, fields=("t", "obj", "sub", "u", "v", "normal", "material")):
     """Bitwise comparison of two rt_hit arrays; returns indices that differ."""
     bad = np.zeros(len(a), bool)

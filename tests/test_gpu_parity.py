@@ -98,6 +98,21 @@ def test_sequential_scan_mode_bit_exact(ctx, name):
 
 
 @pytest.mark.parametrize("name", ["cornell_box", "spheres", "bunny9k", "soup100k"])
+def test_degenerate_directions(ctx, name):
+    """Rays with direction components exactly +-0 / denormal / 1e-30 and origins exactly on box planes: the
+    slab tests (FFMA form, clamped reciprocal) must never cull a record the reference accepts.  Every
+    traversal (binary, 8-wide, cooperative) against the oracle's exhaustive scan."""
+    s, cam, o = _setup(ctx, name)
+    lo, hi = _BOX[name]
+    rr = ck.degenerate_rays(40000, 33, lo, hi)
+    want = o.trace(rr, quirks=0)
+    for mode in (0, 2, 3, 8, 9, 10):
+        got = ctx.trace_closest(rr, mode=mode)
+        bad = ck.hits_equal(got, want, _fields(name))
+        assert len(bad) == 0, (mode, len(bad), rr[bad[:3]], got[bad[:3]], want[bad[:3]])
+
+
+@pytest.mark.parametrize("name", ["cornell_box", "spheres", "bunny9k", "soup100k"])
 def test_traversal_variants_identical(ctx, name):
     """Every traversal variant of the render kernels (modes 2..7 per-lane binary loops, 8 = 8-wide tree,
     9 = 8-wide tree + warp-cooperative record tests, 10 = binary tree + cooperative) returns the oracle's hits."""
@@ -189,13 +204,14 @@ def test_render_bit_exact_vs_oracle(ctx, name, hw, spp):
 
 @pytest.mark.parametrize("name,hw,spp", [("cornell_box", (72, 128), 8), ("spheres", (54, 96), 8), ("bunny9k", (54, 96), 4)])
 def test_render_kernel_variants_bit_exact(ctx, name, hw, spp, monkeypatch):
-    """Every fused-kernel variant (RT_TRAV 0..11; 5 = warp-scheduled vote kernel, 6..8 = pool kernel with 2..4 slots
-    per lane, 9..11 = warp-synchronous kernel: binary + cooperative record tests, 8-wide tree, 8-wide + cooperative)
+    """Every fused-kernel variant (RT_TRAV 0..13; 5 = warp-scheduled vote kernel, 6..8 = pool kernel with 2..4 slots
+    per lane, 9..11 = warp-synchronous kernel: binary + cooperative record tests, 8-wide tree, 8-wide + cooperative, 12..13 = persistent kernel
+    without reconvergence at the query boundary over the binary / 8-wide tree)
     renders the oracle's image."""
     s, cam, o = _setup(ctx, name)
     H, W = hw
     want, cnt = o.render_product(H, W, 0, spp, 99)
-    for trav in range(12):
+    for trav in range(14):
         monkeypatch.setenv("RT_TRAV", str(trav))
         got, _, st = ctx.render_host(H, W, spp, seed=99, flags=abi.RT_RENDER_FUSED)
         assert (got.view(np.uint32) == want.view(np.uint32)).all(), trav
