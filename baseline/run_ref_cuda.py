@@ -31,7 +31,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--tag", default="r1")
     ap.add_argument("--scenes", default="spheres,cornell_box,bunny,birthday")
-    ap.add_argument("--image-spp", type=int, default=256)
+    ap.add_argument("--image-spp", type=int, default=4096)  # north_star: rRMSE <= 1 % at 4096 spp
     ap.add_argument("--timeout", type=int, default=240)
     a = ap.parse_args()
     tmp = tempfile.mkdtemp()
@@ -42,7 +42,12 @@ def main():
            "birthday": (1080, 1920, 8, 90, 160), "soup100k": (540, 960, 1, 54, 96)}
     for name in a.scenes.split(","):
         H, W, spp, h, w = cfg[name]
-        scene, cam = rt.scenes.by_name(name)
+        if name == "spheres":
+            # the layout is drawn inside user code (spheres.cu:54-80): nvcc's device front end evaluates the draws of
+            # `vec3(a + rand, 0.2, b + rand)` left to right, g++ (the host build behind the oracle) right to left
+            scene, cam, _ = rt.scenes.spheres(arg_order="ltr")
+        else:
+            scene, cam = rt.scenes.by_name(name)
         extra, ref_scene = [], name
         if name == "bunny" or name.startswith("soup"):
             fp = os.path.join(tmp, name + "_faces.bin")
@@ -90,7 +95,8 @@ def main():
             img2 = acc2 / a.image_spp
             rr = lambda x, y: float(np.sqrt(((x - y) ** 2).sum()) / np.sqrt((y ** 2).sum()))
             res["image"] = {"spp": a.image_spp, "hw": [h, w], "rrmse_new_vs_ref": rr(img, ref_img),
-                            "rrmse_new_vs_new_other_seed": rr(img, img2), "mean_new": float(img.mean()), "mean_ref": float(ref_img.mean())}
+                            "rrmse_new_vs_new_other_seed": rr(img, img2), "mean_new": float(img.mean()), "mean_ref": float(ref_img.mean()),
+                            "target_rrmse": 0.01, "pass": bool(rr(img, ref_img) <= 0.01)}
         out[name] = res
         print(name, json.dumps(res), flush=True)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
