@@ -625,7 +625,7 @@ enum : int { ST_GEN = 0, ST_NODE = 1, ST_LEAF = 2, ST_SHADE = 3, ST_DONE = 4 };
 
 struct Trav {
   RayQ r;
-  float idx, idy, idz, t_lo;
+  float idx, idy, idz, nox, noy, noz, t_lo;
   Best b;
   uint32_t ca, cb;  // ST_NODE: the (a, b) words of an inner node; ST_LEAF: next record, end record
   int sp;
@@ -663,29 +663,23 @@ __device__ __forceinline__ int trav_begin(const DScene &s, Trav &tv, const Range
   tv.ambiguous = tv.overflow = false;
   tv.sp = 0;
   if (s.n_recs <= 0) return ST_SHADE;
-  tv.idx = 1.0f / tv.r.d.x;
-  tv.idy = 1.0f / tv.r.d.y;
-  tv.idz = 1.0f / tv.r.d.z;
+  tv.idx = slab_rcp(tv.r.d.x);
+  tv.idy = slab_rcp(tv.r.d.y);
+  tv.idz = slab_rcp(tv.r.d.z);
+  tv.nox = -(tv.r.o.x * tv.idx);
+  tv.noy = -(tv.r.o.y * tv.idy);
+  tv.noz = -(tv.r.o.z * tv.idz);
   tv.t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
   return trav_set(tv, s.root_a, s.root_b);
 }
 __device__ __forceinline__ int trav_node_step(const DScene &s, Trav &tv, uint2 *stack) {
   const float4 *__restrict__ nodes = s.nodes;
-  const RayQ &r = tv.r;
   float4 l0 = __ldg(nodes + 2 * (size_t)tv.ca), l1 = __ldg(nodes + 2 * (size_t)tv.ca + 1);
   float4 r0 = __ldg(nodes + 2 * (size_t)tv.cb), r1 = __ldg(nodes + 2 * (size_t)tv.cb + 1);
   float t_hi = tv.b.t_f + fabsf(tv.b.t_f) * 1e-5f;
-  float ax = (l0.x - r.o.x) * tv.idx, bx = (l1.x - r.o.x) * tv.idx;
-  float ay = (l0.y - r.o.y) * tv.idy, by = (l1.y - r.o.y) * tv.idy;
-  float az = (l0.z - r.o.z) * tv.idz, bz = (l1.z - r.o.z) * tv.idz;
-  float ln = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tv.t_lo));
-  float lf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
-  ax = (r0.x - r.o.x) * tv.idx, bx = (r1.x - r.o.x) * tv.idx;
-  ay = (r0.y - r.o.y) * tv.idy, by = (r1.y - r.o.y) * tv.idy;
-  az = (r0.z - r.o.z) * tv.idz, bz = (r1.z - r.o.z) * tv.idz;
-  float rn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tv.t_lo));
-  float rf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_hi));
-  bool hl = ln <= lf + fabsf(lf) * 1e-5f, hr = rn <= rf + fabsf(rf) * 1e-5f;
+  float ln, lf, rn, rf;
+  slab2(l0, l1, r0, r1, tv.idx, tv.idy, tv.idz, tv.nox, tv.noy, tv.noz, tv.t_lo, t_hi, ln, lf, rn, rf);
+  bool hl = ln <= lf * 1.00001f, hr = rn <= rf * 1.00001f;
   uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
   uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
   if (hl && hr) {

@@ -425,6 +425,128 @@ __global__ void __launch_bounds__(128, MINB) k_render_persist(DScene s, DCamera 
   flush_counters(ctr, n_samples, n_rays, n_rays_ref, STATS ? ts.nodes : 0, STATS ? ts.prims : 0);
 }
 
+// Out-of-line forms of the rare steps of the streaming kernel: the node step is the hot loop of a long query
+// and must not carry the registers (or the spills) of shading, camera sampling and the record tests.
+static __device__ __noinline__ bool shade_hit_call(const DScene &s, RayQ &ray, const Hit &h, const PathKey &pk, int depth,
+                                                   V3 &T, V3 &color) {
+  return shade_hit(s, ray, h, pk, depth, T, color);
+}
+static __device__ __noinline__ RayQ camera_sample_call(const DCamera &cam, int i, int j, int height, int width,
+                                                       const PathKey &pk) {
+  return camera_sample(cam, i, j, height, width, pk);
+}
+static __device__ __noinline__ int trav_leaf_step_call(const DScene &s, Trav &tv, const Range &rg, const uint2 *stack) {
+  return trav_leaf_step(s, tv, rg, stack);
+}
+static __device__ __noinline__ Hit trav_finish_call(const DScene &s, const Trav &tv, const Range &rg) {
+  return trav_finish(s, tv, rg);
+}
+
+// ---- streaming kernel: single steps, deferred minority work -----------------------------------------------
+// For scenes whose queries are long (hundreds of node steps: the 1M-10M triangle soups) the per-lane loops leave
+// 5 of 32 lanes active (profiles/r01_j_soup10m_fused_ncu_summary.txt): the warp reconverges after every query and
+// waits for its longest one.  Here one loop iteration = one NODE step for every lane that has one pending; lanes
+// whose next step is a record test (LEAF) or the work between two queries (SHADE: finish the query, shade,
+// scatter or regenerate, begin the next query) wait until `leaf_min` / `shade_min` lanes of the warp wait for
+// the same kind — or nothing else is left to do — and then run it together.  Unlike the vote kernel (one kind
+// per iteration, the minority idles) the majority kind never stops, so a waiting lane costs one idle lane for a
+// few iterations instead of stalling the warp.  Same step functions as the vote kernel: identical hits, image
+// and counters.   (RT_TRAV=14; RT_STREAM_LEAF / RT_STREAM_SHADE set the two thresholds)
+template <bool STATS, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_render_stream(DScene s, DCamera cam, RenderArgs a, int leaf_min,
+                                                             int shade_min, float *__restrict__ accum,
+                                                             RenderCounters *ctr) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+  const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = i < a.height && j < a.width;
+  const int idx = i * a.width + j;
+  PathKey pk;
+  pk.pixel = (uint32_t)idx;
+  pk.sample = 0;
+  pk.k0 = a.k0;
+  pk.k1 = a.k1;
+  int k = a.spp_begin;
+  V3 color = mk(0.f, 0.f, 0.f), T = mk(1.f, 1.f, 1.f);
+  int depth = 0;
+  bool need_new = true, have_query = false;
+  int state = inside ? ST_SHADE : ST_DONE;
+  Range rg;
+  rg.t_from = 1e-3;
+  rg.t_to = (double)CUDART_INF_F;
+  rg.tf_f = float_ge(1e-3);
+  Trav tv;
+  tv.r.o = mk(0.f, 0.f, 0.f);
+  tv.r.d = mk(0.f, 0.f, 1.f);
+  tv.sp = 0;
+  tv.ambiguous = tv.overflow = false;
+  uint2 stack[STACK_SIZE];
+  unsigned long long n_samples = 0, n_rays = 0, n_rays_ref = 0, n_nodes = 0, n_prims = 0, n_iters = 0, n_lanes = 0;
+  for (;;) {
+    const unsigned mN = __ballot_sync(FULL, state == ST_NODE);
+    const unsigned mL = __ballot_sync(FULL, state == ST_LEAF);
+    const unsigned mS = __ballot_sync(FULL, state == ST_SHADE);
+    if ((mN | mL | mS) == 0u) break;
+    const bool do_leaf = __popc(mL) >= leaf_min || mN == 0u;
+    const bool do_shade = __popc(mS) >= shade_min || mN == 0u;
+    if (STATS && lane == 0) {
+      n_iters++;
+      n_lanes += __popc(mN) + (do_leaf ? __popc(mL) : 0) + (do_shade ? __popc(mS) : 0);
+    }
+    if (do_shade && state == ST_SHADE) {  // between two queries of this lane
+      if (have_query) {
+        Hit h = trav_finish_call(s, tv, rg);
+        n_rays++;
+        const bool alive = h.rec != REC_NONE && shade_hit_call(s, tv.r, h, pk, depth, T, color);
+        if (alive) {
+          depth++;
+        } else {
+          k++;
+          need_new = true;
+        }
+        have_query = false;
+      }
+      for (;;) {
+        if (need_new) {
+          if (k >= a.spp_end) {
+            accum[3 * (size_t)idx + 0] += color.x;
+            accum[3 * (size_t)idx + 1] += color.y;
+            accum[3 * (size_t)idx + 2] += color.z;
+            state = ST_DONE;
+            break;
+          }
+          pk.sample = (uint32_t)k;
+          tv.r = camera_sample_call(cam, i, j, a.height, a.width, pk);
+          T = mk(1.f, 1.f, 1.f);
+          depth = 0;
+          need_new = false;
+          n_samples++;
+        }
+        n_rays_ref++;
+        if (depth < a.max_depth) {  // ray_tracing.cu:23: the query at depth == limit yields 0
+          have_query = true;
+          state = trav_begin(s, tv, rg);
+          break;
+        }
+        k++;
+        need_new = true;
+      }
+    } else if (do_leaf && state == ST_LEAF) {
+      if (STATS) n_prims++;
+      state = trav_leaf_step_call(s, tv, rg, stack);
+    } else if (state == ST_NODE) {
+      if (STATS) n_nodes += 2;
+      state = trav_node_step(s, tv, stack);
+    }
+  }
+  flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims);
+  if (STATS && lane == 0) {
+    atomicAdd(&ctr->sched_iters, n_iters);
+    atomicAdd(&ctr->sched_lanes, n_lanes);
+  }
+}
+
 // ---- vote kernel: the fused kernel as a warp-scheduled state machine ------------------------------
 // Same work as k_render_fused (one lane per pixel, samples in increasing order, paths regenerated in
 // registers) but every lane carries an explicit state — GEN (needs a camera sample), NODE (inner-node
@@ -793,8 +915,8 @@ __global__ void __launch_bounds__(256) k_wf_logic(DScene s, DCamera cam, RenderA
   flush_counters(ctr, n_samples, 0, n_rays_ref, 0, 0);
 }
 
-template <bool STATS, int TRAV>
-__global__ void __launch_bounds__(128) k_wf_extend(DScene s, WfState w, int qi, RenderCounters *ctr) {
+template <bool STATS, int TRAV, int MINB = 5>
+__global__ void __launch_bounds__(128, MINB) k_wf_extend(DScene s, WfState w, int qi, RenderCounters *ctr) {
   const uint32_t n_in = w.count[qi];
   unsigned long long n_rays = 0, n_nodes = 0, n_prims = 0;
   TravStats ts;
@@ -849,7 +971,7 @@ int trav_variant(const rt_ctx *ctx) {
   const char *e = getenv("RT_TRAV");
   int dflt = ctx->scene.n_recs <= 4096 ? 1 : 0;
   int v = e ? atoi(e) : dflt;
-  return (v < 0 || v > 13) ? dflt : v;
+  return (v < 0 || v > 14) ? dflt : v;
 }
 
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
@@ -939,6 +1061,9 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, flo
   w.count = ctx->wf[6].as<uint32_t>();
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+  // resident blocks per SM the extend kernel is compiled for: long, latency-bound queries want warps, not registers
+  const char *wmb = getenv("RT_WF_MINB");
+  const int wf_minb = wmb ? atoi(wmb) : (ctx->scene.n_recs >= 500000 ? 10 : 5);
   RT_CUDA(cudaMemsetAsync(w.count, 0, 8, st));
   // first logic pass reads no queue and fills queue 1
   int qi = 0;
@@ -950,9 +1075,15 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, flo
     RT_CUDA(cudaMemcpyAsync(&live, w.count + qi, 4, cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaStreamSynchronize(st));
     if (live == 0) break;
-    int gb = std::min(nblk(live, 128), sms * 16);
+    int gb = std::min(nblk(live, 128), sms * 32);
     if (stats_on)
       k_wf_extend<true, RT_DEFAULT_TRAV><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
+    else if (wf_minb >= 12)
+      k_wf_extend<false, RT_DEFAULT_TRAV, 12><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
+    else if (wf_minb >= 10)
+      k_wf_extend<false, RT_DEFAULT_TRAV, 10><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
+    else if (wf_minb >= 8)
+      k_wf_extend<false, RT_DEFAULT_TRAV, 8><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
     else
       k_wf_extend<false, RT_DEFAULT_TRAV><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
     k_wf_reset<<<1, 1, 0, st>>>(w.count, qi ^ 1);
@@ -1017,7 +1148,18 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     else                                                                                               \
       k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);    \
     break;
-    if (trav >= 12) {  // persistent kernel: 12 binary tree, 13 8-wide tree
+    if (trav == 14) {  // streaming kernel
+      const char *e1 = getenv("RT_STREAM_LEAF"), *e2 = getenv("RT_STREAM_SHADE");
+      const int leaf_min = e1 ? atoi(e1) : 8, shade_min = e2 ? atoi(e2) : 8;
+      if (stats_on)
+        k_render_stream<true, 5><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, leaf_min, shade_min, d_accum_rgb, ctr);
+      else if (minb == 8)
+        k_render_stream<false, 8><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, leaf_min, shade_min, d_accum_rgb, ctr);
+      else if (minb == 6)
+        k_render_stream<false, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, leaf_min, shade_min, d_accum_rgb, ctr);
+      else
+        k_render_stream<false, 5><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, leaf_min, shade_min, d_accum_rgb, ctr);
+    } else if (trav >= 12) {  // persistent kernel: 12 binary tree, 13 8-wide tree
 #define RT_PERSIST_CASE(WK)                                                                                      \
   if (stats_on)                                                                                                  \
     k_render_persist<true, WK, 5><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);           \

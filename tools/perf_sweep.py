@@ -9,11 +9,11 @@ import torch
 rt = importlib.import_module("ray-tracing-cuda_b200")
 
 CASES = {"cornell_box": (1024, 1024, 64), "spheres": (720, 1280, 32), "bunny": (1080, 1920, 16),
-         "birthday": (1080, 1920, 32), "soup1m": (1080, 1920, 4), "soup100k": (1080, 1920, 8), "soup10m": (2160, 3840, 2), "soup1m4k": (2160, 3840, 4)}
+         "birthday": (1080, 1920, 32), "soup1m": (1080, 1920, 4), "soup100k": (1080, 1920, 8), "soup10m": (2160, 3840, 2), "soup1m4k": (2160, 3840, 4), "soup1m16": (1080, 1920, 16), "soup10m8": (1080, 1920, 8)}
 
 def scene_of(name):
     if name.startswith("soup"):
-        n = {"soup1m": 1000000, "soup100k": 100000, "soup10m": 10000000, "soup1m4k": 1000000}[name]
+        n = {"soup1m": 1000000, "soup100k": 100000, "soup10m": 10000000, "soup1m4k": 1000000, "soup1m16": 1000000, "soup10m8": 10000000}[name]
         return rt.scenes.soup(n)
     return rt.scenes.by_name(name)
 
