@@ -103,6 +103,19 @@ def load_profile_constants():
         return {}
 
 
+def ref_scene_named(ck, name):
+    """The reference's own scene (oracle/_ref host build of scenes/<name>.cu) with the same synthetic mesh / texture
+    the CUDA arm renders (the model and image files of the reference repo are absent: SURVEY 8d)."""
+    pkg = ck.pkg
+    if name == "bunny":
+        scene, _ = pkg.scenes.by_name(name)
+        return ck.RefScene.named(name, 10086, scene.meshes[0], None)
+    if name == "birthday":
+        scene, _ = pkg.scenes.by_name(name)
+        return ck.RefScene.named(name, 10086, None, scene.textures[0])
+    return ck.RefScene.named(name, 10086)
+
+
 def reference_arm(args, workload):
     """The reference's own CPU code for the path (oracle/_ref/libref_host.so) on all host threads."""
     rank = int(os.environ.get("RANK", "0"))
@@ -122,7 +135,7 @@ def reference_arm(args, workload):
     kind = "reference" if ck.have_ref() else "port"
     threads = os.cpu_count() or 1
     if kind == "reference":
-        ref = ck.RefScene.named(name, 10086)
+        ref = ref_scene_named(ck, name)
         run = lambda rows, s: ref.render(rows, W, s, post=0, nthreads=threads)  # noqa: E731
     else:
         pkg = ck.pkg
@@ -161,23 +174,31 @@ def cpu_baseline(name, H, W, spp, budget_s=12.0):
     threads = os.cpu_count() or 1
     if ck.have_ref():
         kind = "reference"
-        ref = ck.RefScene.named(name, 10086)
-        run = lambda s: ref.render(H, W, s, post=0, nthreads=threads)  # noqa: E731
+        ref = ref_scene_named(ck, name)
+        run = lambda s, h, w: ref.render(h, w, s, post=0, nthreads=threads)  # noqa: E731
     else:
         kind = "port"
         scene, cam = ck.pkg.scenes.by_name(name)
         o = ck.OracleScene(scene)
         o.camera_look_at(cam)
-        run = lambda s: o.render_reference(H, W, s, 10086, nthreads=threads)  # noqa: E731
+        run = lambda s, h, w: o.render_reference(h, w, s, 10086, nthreads=threads)  # noqa: E731
+    # bounded sample: probe a quarter-resolution frame (same camera, same field of view); if a full frame at 1 spp
+    # would not fit the budget (bunny: 2048-triangle leaves), the quarter-resolution frame is the sample
+    h4, w4 = max(H // 4, 1), max(W // 4, 1)
     t0 = time.perf_counter()
-    run(1)
-    t1 = time.perf_counter() - t0
-    spp_s = max(1, min(spp, int(budget_s / max(t1, 1e-6))))
+    run(1, h4, w4)
+    tp = time.perf_counter() - t0
+    if tp * 16 > budget_s:
+        hs, ws, label = h4, w4, f"quarter-resolution {w4}x{h4} frame"
+        spp_s = max(1, min(spp, int(budget_s / max(tp, 1e-6))))
+    else:
+        hs, ws, label = H, W, f"full {W}x{H} frame"
+        spp_s = max(1, min(spp, int(budget_s / max(tp * 16, 1e-6))))
     t0 = time.perf_counter()
-    run(spp_s)
+    run(spp_s, hs, ws)
     t = time.perf_counter() - t0
-    return {"value": H * W * spp_s / t / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
-            "sample": f"full {W}x{H} frame at {spp_s} spp (of {spp}), {t:.1f} s"}
+    return {"value": hs * ws * spp_s / t / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
+            "sample": f"{label} at {spp_s} spp (of {spp}), {t:.1f} s"}
 
 
 def ref_cuda_baseline(name, H, W, scene, spp=16):
@@ -339,8 +360,14 @@ def main():
     alg_bytes = H * W * 24 + build.n_prims * 48 + build.n_nodes * 32  # accumulation r+w, scene read once
     hbm_achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
     is_soup = name.startswith("soup")
+    # DRAM bytes per launch from the committed ncu capture of the same workload (profiles/constants.json).  Cache-
+    # resident scenes: the traffic is the accumulation buffer + one read of the scene, independent of spp.  Soups:
+    # node/record misses dominate and scale with the samples of the launch (capture spp -> this launch's spp).
+    traffic = consts.get("dram_bytes_per_launch", {}).get(args.workload)
+    if traffic is not None and is_soup:
+        traffic = int(traffic * float(count) / consts.get("dram_bytes_capture_spp", {}).get(args.workload, count))
     roofline = {"bound": "issue", "achieved": achieved / 1e9, "peak": issue_peak / 1e9, "unit": "Gwarp-inst/s",
-                "frac": achieved / issue_peak, "traffic": consts.get("dram_bytes_per_launch", {}).get(args.workload),
+                "frac": achieved / issue_peak, "traffic": traffic,
                 "kernel": kernel, "kernel_ms": kern_ms, "sm_mhz": sm_mhz,
                 "peak_source": "148 SMs x 4 issue slots x sampled SM clock (B200_PROFILING.md / SURVEY 8d); not a tensor or HBM bound",
                 "algorithmic": {"box_tests_per_ray": boxes / max(float(st_prof.rays), 1.0),
