@@ -12,6 +12,9 @@
 //   apply: each owner folds the results of its items in record order with rec_test's own rules.
 // The arithmetic per (ray, record) pair and the order in which an owner sees its records are those of
 // rec_test, so hits are bit-identical to the per-lane traversals (tests/test_gpu_parity.py).
+// Measured (profiles/r01_h_variants_sweep.txt): with the while-while loop the record tests already run at 12 lanes
+// and the pooling (scan, 3 __syncwarp, shared-memory round trip per round) costs more than it saves: 1559 vs
+// 1909 Msamples/s on Cornell.  NOT the default; kept as a variant (RT_TRAV=9/11) with its evidence.
 #pragma once
 #include "rt_device.cuh"
 

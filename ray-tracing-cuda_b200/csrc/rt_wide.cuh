@@ -1,15 +1,17 @@
-// rt_wide.cuh — closest hit over the 8-wide tree (the render kernels' default traversal).
+// rt_wide.cuh — closest hit over the 8-wide tree (traversal variants RT_TRAV=10/11/13; parity modes 8/9).
 //
 // Why wide: ncu on the binary while-while loop (profiles/r01_g_cornell_ww_ncu_summary.txt) shows the inner-node
 // steps — 48 % of all warp instructions — running with 9 of 32 lanes: a ray takes 7-8 dependent two-box steps
 // and the lanes of a warp need different numbers of them.  With 8 children per node a Cornell-box ray takes
-// 2-3 steps (bunny 4-5 instead of 12), the lanes stay in lockstep, and per child the box test shrinks to
-// 6 FFMA + 2 three-input min/max because the ray selects near/far planes by address (direction octant).
+// 1-2 steps, and per child the box test shrinks to 6 FFMA + 2 three-input min/max because the ray selects its
+// near / far planes by address (direction octant).
+// Measured (profiles/r01_h_cornell_wide_ncu_summary.txt, r01_h_variants_sweep.txt): -7 % warp instructions and
+// +2 % on Cornell, equal on bunny, slower on spheres and the soups (more box tests per ray, 14 LDG.128 per step):
+// NOT the default; kept as a variant with its evidence.
 //
-// Box culling only has to be conservative (rt_device.cuh header): planes are evaluated as
-// fma(plane, 1/d, -(o/d)); the error of that form is covered by the builder's relative box padding plus the
-// relative guard bands on t below.  A NaN slab (0 * inf) is ignored by fminf/fmaxf,
-// which only widens the interval.
+// Box culling only has to be conservative (rt_device.cuh, slab2): planes are evaluated as
+// fma(plane, 1/d, -(o/d)) with 1/d from slab_rcp (finite); the rounding of that form is covered by the builder's
+// relative box padding plus the relative guard bands on t below.
 //
 // Visit order: nearest hit child first; the other hit children are pushed with their entry distance and
 // dropped at pop time once the closest hit has moved in front of them.  Hits are decided by rec_test /
