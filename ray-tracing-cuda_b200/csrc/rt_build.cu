@@ -261,14 +261,15 @@ __global__ void k_refit(const uint32_t *left, const uint32_t *right, const uint3
 // only leaves are left (the greedy collapse of Wald et al. 2008 / Ylitie et al. 2017).  Inner
 // children get a wide-node index (atomic counter) and go to the next level's queue.  WRITE = false
 // only counts (sizes the node buffer).
-template <bool WRITE>
+template <bool WRITE, int W>
 __global__ void k_wide_expand(const float4 *__restrict__ nodes, const uint2 *__restrict__ in_q, int n_in, uint2 *out_q,
                               uint32_t *counters /* [0] next-level queue length, [1] wide nodes allocated */,
                               float4 *wnodes) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_in) return;
   const uint32_t bn = in_q[t].x, wn = in_q[t].y;
-  uint32_t slot[WIDE];
+  uint32_t slot[W];
+  using L = WideLayout<W>;
   int n;
   {
     uint32_t a = __float_as_uint(nodes[2 * (size_t)bn].w), b = __float_as_uint(nodes[2 * (size_t)bn + 1].w);
@@ -281,7 +282,7 @@ __global__ void k_wide_expand(const float4 *__restrict__ nodes, const uint2 *__r
       n = 2;
     }
   }
-  while (n < WIDE) {
+  while (n < W) {
     int best = -1;
     float best_area = -1.f;
     for (int i = 0; i < n; i++) {
@@ -298,14 +299,14 @@ __global__ void k_wide_expand(const float4 *__restrict__ nodes, const uint2 *__r
     slot[best] = a;
     slot[n++] = b;
   }
-  float *f = WRITE ? reinterpret_cast<float *>(wnodes + (size_t)WNODE_F4 * wn) : nullptr;
+  float *f = WRITE ? reinterpret_cast<float *>(wnodes + (size_t)L::F4 * wn) : nullptr;
   uint32_t *u = reinterpret_cast<uint32_t *>(f);
-  for (int i = 0; i < WIDE; i++) {
+  for (int i = 0; i < W; i++) {
     if (i >= n) {
       if (WRITE) {
-        f[i] = f[8 + i] = f[16 + i] = CUDART_INF_F;
-        f[24 + i] = f[32 + i] = f[40 + i] = -CUDART_INF_F;
-        u[48 + i] = WREF_EMPTY;
+        f[i] = f[W + i] = f[2 * W + i] = CUDART_INF_F;
+        f[3 * W + i] = f[4 * W + i] = f[5 * W + i] = -CUDART_INF_F;
+        u[6 * W + i] = WREF_EMPTY;
       }
       continue;
     }
@@ -320,16 +321,15 @@ __global__ void k_wide_expand(const float4 *__restrict__ nodes, const uint2 *__r
       if (out_q) out_q[q] = make_uint2(slot[i], ref);
     }
     if (WRITE) {
-      f[i] = lo.x, f[8 + i] = lo.y, f[16 + i] = lo.z;
-      f[24 + i] = hi.x, f[32 + i] = hi.y, f[40 + i] = hi.z;
-      u[48 + i] = ref;
+      f[i] = lo.x, f[W + i] = lo.y, f[2 * W + i] = lo.z;
+      f[3 * W + i] = hi.x, f[4 * W + i] = hi.y, f[5 * W + i] = hi.z;
+      u[6 * W + i] = ref;
     }
   }
   if (WRITE) {
-    u[56] = (1u << n) - 1u;
-    u[57] = (uint32_t)n;
-    u[58] = u[59] = 0;
-    u[60] = u[61] = u[62] = u[63] = 0;
+    u[7 * W] = (1u << n) - 1u;
+    u[7 * W + 1] = (uint32_t)n;
+    for (int q = 2; q < W; q++) u[7 * W + q] = 0;
   }
 }
 
@@ -652,35 +652,45 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
       return RT_ERR_LIMIT;
     }
     uint32_t *cnt = S[10].as<uint32_t>();
-    for (int pass = 0; pass < 2; pass++) {
-      uint2 *in = S[6].as<uint2>(), *out = S[7].as<uint2>();
-      uint2 seed = make_uint2(0u, 0u);
-      uint32_t c[2] = {0u, 1u};
-      RT_CUDA(cudaMemcpyAsync(in, &seed, sizeof(seed), cudaMemcpyHostToDevice, st));
-      RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
-      int n_in = 1, levels = 0;
-      while (n_in > 0) {
-        if (pass == 0)
-          k_wide_expand<false><<<nblk(n_in), 256, 0, st>>>(ctx->nodes.as<float4>(), in, n_in, out, cnt, nullptr);
-        else
-          k_wide_expand<true><<<nblk(n_in), 256, 0, st>>>(ctx->nodes.as<float4>(), in, n_in, out, cnt,
-                                                          ctx->wnodes.as<float4>());
-        RT_CUDA(cudaMemcpyAsync(c, cnt, sizeof(c), cudaMemcpyDeviceToHost, st));
-        RT_CUDA(cudaStreamSynchronize(st));
-        n_in = (int)c[0];
-        c[0] = 0;
+    for (int width = 8; width >= 4; width -= 4) {
+      DevBuf &wbuf = width == 8 ? ctx->wnodes : ctx->wnodes4;
+      const int f4 = width == 8 ? WideLayout<8>::F4 : WideLayout<4>::F4;
+      int n_w = 0;
+      for (int pass = 0; pass < 2; pass++) {
+        uint2 *in = S[6].as<uint2>(), *out = S[7].as<uint2>();
+        uint2 seed = make_uint2(0u, 0u);
+        uint32_t c[2] = {0u, 1u};
+        RT_CUDA(cudaMemcpyAsync(in, &seed, sizeof(seed), cudaMemcpyHostToDevice, st));
         RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
-        std::swap(in, out);
-        levels++;
+        int n_in = 1, levels = 0;
+        while (n_in > 0) {
+          const float4 *bn = ctx->nodes.as<float4>();
+          float4 *wn = pass ? wbuf.as<float4>() : nullptr;
+          if (width == 8) {
+            if (pass == 0) k_wide_expand<false, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
+            else k_wide_expand<true, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
+          } else {
+            if (pass == 0) k_wide_expand<false, 4><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
+            else k_wide_expand<true, 4><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
+          }
+          RT_CUDA(cudaMemcpyAsync(c, cnt, sizeof(c), cudaMemcpyDeviceToHost, st));
+          RT_CUDA(cudaStreamSynchronize(st));
+          n_in = (int)c[0];
+          c[0] = 0;
+          RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
+          std::swap(in, out);
+          levels++;
+        }
+        if (pass == 0) {
+          n_w = (int)c[1];
+          RT_CUDA(wbuf.reserve((size_t)n_w * f4 * 16));
+        } else if ((int)c[1] != n_w) {
+          set_error("rt_scene_commit: wide collapse passes disagree");
+          return RT_ERR_CUDA;
+        }
+        if (width == 8) wide_depth = levels;
       }
-      if (pass == 0) {
-        n_wnodes = (int)c[1];
-        RT_CUDA(ctx->wnodes.reserve((size_t)n_wnodes * WNODE_F4 * 16));
-      } else if ((int)c[1] != n_wnodes) {
-        set_error("rt_scene_commit: wide collapse passes disagree");
-        return RT_ERR_CUDA;
-      }
-      wide_depth = levels;
+      if (width == 8) n_wnodes = n_w;
     }
     RT_CUDA(cudaGetLastError());
   }
@@ -692,6 +702,7 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   DScene &s = ctx->scene;
   s.nodes = ctx->nodes.as<float4>();
   s.wnodes = n_wnodes > 0 ? ctx->wnodes.as<float4>() : nullptr;
+  s.wnodes4 = n_wnodes > 0 ? ctx->wnodes4.as<float4>() : nullptr;
   s.n_wnodes = n_wnodes;
   s.recs = ctx->recs.as<float4>();
   s.recs_seq = recs_seq;

@@ -71,6 +71,12 @@ constexpr int STACK_SIZE = 64;
 // empty slot = WREF_EMPTY with an inverted box.
 // ------------------------------------------------------------------------------------------------
 constexpr int WIDE = 8, WNODE_F4 = 16;
+// Same layout at width W = 4 (128-byte nodes, one cache line): W/4 float4 per component array.
+//   float4 index of lo.{x,y,z}: axis * W/4;  hi: (3 + axis) * W/4;  ref: 6 * W/4;  meta: 7 * W/4
+template <int W>
+struct WideLayout {
+  static constexpr int G = W / 4, F4 = 8 * G, HI = 3 * G, REF = 6 * G, META = 7 * G;
+};
 constexpr uint32_t WLEAF = 0x80000000u, WREF_EMPTY = 0xffffffffu;
 constexpr int WLEAF_COUNT_SHIFT = 28, WLEAF_MAX_COUNT = 7;
 constexpr uint32_t WLEAF_FIRST_MASK = (1u << WLEAF_COUNT_SHIFT) - 1;
@@ -92,6 +98,7 @@ struct DTexture {
 struct DScene {
   const float4 *nodes;     // 32-byte nodes: {lo.xyz, a}, {hi.xyz, b}
   const float4 *wnodes;    // 256-byte wide nodes (8 children), node 0 = root; null when n_recs == 0
+  const float4 *wnodes4;   // 128-byte wide nodes (4 children)
   const float4 *recs;      // records in BVH (Morton) order, 3 float4 each
   const float4 *recs_seq;  // records in list order (Append order; faces in post-sort order; incl. SKY)
   const float *face_uv;    // per BVH-order record: 6 floats (Face<true> texcoords), or null

@@ -55,7 +55,7 @@ struct rt_ctx {
   rtc::DCamera camera{};
   rt_camera camera_host{};
   // scene storage
-  rtc::DevBuf nodes, wnodes, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;
+  rtc::DevBuf nodes, wnodes, wnodes4, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;
   std::vector<void *> tex_allocs;
   // build scratch
   rtc::DevBuf scratch[12];

@@ -51,7 +51,8 @@ __device__ __forceinline__ rt_hit make_rt_hit(const DScene &s, const RayQ &r, co
 }
 
 // Parity hook of the warp-synchronous traversals (every lane of a warp enters the query):
-// mode 8 wide tree, per-lane record tests; 9 wide tree + cooperative record tests; 10 binary tree + cooperative.
+// mode 8 wide tree, per-lane record tests; 9 wide tree + cooperative record tests; 10 binary tree + cooperative;
+// 11 4-wide tree, per-lane record tests.
 __global__ void __launch_bounds__(128) k_trace_closest_warp(DScene s, const float *__restrict__ rays, int64_t n,
                                                             double t_from, double t_to, int mode, rt_hit *out) {
   __shared__ CoopWarp sm_all[4];
@@ -69,6 +70,8 @@ __global__ void __launch_bounds__(128) k_trace_closest_warp(DScene s, const floa
     h = world_hit_wide<false, false>(s, r, active, t_from, t_to, &sm, nullptr);
   else if (mode == 9)
     h = world_hit_wide<false, true>(s, r, active, t_from, t_to, &sm, nullptr);
+  else if (mode == 11)
+    h = world_hit_wide<false, false, 4>(s, r, active, t_from, t_to, &sm, nullptr);
   else
     h = world_hit_coop<false>(s, r, active, t_from, t_to, sm, nullptr);
   if (active) out[i] = make_rt_hit(s, r, h);
@@ -220,7 +223,11 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
     n_rays_ref++;
     bool alive = depth < a.max_depth;  // ray_tracing.cu:23: the query at depth == limit yields 0
     if (alive) {
-      Hit h = world_hit_bvh<STATS, TRAV>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
+      Hit h;
+      if constexpr (TRAV >= 16)
+        h = world_hit_wide_ifif<STATS, TRAV == 16 ? 4 : 8>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
+      else
+        h = world_hit_bvh<STATS, TRAV>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
       n_rays++;
       if (STATS) {
         n_nodes += ts.nodes;
@@ -253,14 +260,15 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
 //   MODE 0: binary tree + cooperative record tests      (RT_TRAV=9)
 //   MODE 1: 8-wide tree, per-lane record tests          (RT_TRAV=10)
 //   MODE 2: 8-wide tree + cooperative record tests      (RT_TRAV=11)
+//   MODE 3: 4-wide tree, per-lane record tests          (RT_TRAV=15)
 // Image and counters are bit-identical to k_render_fused.
 template <bool STATS, int MODE, int MINB>
 __global__ void __launch_bounds__(128, MINB) k_render_warp(DScene s, DCamera cam, RenderArgs a,
                                                            float *__restrict__ accum, RenderCounters *ctr) {
   constexpr unsigned FULL = 0xffffffffu;
-  __shared__ CoopWarp sm_all[MODE == 1 ? 1 : 4];
+  __shared__ CoopWarp sm_all[(MODE == 1 || MODE == 3) ? 1 : 4];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  CoopWarp &sm = sm_all[MODE == 1 ? 0 : warp];
+  CoopWarp &sm = sm_all[(MODE == 1 || MODE == 3) ? 0 : warp];
   const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
   const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
   const bool inside = i < a.height && j < a.width;
@@ -298,6 +306,8 @@ __global__ void __launch_bounds__(128, MINB) k_render_warp(DScene s, DCamera cam
     Hit h;
     if (MODE == 0)
       h = world_hit_coop<STATS>(s, ray, query, 1e-3, (double)CUDART_INF_F, sm, &ts);
+    else if (MODE == 3)
+      h = world_hit_wide<STATS, false, 4>(s, ray, query, 1e-3, (double)CUDART_INF_F, &sm, &ts);
     else
       h = world_hit_wide<STATS, MODE == 2>(s, ray, query, 1e-3, (double)CUDART_INF_F, &sm, &ts);
     bool alive = false;
@@ -963,15 +973,18 @@ using namespace rtc;
 namespace {
 inline int nblk(size_t n, int b) { return (int)((n + b - 1) / b); }
 
-// Traversal variant of the render kernels: RT_TRAV=0..4 overrides the default (diagnostics).
-// Default (measured, profiles/r01_b_sweep_variants.txt): scenes of a few thousand records are
-// dominated by incoherent bounce rays in a cache-resident tree, where the while-while loop wins;
-// large meshes, dominated by coherent primary rays / long traversals, run the if-if loop faster.
+// Traversal variant of the render kernels: RT_TRAV=0..17 overrides the default (diagnostics).
+// Default (measured, profiles/r01_h_variants_sweep.txt, r01_o_wide_ifif_sweep.txt):
+//   <= 4096 records (Cornell, spheres, birthday): binary tree, while-while loop — incoherent bounce rays in an
+//      L1-resident tree;
+//   meshes up to 500 k records (bunny): 8-wide tree, per-lane if-if loop — 4-5 dependent steps instead of 12,
+//      +13 % over the binary if-if loop;
+//   larger (soups): binary tree, if-if loop at 64 registers — latency bound, 32 warps/SM beat fewer, fatter steps.
 int trav_variant(const rt_ctx *ctx) {
   const char *e = getenv("RT_TRAV");
-  int dflt = ctx->scene.n_recs <= 4096 ? 1 : 0;
+  int dflt = ctx->scene.n_recs <= 4096 ? 1 : (ctx->scene.n_recs < 500000 ? 17 : 0);
   int v = e ? atoi(e) : dflt;
-  return (v < 0 || v > 14) ? dflt : v;
+  return (v < 0 || v > 17) ? dflt : v;
 }
 
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
@@ -995,7 +1008,7 @@ extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t
                                        rt_hit *d_hits, void *stream) {
   int rc = check_ready(ctx, false, "rt_trace_closest");
   if (rc) return rc;
-  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 10)) {
+  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 11)) {
     set_error("rt_trace_closest: bad argument");
     return RT_ERR_INVALID;
   }
@@ -1148,7 +1161,35 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     else                                                                                               \
       k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);    \
     break;
-    if (trav == 14) {  // streaming kernel
+    if (trav >= 16) {  // fused kernel, per-lane if-if loop over the 4-wide (16) / 8-wide (17) tree
+#define RT_WIDE_IFIF_CASE(T)                                                                                     \
+  if (stats_on)                                                                                                  \
+    k_render_fused<true, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);                 \
+  else if (minb == 6)                                                                                            \
+    k_render_fused<false, T, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);             \
+  else if (minb == 8)                                                                                            \
+    k_render_fused<false, T, 8><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);             \
+  else                                                                                                           \
+    k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+      if (trav == 16) {
+        RT_WIDE_IFIF_CASE(16)
+      } else {
+        RT_WIDE_IFIF_CASE(17)
+      }
+#undef RT_WIDE_IFIF_CASE
+    } else if (trav == 15) {  // warp-synchronous kernel over the 4-wide tree
+#define RT_WARP4_CASE                                                                                            \
+  if (stats_on)                                                                                                  \
+    k_render_warp<true, 3, 5><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);               \
+  else if (minb == 6)                                                                                            \
+    k_render_warp<false, 3, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);              \
+  else if (minb == 8)                                                                                            \
+    k_render_warp<false, 3, 8><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);              \
+  else                                                                                                           \
+    k_render_warp<false, 3, 5><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+      RT_WARP4_CASE
+#undef RT_WARP4_CASE
+    } else if (trav == 14) {  // streaming kernel
       const char *e1 = getenv("RT_STREAM_LEAF"), *e2 = getenv("RT_STREAM_SHADE");
       const int leaf_min = e1 ? atoi(e1) : 8, shade_min = e2 ? atoi(e2) : 8;
       if (stats_on)
