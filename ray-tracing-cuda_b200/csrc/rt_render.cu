@@ -224,7 +224,9 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
     bool alive = depth < a.max_depth;  // ray_tracing.cu:23: the query at depth == limit yields 0
     if (alive) {
       Hit h;
-      if constexpr (TRAV >= 16)
+      if constexpr (TRAV >= 18)  // while-while over the 4-/8-wide tree, per lane
+        h = world_hit_wide<STATS, false, TRAV == 18 ? 4 : 8>(s, ray, true, 1e-3, (double)CUDART_INF_F, nullptr, &ts);
+      else if constexpr (TRAV >= 16)
         h = world_hit_wide_ifif<STATS, TRAV == 16 ? 4 : 8>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
       else
         h = world_hit_bvh<STATS, TRAV>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
@@ -975,16 +977,18 @@ inline int nblk(size_t n, int b) { return (int)((n + b - 1) / b); }
 
 // Traversal variant of the render kernels: RT_TRAV=0..17 overrides the default (diagnostics).
 // Default (measured, profiles/r01_h_variants_sweep.txt, r01_o_wide_ifif_sweep.txt):
-//   <= 4096 records (Cornell, spheres, birthday): binary tree, while-while loop — incoherent bounce rays in an
-//      L1-resident tree;
+//   <= 4096 records (spheres, birthday): binary tree, while-while loop — incoherent bounce rays in an
+//      L1-resident tree;  <= 64 records without spheres (Cornell): the same loop over the 4-wide tree, +4 %
+//      (with FP64 sphere tests in the loop the wide step spills at 80 registers and loses);
 //   meshes up to 500 k records (bunny): 8-wide tree, per-lane if-if loop — 4-5 dependent steps instead of 12,
 //      +13 % over the binary if-if loop;
 //   larger (soups): binary tree, if-if loop at 64 registers — latency bound, 32 warps/SM beat fewer, fatter steps.
 int trav_variant(const rt_ctx *ctx) {
   const char *e = getenv("RT_TRAV");
   int dflt = ctx->scene.n_recs <= 4096 ? 1 : (ctx->scene.n_recs < 500000 ? 17 : 0);
+  if (ctx->scene.n_recs <= 64 && !ctx->scene.has_spheres) dflt = 18;
   int v = e ? atoi(e) : dflt;
-  return (v < 0 || v > 17) ? dflt : v;
+  return (v < 0 || v > 19) ? dflt : v;
 }
 
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
@@ -1161,7 +1165,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     else                                                                                               \
       k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);    \
     break;
-    if (trav >= 16) {  // fused kernel, per-lane if-if loop over the 4-wide (16) / 8-wide (17) tree
+    if (trav >= 16) {  // fused kernel over the wide trees, per lane: if-if 4-wide (16) / 8-wide (17), while-while 4-wide (18) / 8-wide (19)
 #define RT_WIDE_IFIF_CASE(T)                                                                                     \
   if (stats_on)                                                                                                  \
     k_render_fused<true, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);                 \
@@ -1173,8 +1177,12 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
       if (trav == 16) {
         RT_WIDE_IFIF_CASE(16)
-      } else {
+      } else if (trav == 17) {
         RT_WIDE_IFIF_CASE(17)
+      } else if (trav == 18) {
+        RT_WIDE_IFIF_CASE(18)
+      } else {
+        RT_WIDE_IFIF_CASE(19)
       }
 #undef RT_WIDE_IFIF_CASE
     } else if (trav == 15) {  // warp-synchronous kernel over the 4-wide tree

@@ -204,14 +204,14 @@ def test_render_bit_exact_vs_oracle(ctx, name, hw, spp):
 
 @pytest.mark.parametrize("name,hw,spp", [("cornell_box", (72, 128), 8), ("spheres", (54, 96), 8), ("bunny9k", (54, 96), 4)])
 def test_render_kernel_variants_bit_exact(ctx, name, hw, spp, monkeypatch):
-    """Every fused-kernel variant (RT_TRAV 0..17; 5 = warp-scheduled vote kernel, 6..8 = pool kernel with 2..4 slots
+    """Every fused-kernel variant (RT_TRAV 0..19; 5 = warp-scheduled vote kernel, 6..8 = pool kernel with 2..4 slots
     per lane, 9..11 = warp-synchronous kernel: binary + cooperative record tests, 8-wide tree, 8-wide + cooperative, 12..13 = persistent kernel
-    without reconvergence at the query boundary over the binary / 8-wide tree, 14 = streaming kernel: single steps with deferred record tests and shading, 15 = 4-wide tree, 16/17 = fused kernel with the if-if loop over the 4-/8-wide tree)
+    without reconvergence at the query boundary over the binary / 8-wide tree, 14 = streaming kernel: single steps with deferred record tests and shading, 15 = 4-wide tree, 16/17 = fused kernel with the if-if loop over the 4-/8-wide tree, 18/19 = the same with the while-while loop)
     renders the oracle's image."""
     s, cam, o = _setup(ctx, name)
     H, W = hw
     want, cnt = o.render_product(H, W, 0, spp, 99)
-    for trav in range(18):
+    for trav in range(20):
         monkeypatch.setenv("RT_TRAV", str(trav))
         got, _, st = ctx.render_host(H, W, spp, seed=99, flags=abi.RT_RENDER_FUSED)
         assert (got.view(np.uint32) == want.view(np.uint32)).all(), trav
