@@ -204,7 +204,10 @@ __device__ __forceinline__ double rec_radius(float4 r1) {
 
 // sphere.cu:11-44 Sphere::Hit, decision part: the root the reference would return for an
 // unbounded t_to (near root if >= t_from, else far root), or false.
-__device__ __forceinline__ bool sphere_test(V3 c, double radius, const RayQ &r, double t_from, double *out_t) {
+#ifndef RT_SPHERE_INLINE
+#define RT_SPHERE_INLINE __forceinline__
+#endif
+static __device__ RT_SPHERE_INLINE bool sphere_test(V3 c, double radius, const RayQ &r, double t_from, double *out_t) {
   double len_d = (double)length(r.d);
   double a = len_d * len_d;
   V3 oc = r.o - c;
