@@ -438,21 +438,37 @@ __global__ void __launch_bounds__(128, MINB) k_render_persist(DScene s, DCamera 
 }
 
 // Out-of-line forms of the rare steps of the streaming kernel: the node step is the hot loop of a long query
-// and must not carry the registers (or the spills) of shading, camera sampling and the record tests.
-static __device__ __noinline__ bool shade_hit_call(const DScene &s, RayQ &ray, const Hit &h, const PathKey &pk, int depth,
-                                                   V3 &T, V3 &color) {
-  return shade_hit(s, ray, h, pk, depth, T, color);
+// and must not carry the registers (or the spills) of shading, camera sampling and the record tests.  Everything
+// goes in and out BY VALUE: a reference parameter would pin the traversal state of the hot loop in local memory.
+struct ShadeRet {
+  RayQ ray;
+  V3 T, color;
+  bool alive;
+};
+static __device__ __noinline__ ShadeRet shade_hit_call(const DScene &s, RayQ ray, Hit h, PathKey pk, int depth, V3 T,
+                                                       V3 color) {
+  ShadeRet r;
+  r.alive = shade_hit(s, ray, h, pk, depth, T, color);
+  r.ray = ray;
+  r.T = T;
+  r.color = color;
+  return r;
 }
 static __device__ __noinline__ RayQ camera_sample_call(const DCamera &cam, int i, int j, int height, int width,
-                                                       const PathKey &pk) {
+                                                       PathKey pk) {
   return camera_sample(cam, i, j, height, width, pk);
 }
-static __device__ __noinline__ int trav_leaf_step_call(const DScene &s, Trav &tv, const Range &rg, const uint2 *stack) {
-  return trav_leaf_step(s, tv, rg, stack);
+struct LeafRet {
+  Trav tv;
+  int state;
+};
+static __device__ __noinline__ LeafRet trav_leaf_step_call(const DScene &s, Trav tv, Range rg, const uint2 *stack) {
+  LeafRet r;
+  r.state = trav_leaf_step(s, tv, rg, stack);
+  r.tv = tv;
+  return r;
 }
-static __device__ __noinline__ Hit trav_finish_call(const DScene &s, const Trav &tv, const Range &rg) {
-  return trav_finish(s, tv, rg);
-}
+static __device__ __noinline__ Hit trav_finish_call(const DScene &s, Trav tv, Range rg) { return trav_finish(s, tv, rg); }
 
 // ---- streaming kernel: single steps, deferred minority work -----------------------------------------------
 // For scenes whose queries are long (hundreds of node steps: the 1M-10M triangle soups) the per-lane loops leave
@@ -510,7 +526,14 @@ __global__ void __launch_bounds__(128, MINB) k_render_stream(DScene s, DCamera c
       if (have_query) {
         Hit h = trav_finish_call(s, tv, rg);
         n_rays++;
-        const bool alive = h.rec != REC_NONE && shade_hit_call(s, tv.r, h, pk, depth, T, color);
+        bool alive = false;
+        if (h.rec != REC_NONE) {
+          ShadeRet sr = shade_hit_call(s, tv.r, h, pk, depth, T, color);
+          alive = sr.alive;
+          tv.r = sr.ray;
+          T = sr.T;
+          color = sr.color;
+        }
         if (alive) {
           depth++;
         } else {
@@ -546,7 +569,9 @@ __global__ void __launch_bounds__(128, MINB) k_render_stream(DScene s, DCamera c
       }
     } else if (do_leaf && state == ST_LEAF) {
       if (STATS) n_prims++;
-      state = trav_leaf_step_call(s, tv, rg, stack);
+      LeafRet lr = trav_leaf_step_call(s, tv, rg, stack);
+      tv = lr.tv;
+      state = lr.state;
     } else if (state == ST_NODE) {
       if (STATS) n_nodes += 2;
       state = trav_node_step(s, tv, stack);
