@@ -185,6 +185,39 @@ __device__ __forceinline__ void flush_counters(RenderCounters *ctr, unsigned lon
   }
 }
 
+// Out-of-line forms of the rare steps (streaming kernel; fused kernel at 64 registers): the node step is the hot loop of a long query
+// and must not carry the registers (or the spills) of shading, camera sampling and the record tests.  Everything
+// goes in and out BY VALUE: a reference parameter would pin the traversal state of the hot loop in local memory.
+struct ShadeRet {
+  RayQ ray;
+  V3 T, color;
+  bool alive;
+};
+static __device__ __noinline__ ShadeRet shade_hit_call(const DScene &s, RayQ ray, Hit h, PathKey pk, int depth, V3 T,
+                                                       V3 color) {
+  ShadeRet r;
+  r.alive = shade_hit(s, ray, h, pk, depth, T, color);
+  r.ray = ray;
+  r.T = T;
+  r.color = color;
+  return r;
+}
+static __device__ __noinline__ RayQ camera_sample_call(const DCamera &cam, int i, int j, int height, int width,
+                                                       PathKey pk) {
+  return camera_sample(cam, i, j, height, width, pk);
+}
+struct LeafRet {
+  Trav tv;
+  int state;
+};
+static __device__ __noinline__ LeafRet trav_leaf_step_call(const DScene &s, Trav tv, Range rg, const uint2 *stack) {
+  LeafRet r;
+  r.state = trav_leaf_step(s, tv, rg, stack);
+  r.tv = tv;
+  return r;
+}
+static __device__ __noinline__ Hit trav_finish_call(const DScene &s, Trav tv, Range rg) { return trav_finish(s, tv, rg); }
+
 // ---- fused kernel: one thread per pixel, paths regenerated in registers ---------------------------
 // Each lane runs its pixel's samples in increasing order and starts the next sample the moment the
 // current path ends, so a warp stays full until its pixels run out of samples.  No queue traffic.
@@ -214,7 +247,10 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
     if (need_new) {
       if (k >= a.spp_end) break;
       pk.sample = (uint32_t)k;
-      ray = camera_sample(cam, i, j, a.height, a.width, pk);
+      if constexpr (MINB >= 8)  // 64 registers: keep camera sampling and shading out of the traversal loop's budget
+        ray = camera_sample_call(cam, i, j, a.height, a.width, pk);
+      else
+        ray = camera_sample(cam, i, j, a.height, a.width, pk);
       T = mk(1.f, 1.f, 1.f);
       depth = 0;
       need_new = false;
@@ -236,7 +272,18 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
         n_prims += ts.prims;
         ts.nodes = ts.prims = 0;
       }
-      alive = h.rec != REC_NONE && shade_hit(s, ray, h, pk, depth, T, color);
+      if constexpr (MINB >= 8) {
+        alive = false;
+        if (h.rec != REC_NONE) {
+          ShadeRet sr = shade_hit_call(s, ray, h, pk, depth, T, color);
+          alive = sr.alive;
+          ray = sr.ray;
+          T = sr.T;
+          color = sr.color;
+        }
+      } else {
+        alive = h.rec != REC_NONE && shade_hit(s, ray, h, pk, depth, T, color);
+      }
     }
     if (alive) {
       depth++;
@@ -436,39 +483,6 @@ __global__ void __launch_bounds__(128, MINB) k_render_persist(DScene s, DCamera 
   }
   flush_counters(ctr, n_samples, n_rays, n_rays_ref, STATS ? ts.nodes : 0, STATS ? ts.prims : 0);
 }
-
-// Out-of-line forms of the rare steps of the streaming kernel: the node step is the hot loop of a long query
-// and must not carry the registers (or the spills) of shading, camera sampling and the record tests.  Everything
-// goes in and out BY VALUE: a reference parameter would pin the traversal state of the hot loop in local memory.
-struct ShadeRet {
-  RayQ ray;
-  V3 T, color;
-  bool alive;
-};
-static __device__ __noinline__ ShadeRet shade_hit_call(const DScene &s, RayQ ray, Hit h, PathKey pk, int depth, V3 T,
-                                                       V3 color) {
-  ShadeRet r;
-  r.alive = shade_hit(s, ray, h, pk, depth, T, color);
-  r.ray = ray;
-  r.T = T;
-  r.color = color;
-  return r;
-}
-static __device__ __noinline__ RayQ camera_sample_call(const DCamera &cam, int i, int j, int height, int width,
-                                                       PathKey pk) {
-  return camera_sample(cam, i, j, height, width, pk);
-}
-struct LeafRet {
-  Trav tv;
-  int state;
-};
-static __device__ __noinline__ LeafRet trav_leaf_step_call(const DScene &s, Trav tv, Range rg, const uint2 *stack) {
-  LeafRet r;
-  r.state = trav_leaf_step(s, tv, rg, stack);
-  r.tv = tv;
-  return r;
-}
-static __device__ __noinline__ Hit trav_finish_call(const DScene &s, Trav tv, Range rg) { return trav_finish(s, tv, rg); }
 
 // ---- streaming kernel: single steps, deferred minority work -----------------------------------------------
 // For scenes whose queries are long (hundreds of node steps: the 1M-10M triangle soups) the per-lane loops leave
