@@ -236,6 +236,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cornell_box", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override spp (diagnostic; the headline uses the config's)")
+    ap.add_argument("--depth", type=int, default=0,
+                    help="bounce limit (default 10 = the reference's TRACE_DEPTH_LIMIT, ray_tracing.cu:10; BASELINE config 1 "
+                         "also names depth 50: --workload spheres --depth 50)")
     ap.add_argument("--strategy", default="auto", choices=["auto", "fused", "wavefront"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -256,6 +259,7 @@ def main():
     name, H, W, spp = WORKLOADS[args.workload]
     if args.spp:
         spp = args.spp
+    MAX_DEPTH = args.depth if args.depth > 0 else globals()["MAX_DEPTH"]
     scene, camspec = rt.scenes.by_name(name)
     ctx = rt.Context(local)
     camera = rt.core.camera_look_at(camspec)
