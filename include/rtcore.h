@@ -205,7 +205,8 @@ enum {
   RT_RENDER_CLEAR = 1,     /* zero the accumulation buffer first */
   RT_RENDER_PROFILE = 2,   /* per-stage event timing (serialises stages) */
   RT_RENDER_FUSED = 4,     /* force the fused persistent-path kernel (paths regenerated in registers) */
-  RT_RENDER_NO_SORT = 8,   /* wavefront: single shade queue instead of material-sorted queues */
+  RT_RENDER_SORT = 8,      /* wavefront: material-sorted shade queues (one Scatter/Emit body per warp) instead of one queue;
+                              same sums, measured 6-9 % slower (profiles/r01_t_wavefront_sorted_queues.txt) */
   RT_RENDER_WAVEFRONT = 16 /* force the wavefront pipeline (logic/shade -> extend over compacted queues) */
 };
 

@@ -13,7 +13,7 @@ RT_HIT_SPHERE, RT_HIT_TRIANGLE, RT_HIT_PARALLELOGRAM, RT_HIT_SKY, RT_HIT_MESH = 
 RT_RENDER_CLEAR = 1
 RT_RENDER_PROFILE = 2
 RT_RENDER_FUSED = 4
-RT_RENDER_NO_SORT = 8
+RT_RENDER_SORT = 8
 RT_RENDER_WAVEFRONT = 16
 
 material_dtype = np.dtype(

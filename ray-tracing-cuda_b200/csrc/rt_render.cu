@@ -855,8 +855,26 @@ struct WfState {
   float4 *thr;     // T.xyz, w = depth | flags
   float4 *color;   // colour sum of the pixel, w = current sample index
   uint32_t *queue[2];
-  uint32_t *count;  // [2] queue lengths, ping-pong
+  uint32_t *count;   // [2] queue lengths, ping-pong
+  uint32_t *mqueue;  // material-sorted shade queues: WF_CLASSES segments of n_slots entries (null: unsorted)
+  uint32_t *mcount;  // [2][WF_CLASSES] lengths, ping-pong with `count`
+  uint32_t n_slots;
 };
+// Shade classes: the five material types (RT_MAT_*) and "no hit".  A warp of the sorted logic pass runs one
+// Material::Scatter / Emit body instead of a mixture (north_star (3): material-sorted shading queues).
+constexpr int WF_CLASSES = 6;
+__device__ __forceinline__ int shade_class(const DScene &s, const Hit &h) {
+  if (h.rec == REC_NONE) return 5;
+  int mat_id;
+  if (h.rec == REC_SKY) {
+    mat_id = s.sky_mat;
+  } else {
+    const float4 *recs = h.seq ? s.recs_seq : s.recs;
+    mat_id = (int)(__float_as_uint(__ldg(recs + 3 * (size_t)h.rec + 2).w) >> KIND_BITS);
+  }
+  int t = __float_as_int(__ldg(reinterpret_cast<const float4 *>(s.mats + mat_id) + 1).x);
+  return (t < 0 || t > 4) ? 5 : t;
+}
 constexpr int WF_DONE = 1 << 30, WF_NEW = 1 << 29;
 
 __device__ __forceinline__ int hit_encode(const Hit &h) { return (h.rec < 0) ? h.rec : (h.seq ? (h.rec | 0x40000000) : h.rec); }
@@ -891,9 +909,36 @@ __global__ void __launch_bounds__(256) k_wf_logic(DScene s, DCamera cam, RenderA
   const int n_slots = a.height * a.width;
   const uint32_t n_in = FIRST ? (uint32_t)n_slots : w.count[qi];
   unsigned long long n_samples = 0, n_rays_ref = 0;
-  for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < ((n_in + 31u) & ~31u); q += gridDim.x * blockDim.x) {
+  // sorted input: position q of the concatenated class queues (each class padded to a warp boundary, so that no
+  // warp mixes two classes)
+  uint32_t mend[WF_CLASSES], mtotal = 0;
+  const bool sorted = !FIRST && w.mqueue != nullptr;
+  const uint32_t *mc = w.mcount + qi * WF_CLASSES;
+  if (sorted) {
+#pragma unroll
+    for (int c = 0; c < WF_CLASSES; c++) {
+      mtotal += (mc[c] + 31u) & ~31u;
+      mend[c] = mtotal;
+    }
+  }
+  const uint32_t n_iter = sorted ? mtotal : ((n_in + 31u) & ~31u);
+  for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < n_iter; q += gridDim.x * blockDim.x) {
     bool valid = q < n_in;
-    uint32_t slot = valid ? (FIRST ? q : w.queue[qi][q]) : 0;
+    uint32_t slot = 0;
+    if (sorted) {
+      int c = 0;
+      uint32_t begin = 0;
+#pragma unroll
+      for (int k = 0; k < WF_CLASSES - 1; k++)
+        if (q >= mend[k]) {
+          c = k + 1;
+          begin = mend[k];
+        }
+      valid = q - begin < mc[c];
+      if (valid) slot = w.mqueue[(size_t)c * w.n_slots + (q - begin)];
+    } else if (valid) {
+      slot = FIRST ? q : w.queue[qi][q];
+    }
     bool push = false;
     if (valid) {
       const int i = slot / a.width, j = slot % a.width;
@@ -983,6 +1028,15 @@ __global__ void __launch_bounds__(128, MINB) k_wf_extend(DScene s, WfState w, in
     // only the two .w words change: t and the record
     reinterpret_cast<float *>(w.ray_o + slot)[3] = float(h.t);
     reinterpret_cast<int *>(w.ray_d + slot)[3] = hit_encode(h);
+    if (w.mqueue) {  // one warp-aggregated push per class present in the warp
+      const int c = shade_class(s, h);
+      const unsigned peers = __match_any_sync(__activemask(), c);
+      const int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
+      uint32_t base = 0;
+      if (lane == leader) base = atomicAdd(w.mcount + qi * WF_CLASSES + c, (uint32_t)__popc(peers));
+      base = __shfl_sync(peers, base, leader);
+      w.mqueue[(size_t)c * w.n_slots + base + __popc(peers & ((1u << lane) - 1))] = slot;
+    }
   }
   if (STATS) {
     n_nodes = ts.nodes;
@@ -991,7 +1045,10 @@ __global__ void __launch_bounds__(128, MINB) k_wf_extend(DScene s, WfState w, in
   flush_counters(ctr, 0, n_rays, 0, n_nodes, n_prims);
 }
 
-__global__ void k_wf_reset(uint32_t *count, int which) { count[which] = 0; }
+__global__ void k_wf_reset(uint32_t *count, int which, uint32_t *mcount) {
+  if (threadIdx.x == 0) count[which] = 0;
+  if (threadIdx.x < WF_CLASSES) mcount[which * WF_CLASSES + threadIdx.x] = 0;
+}
 
 // ---- resolve: ray_tracing.cu:78-83 + WriteImage's *255 truncation (utils.cu:87-96) ---------------
 __global__ void k_resolve(const float *__restrict__ accum, int64_t n, int spp_total, float *rgb, uint8_t *rgb8) {
@@ -1100,8 +1157,8 @@ extern "C" int rt_primary_rays_host(rt_ctx *ctx, int height, int width, float *h
   return RT_OK;
 }
 
-static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, float *d_accum, RenderCounters *ctr,
-                            cudaStream_t st, uint32_t *iterations, uint32_t *launches) {
+static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, bool sort, float *d_accum,
+                            RenderCounters *ctr, cudaStream_t st, uint32_t *iterations, uint32_t *launches) {
   size_t n = (size_t)a.height * a.width;
   for (int i = 0; i < 4; i++) RT_CUDA(ctx->wf[i].reserve(n * 16));
   RT_CUDA(ctx->wf[4].reserve(n * 4));
@@ -1115,12 +1172,19 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, flo
   w.queue[0] = ctx->wf[4].as<uint32_t>();
   w.queue[1] = ctx->wf[5].as<uint32_t>();
   w.count = ctx->wf[6].as<uint32_t>();
+  w.n_slots = (uint32_t)n;
+  w.mqueue = nullptr;
+  w.mcount = w.count + 4;
+  if (sort) {
+    RT_CUDA(ctx->wf[7].reserve(n * 4 * WF_CLASSES));
+    w.mqueue = ctx->wf[7].as<uint32_t>();
+  }
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
   // resident blocks per SM the extend kernel is compiled for: long, latency-bound queries want warps, not registers
   const char *wmb = getenv("RT_WF_MINB");
   const int wf_minb = wmb ? atoi(wmb) : (ctx->scene.n_recs >= 500000 ? 10 : 5);
-  RT_CUDA(cudaMemsetAsync(w.count, 0, 8, st));
+  RT_CUDA(cudaMemsetAsync(w.count, 0, 64, st));
   // first logic pass reads no queue and fills queue 1
   int qi = 0;
   k_wf_logic<true><<<std::min(nblk(n, 256), sms * 8), 256, 0, st>>>(ctx->scene, ctx->camera, a, w, qi, d_accum, ctr);
@@ -1142,8 +1206,10 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, flo
       k_wf_extend<false, RT_DEFAULT_TRAV, 8><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
     else
       k_wf_extend<false, RT_DEFAULT_TRAV><<<gb, 128, 0, st>>>(ctx->scene, w, qi, ctr);
-    k_wf_reset<<<1, 1, 0, st>>>(w.count, qi ^ 1);
-    k_wf_logic<false><<<std::min(nblk(live, 256), sms * 8), 256, 0, st>>>(ctx->scene, ctx->camera, a, w, qi, d_accum, ctr);
+    k_wf_reset<<<1, 32, 0, st>>>(w.count, qi ^ 1, w.mcount);
+    // sorted: up to WF_CLASSES * 31 padding slots on top of `live`
+    k_wf_logic<false><<<std::min(nblk(live + 32 * WF_CLASSES, 256), sms * 8), 256, 0, st>>>(ctx->scene, ctx->camera, a, w, qi,
+                                                                                          d_accum, ctr);
     *launches += 3;
     *iterations += 1;
     qi ^= 1;
@@ -1316,7 +1382,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     launches = 1;
     iterations = 1;
   } else {
-    rc = render_wavefront(ctx, a, stats_on, d_accum_rgb, ctr, st, &iterations, &launches);
+    rc = render_wavefront(ctx, a, stats_on, (p->flags & RT_RENDER_SORT) != 0, d_accum_rgb, ctr, st, &iterations, &launches);
     if (rc) return rc;
   }
   RT_CUDA(cudaEventRecord(ctx->ev1, st));

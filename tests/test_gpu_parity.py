@@ -186,7 +186,8 @@ def test_render_bit_exact_vs_oracle(ctx, name, hw, spp):
     s, cam, o = _setup(ctx, name)
     H, W = hw
     want, cnt = o.render_product(H, W, 0, spp, 1234)
-    for flags in (abi.RT_RENDER_FUSED, abi.RT_RENDER_WAVEFRONT):
+    # wavefront: the single shade queue (default) and material-sorted queues (SORT) give the same sums
+    for flags in (abi.RT_RENDER_FUSED, abi.RT_RENDER_WAVEFRONT, abi.RT_RENDER_WAVEFRONT | abi.RT_RENDER_SORT):
         got, _, st = ctx.render_host(H, W, spp, seed=1234, flags=flags)
         diff = np.nonzero((got.view(np.uint32) != want.view(np.uint32)).any(axis=2))
         assert len(diff[0]) == 0, (flags, len(diff[0]), got[diff][:3], want[diff][:3])

@@ -26,7 +26,8 @@ def main():
     ap.add_argument("--env", default="", help="extra VAR=a|b|c axis")
     a = ap.parse_args()
     ctx = rt.Context(0)
-    flags = rt.abi.RT_RENDER_FUSED if a.strategy == "fused" else rt.abi.RT_RENDER_WAVEFRONT
+    flags = {"fused": rt.abi.RT_RENDER_FUSED, "wavefront": rt.abi.RT_RENDER_WAVEFRONT,
+             "wavefront_sorted": rt.abi.RT_RENDER_WAVEFRONT | rt.abi.RT_RENDER_SORT}[a.strategy]
     extra = [None]
     if a.env:
         var, vals = a.env.split("=")
