@@ -718,6 +718,13 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   s.sky_obj = sky_obj;
   s.sky_mat = sky_mat;
   s.has_spheres = n_spheres > 0;
+  // box list for the flat traversal (rt_flat.cuh): the single-primitive leaf nodes k_emit wrote
+  ctx->flat.n = 0;
+  if (n_bp > 0 && n_bp <= FLAT_MAX) {
+    RT_CUDA(cudaMemcpy(ctx->flat.box, ctx->nodes.as<float4>() + 2 * (size_t)(n_bp - 1), (size_t)n_bp * 32,
+                       cudaMemcpyDeviceToHost));
+    ctx->flat.n = n_bp;
+  }
   ctx->has_scene = true;
 
   rt_build_stats &bs = ctx->build_stats;

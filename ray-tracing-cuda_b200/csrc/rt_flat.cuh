@@ -1,0 +1,129 @@
+// rt_flat.cuh — box-list closest hit for scenes of at most FLAT_MAX primitives (Cornell box: 18 parallelograms).
+//
+// On such scenes a tree does not pay: profiles/r01_q_cornell_fused_ncu_summary.txt shows 47 % of the warp instructions
+// of the 4-wide while-while loop in node stepping (stack, leaf detection, child ordering) at 10 of 32 lanes, for 13 box
+// tests per ray.  Here every lane tests ALL primitive boxes in one uniform loop (the boxes are a kernel parameter, i.e.
+// constant-bank operands: no loads, no divergence, 32 of 32 lanes), keeps the hits as a bit mask, runs the record
+// tests of the NEAREST box first, and then walks the remaining mask bits, re-testing each box against the closest hit
+// found so far before its records are tested.  Record tests, tie rules and the fallback are those of the tree loops
+// (rec_test / best_offer are order independent): identical hits.
+//
+// The boxes are the single-primitive leaf nodes the LBVH builder writes (rt_build.cu k_emit: nodes[n_bp-1 .. 2n_bp-2],
+// padded by k_bp_bounds), copied to the host at commit time.
+#pragma once
+#include "rt_device.cuh"
+
+namespace rtc {
+
+constexpr int FLAT_MAX = 32;
+
+struct FlatItems {
+  float4 box[2 * FLAT_MAX];  // {lo.xyz, first record}, {hi.xyz, LEAF_FLAG | record count}
+  int32_t n;                 // 0: no box list for this scene
+  int32_t pad[3];
+};
+struct FlatNone {};
+template <bool ON>
+struct FlatParamT {
+  using type = FlatNone;
+};
+template <>
+struct FlatParamT<true> {
+  using type = FlatItems;
+};
+
+#define RT_FLAT_SLAB(LO, HI, T_HI, TN, TF)                                                       \
+  {                                                                                              \
+    const float ax_ = __fmaf_rn((LO).x, idx, nox), bx_ = __fmaf_rn((HI).x, idx, nox);            \
+    const float ay_ = __fmaf_rn((LO).y, idy, noy), by_ = __fmaf_rn((HI).y, idy, noy);            \
+    const float az_ = __fmaf_rn((LO).z, idz, noz), bz_ = __fmaf_rn((HI).z, idz, noz);            \
+    TN = fmaxf(fmaxf(fminf(ax_, bx_), fminf(ay_, by_)), fmaxf(fminf(az_, bz_), t_lo));           \
+    TF = fminf(fminf(fmaxf(ax_, bx_), fmaxf(ay_, by_)), fminf(fmaxf(az_, bz_), T_HI));           \
+  }
+
+template <bool STATS>
+__device__ __forceinline__ Hit world_hit_flat(const DScene &s, const FlatItems &fl, const RayQ &r, double t_from,
+                                              double t_to, TravStats *st) {
+  Range rg;
+  rg.t_from = t_from;
+  rg.t_to = t_to;
+  rg.tf_f = float_ge(t_from);
+  Best b;
+  best_init(b, t_to);
+  if (s.sky_obj >= 0) {  // sky.cu:18-27: always a candidate at t = 1e9
+    double t = 1e9;
+    if (t_from <= t && t <= t_to) {
+      b.t = t;
+      b.t_f = 1e9f;
+      b.rec = REC_SKY;
+      b.obj = s.sky_obj;
+      b.sub = 0;
+    }
+  }
+  bool ambiguous = false;
+  const int n = fl.n;
+  if (n > 0) {
+    const float idx = slab_rcp(r.d.x), idy = slab_rcp(r.d.y), idz = slab_rcp(r.d.z);
+    const float nox = -(r.o.x * idx), noy = -(r.o.y * idy), noz = -(r.o.z * idz);
+    const float t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
+    const float t_hi0 = b.t_f + fabsf(b.t_f) * 1e-5f;
+    // ---- all boxes, uniformly: hit mask + nearest entry
+    uint32_t mask = 0;
+    float tn_min = CUDART_INF_F;
+    int j = -1;
+#pragma unroll 2
+    for (int c = 0; c < n; c++) {
+      const float4 lo = fl.box[2 * c], hi = fl.box[2 * c + 1];
+      float tn, tf;
+      RT_FLAT_SLAB(lo, hi, t_hi0, tn, tf)
+      const bool hit = tn <= tf * 1.00001f;
+      mask |= hit ? (1u << c) : 0u;
+      const bool nearer = hit && tn < tn_min;
+      tn_min = nearer ? tn : tn_min;
+      j = nearer ? c : j;
+    }
+    if (STATS) st->nodes += n;
+    if (j >= 0) mask &= ~(1u << j);
+    // ---- candidates: nearest box first, then the mask in index order with a re-test against the closest hit
+    const float4 *__restrict__ leaf = s.nodes + 2 * (size_t)(n - 1);
+    uint32_t w_first = 0, w_count = 0;
+    if (j >= 0) {
+      w_first = __float_as_uint(__ldg(leaf + 2 * j).w);
+      w_count = __float_as_uint(__ldg(leaf + 2 * j + 1).w) & ~LEAF_FLAG;
+    }
+    while (j >= 0) {
+      int k = (int)w_first;
+      const int end = k + (int)w_count;
+      while (k < end) {
+        int used = rec_test(s.recs, k, r, rg, b, ambiguous);
+        if (STATS) st->prims += used;
+        k += used;
+      }
+      const float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
+      j = -1;
+      while (mask) {
+        const int c = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const float4 lo = __ldg(leaf + 2 * c), hi = __ldg(leaf + 2 * c + 1);
+        float tn, tf;
+        RT_FLAT_SLAB(lo, hi, t_hi, tn, tf)
+        if (STATS) st->nodes += 1;
+        if (tn <= tf * 1.00001f) {
+          j = c;
+          w_first = __float_as_uint(lo.w);
+          w_count = __float_as_uint(hi.w) & ~LEAF_FLAG;
+          break;
+        }
+      }
+    }
+  }
+  if (ambiguous) return world_hit_seq(s, r, t_from, t_to);
+  Hit h;
+  h.t = b.rec == REC_NONE ? 0.0 : b.t;
+  h.rec = b.rec;
+  h.seq = 0;
+  return h;
+}
+#undef RT_FLAT_SLAB
+
+}  // namespace rtc

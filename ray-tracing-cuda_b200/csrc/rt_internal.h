@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "rt_device.cuh"
+#include "rt_flat.cuh"
 
 namespace rtc {
 
@@ -53,6 +54,7 @@ struct rt_ctx {
   bool has_scene = false, has_camera = false;
   rtc::DScene scene{};
   rtc::DCamera camera{};
+  rtc::FlatItems flat{};  // box list of scenes with <= FLAT_MAX primitives (flat.n = 0: none)
   rt_camera camera_host{};
   // scene storage
   rtc::DevBuf nodes, wnodes, wnodes4, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;

@@ -77,6 +77,18 @@ __global__ void __launch_bounds__(128) k_trace_closest_warp(DScene s, const floa
   if (active) out[i] = make_rt_hit(s, r, h);
 }
 
+// Parity hook of the box-list traversal (mode 12; scenes with at most FLAT_MAX primitives).
+__global__ void __launch_bounds__(128) k_trace_closest_flat(DScene s, FlatItems fl, const float *__restrict__ rays, int64_t n,
+                                                            double t_from, double t_to, rt_hit *out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  RayQ r;
+  r.o = mk(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]);
+  r.d = mk(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]);
+  Hit h = world_hit_flat<false>(s, fl, r, t_from, t_to, nullptr);
+  out[i] = make_rt_hit(s, r, h);
+}
+
 // ---- parity hook: HitableList::Hit on explicit rays ------------------------------------------------
 __global__ void __launch_bounds__(128) k_trace_closest(DScene s, const float *__restrict__ rays, int64_t n,
                                                        double t_from, double t_to, int mode, rt_hit *out) {
@@ -223,7 +235,8 @@ static __device__ __noinline__ Hit trav_finish_call(const DScene &s, Trav tv, Ra
 // current path ends, so a warp stays full until its pixels run out of samples.  No queue traffic.
 template <bool STATS, int TRAV, int MINB = 5>
 __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera cam, RenderArgs a, float *__restrict__ accum,
-                                                      RenderCounters *ctr) {
+                                                      RenderCounters *ctr,
+                                                      typename FlatParamT<TRAV == 20>::type fl = {}) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
   const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -260,7 +273,9 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
     bool alive = depth < a.max_depth;  // ray_tracing.cu:23: the query at depth == limit yields 0
     if (alive) {
       Hit h;
-      if constexpr (TRAV >= 18)  // while-while over the 4-/8-wide tree, per lane
+      if constexpr (TRAV == 20)  // box list (<= 32 primitives)
+        h = world_hit_flat<STATS>(s, fl, ray, 1e-3, (double)CUDART_INF_F, &ts);
+      else if constexpr (TRAV >= 18)  // while-while over the 4-/8-wide tree, per lane
         h = world_hit_wide<STATS, false, TRAV == 18 ? 4 : 8>(s, ray, true, 1e-3, (double)CUDART_INF_F, nullptr, &ts);
       else if constexpr (TRAV >= 16)
         h = world_hit_wide_ifif<STATS, TRAV == 16 ? 4 : 8>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
@@ -1071,8 +1086,9 @@ using namespace rtc;
 namespace {
 inline int nblk(size_t n, int b) { return (int)((n + b - 1) / b); }
 
-// Traversal variant of the render kernels: RT_TRAV=0..17 overrides the default (diagnostics).
-// Default (measured, profiles/r01_h_variants_sweep.txt, r01_o_wide_ifif_sweep.txt):
+// Traversal variant of the render kernels: RT_TRAV=0..20 overrides the default (diagnostics).
+// Default (measured, profiles/r01_h_variants_sweep.txt, r01_o_wide_ifif_sweep.txt, r01_v_box_list_sweep.txt):
+//   <= 32 primitives (Cornell, birthday): no tree — box list, every lane tests every box (rt_flat.cuh);
 //   <= 4096 records (spheres, birthday): binary tree, while-while loop — incoherent bounce rays in an
 //      L1-resident tree;  <= 64 records without spheres (Cornell): the same loop over the 4-wide tree, +4 %
 //      (with FP64 sphere tests in the loop the wide step spills at 80 registers and loses);
@@ -1083,8 +1099,10 @@ int trav_variant(const rt_ctx *ctx) {
   const char *e = getenv("RT_TRAV");
   int dflt = ctx->scene.n_recs <= 4096 ? 1 : (ctx->scene.n_recs < 500000 ? 17 : 0);
   if (ctx->scene.n_recs <= 64 && !ctx->scene.has_spheres) dflt = 18;
+  if (ctx->flat.n > 0) dflt = 20;  // <= 32 primitives: box list (rt_flat.cuh), +37 % on Cornell, +20 % on birthday
   int v = e ? atoi(e) : dflt;
-  return (v < 0 || v > 19) ? dflt : v;
+  if (v == 20 && ctx->flat.n == 0) v = dflt;  // no box list for this scene
+  return (v < 0 || v > 20) ? dflt : v;
 }
 
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
@@ -1108,13 +1126,20 @@ extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t
                                        rt_hit *d_hits, void *stream) {
   int rc = check_ready(ctx, false, "rt_trace_closest");
   if (rc) return rc;
-  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 11)) {
+  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 12)) {
     set_error("rt_trace_closest: bad argument");
     return RT_ERR_INVALID;
   }
   if (n == 0) return RT_OK;
   RT_CUDA(cudaSetDevice(ctx->device));
-  if (mode >= 8)
+  if (mode == 12 && ctx->flat.n == 0 && ctx->scene.n_recs > 0) {
+    set_error("rt_trace_closest: mode 12 (box list) needs a scene of at most 32 primitives");
+    return RT_ERR_INVALID;
+  }
+  if (mode == 12)
+    k_trace_closest_flat<<<nblk((size_t)n, 128), 128, 0, (cudaStream_t)stream>>>(ctx->scene, ctx->flat, d_rays, n, t_from,
+                                                                                 t_to, d_hits);
+  else if (mode >= 8)
     k_trace_closest_warp<<<nblk((size_t)n, 128), 128, 0, (cudaStream_t)stream>>>(ctx->scene, d_rays, n, t_from, t_to,
                                                                                  mode, d_hits);
   else
@@ -1270,7 +1295,16 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     else                                                                                               \
       k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);    \
     break;
-    if (trav >= 16) {  // fused kernel over the wide trees, per lane: if-if 4-wide (16) / 8-wide (17), while-while 4-wide (18) / 8-wide (19)
+    if (trav == 20) {  // box list
+      if (stats_on)
+        k_render_fused<true, 20><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr, ctx->flat);
+      else if (minb == 6)
+        k_render_fused<false, 20, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr, ctx->flat);
+      else if (minb == 8)
+        k_render_fused<false, 20, 8><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr, ctx->flat);
+      else
+        k_render_fused<false, 20><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr, ctx->flat);
+    } else if (trav >= 16) {  // fused kernel over the wide trees, per lane: if-if 4-wide (16) / 8-wide (17), while-while 4-wide (18) / 8-wide (19)
 #define RT_WIDE_IFIF_CASE(T)                                                                                     \
   if (stats_on)                                                                                                  \
     k_render_fused<true, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);                 \

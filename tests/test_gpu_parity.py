@@ -126,6 +126,50 @@ def test_traversal_variants_identical(ctx, name):
         assert len(bad) == 0, (mode, len(bad), got[bad[:3]], want[bad[:3]])
 
 
+@pytest.mark.parametrize("name", ["cornell_box", "birthday", "mixed30"])
+def test_box_list_traversal(ctx, name):
+    """Mode 12: the box-list traversal of scenes with at most 32 primitives (every box tested by every lane, nearest
+    box first, the rest re-tested against the closest hit) returns the oracle's hits on random, primary and
+    degenerate rays; larger scenes refuse the mode."""
+    if name == "mixed30":
+        rng = np.random.RandomState(8)
+        mats = [scenes._mat(abi.RT_MAT_LAMBERTIAN, (0.5, 0.5, 0.5)), scenes._mat(abi.RT_MAT_METAL, (0.7, 0.6, 0.5), fuzz=0.3),
+                scenes._mat(abi.RT_MAT_SKY)]
+        hs = []
+        for i in range(30):
+            k = i % 3
+            if k == 0:
+                hs.append(scenes._hit(abi.RT_HIT_SPHERE, i % 2, [rng.uniform(-3, 3, 3)], radius=float(rng.uniform(0.1, 1.0))))
+            elif k == 1:
+                hs.append(scenes._hit(abi.RT_HIT_TRIANGLE, i % 2, rng.uniform(-3, 3, (3, 3))))
+            else:
+                hs.append(scenes.parallelogram(rng.uniform(-3, 3, (3, 3)), i % 2))
+        hs.append(scenes._hit(abi.RT_HIT_SKY, 2))
+        s = abi.SceneData(np.stack(hs), np.stack(mats))
+        ctx.commit(s)
+        o = ck.OracleScene(s)
+        lo, hi, fields = -4, 4, ("t", "obj", "sub", "normal", "material")
+        rr = ck.random_rays(40000, 5, lo, hi)
+    else:
+        s, cam, o = _setup(ctx, name)
+        lo, hi = _BOX[name]
+        fields = _fields(name)
+        rr = np.concatenate([ctx.primary_rays(54, 96), ck.random_rays(40000, 5, lo, hi)])
+    rr = np.concatenate([rr, ck.degenerate_rays(20000, 34, lo, hi)])
+    want = o.trace(rr, quirks=0)
+    got = ctx.trace_closest(rr, mode=12)
+    bad = ck.hits_equal(got, want, fields)
+    assert len(bad) == 0, (len(bad), rr[bad[:3]], got[bad[:3]], want[bad[:3]])
+    # ranges other than the render default
+    for rng_ in ((0.0, 1e9), (1e-3, 300.0)):
+        got = ctx.trace_closest(rr[:20000], *rng_, mode=12)
+        assert len(ck.hits_equal(got, o.trace(rr[:20000], *rng_, quirks=0), fields)) == 0, rng_
+    # a scene with more than 32 primitives has no box list
+    _setup(ctx, "spheres")
+    with pytest.raises(Exception):
+        ctx.trace_closest(rr[:10], mode=12)
+
+
 def test_mixed_scene_all_primitive_types(ctx):
     rng = np.random.RandomState(3)
     mats = [scenes._mat(abi.RT_MAT_LAMBERTIAN, (0.5, 0.5, 0.5)), scenes._mat(abi.RT_MAT_METAL, (0.7, 0.6, 0.5), fuzz=0.3),
@@ -207,12 +251,12 @@ def test_render_bit_exact_vs_oracle(ctx, name, hw, spp):
 def test_render_kernel_variants_bit_exact(ctx, name, hw, spp, monkeypatch):
     """Every fused-kernel variant (RT_TRAV 0..19; 5 = warp-scheduled vote kernel, 6..8 = pool kernel with 2..4 slots
     per lane, 9..11 = warp-synchronous kernel: binary + cooperative record tests, 8-wide tree, 8-wide + cooperative, 12..13 = persistent kernel
-    without reconvergence at the query boundary over the binary / 8-wide tree, 14 = streaming kernel: single steps with deferred record tests and shading, 15 = 4-wide tree, 16/17 = fused kernel with the if-if loop over the 4-/8-wide tree, 18/19 = the same with the while-while loop)
+    without reconvergence at the query boundary over the binary / 8-wide tree, 14 = streaming kernel: single steps with deferred record tests and shading, 15 = 4-wide tree, 16/17 = fused kernel with the if-if loop over the 4-/8-wide tree, 18/19 = the same with the while-while loop, 20 = box list for scenes of at most 32 primitives)
     renders the oracle's image."""
     s, cam, o = _setup(ctx, name)
     H, W = hw
     want, cnt = o.render_product(H, W, 0, spp, 99)
-    for trav in range(20):
+    for trav in range(21):
         monkeypatch.setenv("RT_TRAV", str(trav))
         got, _, st = ctx.render_host(H, W, spp, seed=99, flags=abi.RT_RENDER_FUSED)
         assert (got.view(np.uint32) == want.view(np.uint32)).all(), trav
