@@ -724,6 +724,20 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
     RT_CUDA(cudaMemcpy(ctx->flat.box, ctx->nodes.as<float4>() + 2 * (size_t)(n_bp - 1), (size_t)n_bp * 32,
                        cudaMemcpyDeviceToHost));
     ctx->flat.n = n_bp;
+    // {lo, hi} -> {centre, half extent}: the half extent covers the rounding of the centre
+    for (int i = 0; i < n_bp; i++) {
+      float4 &lo = ctx->flat.box[2 * i], &hi = ctx->flat.box[2 * i + 1];
+      float *l = &lo.x, *h = &hi.x;
+      for (int a = 0; a < 3; a++) {
+        const double c = 0.5 * ((double)l[a] + (double)h[a]);
+        const float cf = (float)c;
+        const double he = std::max((double)h[a] - (double)cf, (double)cf - (double)l[a]);
+        float hf = (float)he;
+        if ((double)hf < he) hf = std::nextafter(hf, INFINITY);
+        l[a] = cf;
+        h[a] = hf;
+      }
+    }
   }
   ctx->has_scene = true;
 

@@ -18,7 +18,7 @@ namespace rtc {
 constexpr int FLAT_MAX = 32;
 
 struct FlatItems {
-  float4 box[2 * FLAT_MAX];  // {lo.xyz, first record}, {hi.xyz, LEAF_FLAG | record count}
+  float4 box[2 * FLAT_MAX];  // {centre.xyz, first record}, {half extent.xyz (rounded up), LEAF_FLAG | record count}
   int32_t n;                 // 0: no box list for this scene
   int32_t pad[3];
 };
@@ -67,21 +67,27 @@ __device__ __forceinline__ Hit world_hit_flat(const DScene &s, const FlatItems &
     const float nox = -(r.o.x * idx), noy = -(r.o.y * idy), noz = -(r.o.z * idz);
     const float t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
     const float t_hi0 = b.t_f + fabsf(b.t_f) * 1e-5f;
-    // ---- all boxes, uniformly: hit mask + nearest entry
-    uint32_t mask = 0;
+    // ---- all boxes, uniformly: hit mask + nearest entry.  Centre / half-extent form: 3 FFMA per axis
+    //      (m = c/d - o/d, near = m - h/|d|, far = m + h/|d|) instead of 2 FFMA + min + max.
+    const float adx = fabsf(idx), ady = fabsf(idy), adz = fabsf(idz);
+    uint32_t mask = 0, bit = 1u, bit_min = 0u;
     float tn_min = CUDART_INF_F;
-    int j = -1;
 #pragma unroll 2
     for (int c = 0; c < n; c++) {
-      const float4 lo = fl.box[2 * c], hi = fl.box[2 * c + 1];
-      float tn, tf;
-      RT_FLAT_SLAB(lo, hi, t_hi0, tn, tf)
+      const float4 ce = fl.box[2 * c], he = fl.box[2 * c + 1];
+      const float mx = __fmaf_rn(ce.x, idx, nox), my = __fmaf_rn(ce.y, idy, noy), mz = __fmaf_rn(ce.z, idz, noz);
+      const float tn = fmaxf(fmaxf(__fmaf_rn(-he.x, adx, mx), __fmaf_rn(-he.y, ady, my)),
+                             fmaxf(__fmaf_rn(-he.z, adz, mz), t_lo));
+      const float tf = fminf(fminf(__fmaf_rn(he.x, adx, mx), __fmaf_rn(he.y, ady, my)),
+                             fminf(__fmaf_rn(he.z, adz, mz), t_hi0));
       const bool hit = tn <= tf * 1.00001f;
-      mask |= hit ? (1u << c) : 0u;
+      mask |= hit ? bit : 0u;
       const bool nearer = hit && tn < tn_min;
       tn_min = nearer ? tn : tn_min;
-      j = nearer ? c : j;
+      bit_min = nearer ? bit : bit_min;
+      bit += bit;
     }
+    int j = __ffs(bit_min) - 1;
     if (STATS) st->nodes += n;
     if (j >= 0) mask &= ~(1u << j);
     // ---- candidates: nearest box first, then the mask in index order with a re-test against the closest hit
