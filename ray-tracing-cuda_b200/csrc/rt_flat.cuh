@@ -16,6 +16,10 @@
 namespace rtc {
 
 constexpr int FLAT_MAX = 32;
+#ifndef RT_FLAT_UNROLL
+#define RT_FLAT_UNROLL 2
+#endif
+constexpr int kFlatUnroll = RT_FLAT_UNROLL;
 
 struct FlatItems {
   float4 box[2 * FLAT_MAX];  // {centre.xyz, first record}, {half extent.xyz (rounded up), LEAF_FLAG | record count}
@@ -72,7 +76,7 @@ __device__ __forceinline__ Hit world_hit_flat(const DScene &s, const FlatItems &
     const float adx = fabsf(idx), ady = fabsf(idy), adz = fabsf(idz);
     uint32_t mask = 0, bit = 1u, bit_min = 0u;
     float tn_min = CUDART_INF_F;
-#pragma unroll 2
+#pragma unroll kFlatUnroll
     for (int c = 0; c < n; c++) {
       const float4 ce = fl.box[2 * c], he = fl.box[2 * c + 1];
       const float mx = __fmaf_rn(ce.x, idx, nox), my = __fmaf_rn(ce.y, idy, noy), mz = __fmaf_rn(ce.z, idz, noz);
