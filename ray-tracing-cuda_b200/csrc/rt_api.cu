@@ -54,7 +54,7 @@ extern "C" int rt_ctx_destroy(rt_ctx *c) {
   if (!c) return RT_OK;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
-  DevBuf *bufs[] = {&c->nodes, &c->recs, &c->recs_seq, &c->face_uv, &c->face_uv_seq, &c->mats, &c->textures,
+  DevBuf *bufs[] = {&c->nodes, &c->wnodes, &c->wnodes4, &c->cnodes8, &c->cnodes4, &c->recs, &c->recs_seq, &c->face_uv, &c->face_uv_seq, &c->mats, &c->textures,
                     &c->tex_pixels, &c->counters, &c->accum_tmp, &c->rgb_tmp, &c->rgb8_tmp, &c->rays_tmp, &c->hits_tmp};
   for (DevBuf *b : bufs) b->release();
   for (DevBuf &b : c->scratch) b.release();

@@ -333,6 +333,64 @@ __global__ void k_wide_expand(const float4 *__restrict__ nodes, const uint2 *__r
   }
 }
 
+
+// Compact form of the wide nodes (rt_cwide.cuh; layout: CWideLayout in rt_device.cuh).  One thread per wide node.
+// origin = componentwise minimum of the child boxes; step per axis = the power of two 2^k with
+// 1.001 * extent <= 255 * 2^k; lo planes are rounded down and hi planes up to the grid with at least 1/1024 of a
+// step of slack (a plane exactly at the origin keeps q = 0: there the decoded plane IS the float it came from), so the
+// decoded box contains the float box with a margin far above the rounding of the traversal's two-FMA plane distance.
+// All grid arithmetic in double (exact: differences of floats divided by a power of two).
+template <int W>
+__global__ void k_wide_compress(const float4 *__restrict__ wnodes, int n_w, uint4 *__restrict__ cnodes) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_w) return;
+  using L = WideLayout<W>;
+  using C = CWideLayout<W>;
+  const float *f = reinterpret_cast<const float *>(wnodes + (size_t)L::F4 * t);
+  const uint32_t *u = reinterpret_cast<const uint32_t *>(f);
+  const uint32_t valid = u[7 * W];
+  uint32_t out[C::WORDS];
+  for (int i = 0; i < C::WORDS; i++) out[i] = 0u;
+  uint32_t ebits = 0;
+  for (int a = 0; a < 3; a++) {
+    float org = CUDART_INF_F, top = -CUDART_INF_F;
+    for (int i = 0; i < W; i++)
+      if (valid >> i & 1u) {
+        org = fminf(org, f[a * W + i]);
+        top = fmaxf(top, f[(3 + a) * W + i]);
+      }
+    if (!(org <= top)) org = top = 0.f;  // no valid child (never emitted) or NaN
+    const double ext = ((double)top - (double)org) * 1.001;
+    int k = -126;
+    if (ext > 0.0) {
+      frexp(ext / 255.0, &k);  // ext / 255 = m * 2^k, m in [0.5, 1)  =>  2^k >= ext / 255
+      if (k < -126) k = -126;
+    }
+    const double step = ldexp(1.0, k);
+    ebits |= (uint32_t)(k + 127) << (8 * a);
+    out[a] = __float_as_uint(org);
+    for (int i = 0; i < W; i++) {
+      uint32_t qlo = 255u, qhi = 0u;  // empty slot: inverted box
+      if (valid >> i & 1u) {
+        const double xl = ((double)f[a * W + i] - (double)org) / step;
+        const double xh = ((double)f[(3 + a) * W + i] - (double)org) / step;
+        double l = xl > 0.0 ? floor(xl - 1.0 / 1024) : 0.0;
+        double h = ceil(xh + 1.0 / 1024);
+        l = l < 0.0 ? 0.0 : (l > 255.0 ? 255.0 : l);
+        h = h < 0.0 ? 0.0 : (h > 255.0 ? 255.0 : h);
+        qlo = (uint32_t)l;
+        qhi = (uint32_t)h;
+      }
+      out[4 + (a * C::G) + (i >> 2)] |= qlo << (8 * (i & 3));
+      out[4 + ((3 + a) * C::G) + (i >> 2)] |= qhi << (8 * (i & 3));
+    }
+  }
+  out[3] = ebits | (valid << 24);
+  for (int i = 0; i < W; i++) out[C::REFW + i] = u[6 * W + i];
+  uint4 *o = cnodes + (size_t)C::U4 * t;
+  for (int q = 0; q < C::U4; q++) o[q] = make_uint4(out[4 * q], out[4 * q + 1], out[4 * q + 2], out[4 * q + 3]);
+}
+
 }  // namespace rtc
 
 // =================================================================================================
@@ -690,6 +748,13 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
         }
         if (width == 8) wide_depth = levels;
       }
+      // compact copy of the same tree (same node indices): RT_TRAV=21 / 22
+      DevBuf &cbuf = width == 8 ? ctx->cnodes8 : ctx->cnodes4;
+      RT_CUDA(cbuf.reserve((size_t)n_w * (width == 8 ? CWideLayout<8>::U4 : CWideLayout<4>::U4) * 16));
+      if (width == 8)
+        k_wide_compress<8><<<nblk(n_w), 256, 0, st>>>(wbuf.as<float4>(), n_w, cbuf.as<uint4>());
+      else
+        k_wide_compress<4><<<nblk(n_w), 256, 0, st>>>(wbuf.as<float4>(), n_w, cbuf.as<uint4>());
       if (width == 8) n_wnodes = n_w;
     }
     RT_CUDA(cudaGetLastError());
@@ -703,6 +768,8 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   s.nodes = ctx->nodes.as<float4>();
   s.wnodes = n_wnodes > 0 ? ctx->wnodes.as<float4>() : nullptr;
   s.wnodes4 = n_wnodes > 0 ? ctx->wnodes4.as<float4>() : nullptr;
+  s.cnodes8 = n_wnodes > 0 ? ctx->cnodes8.as<uint4>() : nullptr;
+  s.cnodes4 = n_wnodes > 0 ? ctx->cnodes4.as<uint4>() : nullptr;
   s.n_wnodes = n_wnodes;
   s.recs = ctx->recs.as<float4>();
   s.recs_seq = recs_seq;

@@ -77,6 +77,14 @@ template <int W>
 struct WideLayout {
   static constexpr int G = W / 4, F4 = 8 * G, HI = 3 * G, REF = 6 * G, META = 7 * G;
 };
+// Compact wide node (rt_cwide.cuh): child boxes quantised to 8 bits per plane against the node's own origin and a
+// power-of-two step per axis.  uint32 words: [0..2] origin xyz (float), [3] ex | ey<<8 | ez<<16 | valid<<24 (step =
+// 2^(e-127)), then 6 plane arrays of W bytes (lo.x lo.y lo.z hi.x hi.y hi.z; byte i = child i), then W refs (same
+// encoding as the wide node).  W = 4: 64 B (4 uint4, refs in uint4 #3); W = 8: 96 B (6 uint4, refs in #4, #5).
+template <int W>
+struct CWideLayout {
+  static constexpr int G = W / 4, U4 = W == 4 ? 4 : 6, REFW = 4 * (U4 - G), WORDS = 4 * U4;
+};
 constexpr uint32_t WLEAF = 0x80000000u, WREF_EMPTY = 0xffffffffu;
 constexpr int WLEAF_COUNT_SHIFT = 28, WLEAF_MAX_COUNT = 7;
 constexpr uint32_t WLEAF_FIRST_MASK = (1u << WLEAF_COUNT_SHIFT) - 1;
@@ -99,6 +107,8 @@ struct DScene {
   const float4 *nodes;     // 32-byte nodes: {lo.xyz, a}, {hi.xyz, b}
   const float4 *wnodes;    // 256-byte wide nodes (8 children), node 0 = root; null when n_recs == 0
   const float4 *wnodes4;   // 128-byte wide nodes (4 children)
+  const uint4 *cnodes8;    // 96-byte compact wide nodes (8 children, 8-bit planes), same indices as wnodes
+  const uint4 *cnodes4;    // 64-byte compact wide nodes (4 children), same indices as wnodes4
   const float4 *recs;      // records in BVH (Morton) order, 3 float4 each
   const float4 *recs_seq;  // records in list order (Append order; faces in post-sort order; incl. SKY)
   const float *face_uv;    // per BVH-order record: 6 floats (Face<true> texcoords), or null

@@ -11,6 +11,7 @@
 
 #include "rt_internal.h"
 #include "rt_walk.cuh"
+#include "rt_cwide.cuh"
 
 #ifndef RT_DEFAULT_TRAV
 #define RT_DEFAULT_TRAV 0  // traversal loop of the parity hook and the wavefront extend kernel
@@ -106,6 +107,8 @@ __global__ void __launch_bounds__(128) k_trace_closest(DScene s, const float *__
     case 5: h = world_hit_bvh<false, 3>(s, r, t_from, t_to, nullptr); break;
     case 6: h = world_hit_bvh<false, 4>(s, r, t_from, t_to, nullptr); break;
     case 7: h = world_hit_bvh<false, 5>(s, r, t_from, t_to, nullptr); break;
+    case 13: h = world_hit_cwide<false, 4>(s, r, t_from, t_to, nullptr); break;
+    case 14: h = world_hit_cwide<false, 8>(s, r, t_from, t_to, nullptr); break;
     default: h = world_hit_bvh<false, RT_DEFAULT_TRAV>(s, r, t_from, t_to, nullptr); break;
   }
   out[i] = make_rt_hit(s, r, h);
@@ -273,7 +276,9 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
     bool alive = depth < a.max_depth;  // ray_tracing.cu:23: the query at depth == limit yields 0
     if (alive) {
       Hit h;
-      if constexpr (TRAV == 20)  // box list (<= 32 primitives)
+      if constexpr (TRAV == 21 || TRAV == 22)  // if-if over the compact 4-/8-wide tree (rt_cwide.cuh)
+        h = world_hit_cwide<STATS, TRAV == 21 ? 4 : 8>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
+      else if constexpr (TRAV == 20)  // box list (<= 32 primitives)
         h = world_hit_flat<STATS>(s, fl, ray, 1e-3, (double)CUDART_INF_F, &ts);
       else if constexpr (TRAV >= 18)  // while-while over the 4-/8-wide tree, per lane
         h = world_hit_wide<STATS, false, TRAV == 18 ? 4 : 8>(s, ray, true, 1e-3, (double)CUDART_INF_F, nullptr, &ts);
@@ -1086,7 +1091,7 @@ using namespace rtc;
 namespace {
 inline int nblk(size_t n, int b) { return (int)((n + b - 1) / b); }
 
-// Traversal variant of the render kernels: RT_TRAV=0..20 overrides the default (diagnostics).
+// Traversal variant of the render kernels: RT_TRAV=0..22 overrides the default (diagnostics).
 // Default (measured, profiles/r01_h_variants_sweep.txt, r01_o_wide_ifif_sweep.txt, r01_v_box_list_sweep.txt):
 //   <= 32 primitives (Cornell, birthday): no tree — box list, every lane tests every box (rt_flat.cuh);
 //   <= 4096 records (spheres, birthday): binary tree, while-while loop — incoherent bounce rays in an
@@ -1102,7 +1107,7 @@ int trav_variant(const rt_ctx *ctx) {
   if (ctx->flat.n > 0) dflt = 20;  // <= 32 primitives: box list (rt_flat.cuh), +37 % on Cornell, +20 % on birthday
   int v = e ? atoi(e) : dflt;
   if (v == 20 && ctx->flat.n == 0) v = dflt;  // no box list for this scene
-  return (v < 0 || v > 20) ? dflt : v;
+  return (v < 0 || v > 22) ? dflt : v;
 }
 
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
@@ -1126,7 +1131,7 @@ extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t
                                        rt_hit *d_hits, void *stream) {
   int rc = check_ready(ctx, false, "rt_trace_closest");
   if (rc) return rc;
-  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 12)) {
+  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 14)) {
     set_error("rt_trace_closest: bad argument");
     return RT_ERR_INVALID;
   }
@@ -1139,7 +1144,7 @@ extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t
   if (mode == 12)
     k_trace_closest_flat<<<nblk((size_t)n, 128), 128, 0, (cudaStream_t)stream>>>(ctx->scene, ctx->flat, d_rays, n, t_from,
                                                                                  t_to, d_hits);
-  else if (mode >= 8)
+  else if (mode >= 8 && mode <= 11)
     k_trace_closest_warp<<<nblk((size_t)n, 128), 128, 0, (cudaStream_t)stream>>>(ctx->scene, d_rays, n, t_from, t_to,
                                                                                  mode, d_hits);
   else
@@ -1295,7 +1300,23 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     else                                                                                               \
       k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);    \
     break;
-    if (trav == 20) {  // box list
+    if (trav == 21 || trav == 22) {  // if-if over the compact wide trees
+#define RT_CWIDE_CASE(T)                                                                                         \
+  if (stats_on)                                                                                                  \
+    k_render_fused<true, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);                 \
+  else if (minb == 6)                                                                                            \
+    k_render_fused<false, T, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);             \
+  else if (minb == 8)                                                                                            \
+    k_render_fused<false, T, 8><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);             \
+  else                                                                                                           \
+    k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+      if (trav == 21) {
+        RT_CWIDE_CASE(21)
+      } else {
+        RT_CWIDE_CASE(22)
+      }
+#undef RT_CWIDE_CASE
+    } else if (trav == 20) {  // box list
       if (stats_on)
         k_render_fused<true, 20><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr, ctx->flat);
       else if (minb == 6)

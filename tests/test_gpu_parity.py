@@ -106,7 +106,7 @@ def test_degenerate_directions(ctx, name):
     lo, hi = _BOX[name]
     rr = ck.degenerate_rays(40000, 33, lo, hi)
     want = o.trace(rr, quirks=0)
-    for mode in (0, 2, 3, 8, 9, 10, 11):
+    for mode in (0, 2, 3, 8, 9, 10, 11, 13, 14):
         got = ctx.trace_closest(rr, mode=mode)
         bad = ck.hits_equal(got, want, _fields(name))
         assert len(bad) == 0, (mode, len(bad), rr[bad[:3]], got[bad[:3]], want[bad[:3]])
@@ -115,12 +115,13 @@ def test_degenerate_directions(ctx, name):
 @pytest.mark.parametrize("name", ["cornell_box", "spheres", "bunny9k", "soup100k"])
 def test_traversal_variants_identical(ctx, name):
     """Every traversal variant of the render kernels (modes 2..7 per-lane binary loops, 8 = 8-wide tree,
-    9 = 8-wide tree + warp-cooperative record tests, 10 = binary tree + cooperative) returns the oracle's hits."""
+    9 = 8-wide tree + warp-cooperative record tests, 10 = binary tree + cooperative, 11 = 4-wide tree,
+    13 / 14 = compact 4-/8-wide tree with 8-bit quantised child boxes, rt_cwide.cuh) returns the oracle's hits."""
     s, cam, o = _setup(ctx, name)
     lo, hi = _BOX[name]
     rr = np.concatenate([ctx.primary_rays(54, 96), ck.random_rays(30000, 21, lo, hi)])
     want = o.trace(rr, quirks=0)
-    for mode in (2, 3, 4, 5, 6, 7, 8, 9, 10, 11):
+    for mode in (2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 14):
         got = ctx.trace_closest(rr, mode=mode)
         bad = ck.hits_equal(got, want, _fields(name))
         assert len(bad) == 0, (mode, len(bad), got[bad[:3]], want[bad[:3]])
@@ -249,14 +250,15 @@ def test_render_bit_exact_vs_oracle(ctx, name, hw, spp):
 
 @pytest.mark.parametrize("name,hw,spp", [("cornell_box", (72, 128), 8), ("spheres", (54, 96), 8), ("bunny9k", (54, 96), 4)])
 def test_render_kernel_variants_bit_exact(ctx, name, hw, spp, monkeypatch):
-    """Every fused-kernel variant (RT_TRAV 0..19; 5 = warp-scheduled vote kernel, 6..8 = pool kernel with 2..4 slots
+    """Every fused-kernel variant (RT_TRAV 0..22; 5 = warp-scheduled vote kernel, 6..8 = pool kernel with 2..4 slots
     per lane, 9..11 = warp-synchronous kernel: binary + cooperative record tests, 8-wide tree, 8-wide + cooperative, 12..13 = persistent kernel
-    without reconvergence at the query boundary over the binary / 8-wide tree, 14 = streaming kernel: single steps with deferred record tests and shading, 15 = 4-wide tree, 16/17 = fused kernel with the if-if loop over the 4-/8-wide tree, 18/19 = the same with the while-while loop, 20 = box list for scenes of at most 32 primitives)
+    without reconvergence at the query boundary over the binary / 8-wide tree, 14 = streaming kernel: single steps with deferred record tests and shading, 15 = 4-wide tree, 16/17 = fused kernel with the if-if loop over the 4-/8-wide tree, 18/19 = the same with the while-while loop, 20 = box list for scenes of at most 32 primitives,
+    21/22 = if-if loop over the compact 4-/8-wide tree with 8-bit quantised boxes)
     renders the oracle's image."""
     s, cam, o = _setup(ctx, name)
     H, W = hw
     want, cnt = o.render_product(H, W, 0, spp, 99)
-    for trav in range(21):
+    for trav in range(23):
         monkeypatch.setenv("RT_TRAV", str(trav))
         got, _, st = ctx.render_host(H, W, spp, seed=99, flags=abi.RT_RENDER_FUSED)
         assert (got.view(np.uint32) == want.view(np.uint32)).all(), trav
@@ -283,6 +285,25 @@ def test_max_depth_and_resolve(ctx):
         assert st.rays_ref_equiv == int(cnt[2])
         ref_rgb = np.sqrt(np.clip(want / np.float32(spp), 0, 1)).astype(np.float32)
         assert np.abs(rgb - ref_rgb).max() <= 1e-6
+
+
+def test_compact_wide_tree_full_size(ctx):
+    """Quantised boxes must only ever be LARGER than the float boxes: on a 1 M-triangle soup (the size class the compact
+    tree is built for; the oracle would need minutes) modes 13 / 14 return exactly the hits of the binary tree (mode 2)
+    on 400 k primary and random rays, and on rays scaled far away from / shrunk towards the origin."""
+    s, cam = scenes.soup(1000000)
+    ctx.commit(s)
+    ctx.set_camera(rt.core.camera_look_at(cam))
+    rr = np.concatenate([ctx.primary_rays(270, 480), ck.random_rays(270000, 33, -1.2, 1.2)])
+    far = rr[:50000].copy()
+    far[:, :3] *= np.float32(50.0)  # origins far outside the scene box: large |o| / |d| against small boxes
+    rr = np.concatenate([rr, far])
+    want = ctx.trace_closest(rr, mode=2)
+    assert (want["obj"] >= 0).mean() > 0.3
+    for mode in (13, 14):
+        got = ctx.trace_closest(rr, mode=mode)
+        bad = ck.hits_equal(got, want)
+        assert len(bad) == 0, (mode, len(bad), rr[bad[:3]], got[bad[:3]], want[bad[:3]])
 
 
 def test_full_size_properties(ctx):
