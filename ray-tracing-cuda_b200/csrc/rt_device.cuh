@@ -900,15 +900,17 @@ __device__ __forceinline__ bool material_needs_uv(const DMaterial &m) { return m
 // Material::Scatter (lambertian.cu:33-43, metal.cu:12-25, dielectric.cu:16-44, diffuse_light.cu:5-9,
 // sky.cu:3-7).  Returns false when the path ends here.  The scattered ray goes through Ray::Ray,
 // which normalizes (ray.cu:8-11).
-__device__ __forceinline__ bool scatter(const DScene &s, const DMaterial &m, const RayQ &ray, float t, const Surface &sf,
-                                        const PathKey &pk, int depth, V3 *att, RayQ *out) {
+// BALL: float* -> V3, the ball sample of this bounce (ball_rejection, or a sample drawn ahead by ball_rejection_coop).
+template <typename BALL>
+__device__ __forceinline__ bool scatter_with(const DScene &s, const DMaterial &m, const RayQ &ray, float t,
+                                             const Surface &sf, BALL ball, V3 *att, RayQ *out) {
   switch (m.type) {
     case RT_MAT_LAMBERTIAN: {
       if (dot(ray.d, sf.normal) >= 0) return false;
       V3 p = ray.o + t * ray.d;
       V3 albedo = texture_value(s, m, sf.u, sf.v);
       float l;
-      V3 r = ball_rejection(pk, depth, &l);
+      V3 r = ball(&l);
       r.x /= l;
       r.y /= l;
       r.z /= l;
@@ -927,7 +929,7 @@ __device__ __forceinline__ bool scatter(const DScene &s, const DMaterial &m, con
       out->o = p;
       if (fuzz > 0) {
         float l;
-        V3 r = ball_rejection(pk, depth, &l);
+        V3 r = ball(&l);
         out->d = normalize(reflected + fuzz * r);
       } else {
         out->d = normalize(reflected);
@@ -951,6 +953,75 @@ __device__ __forceinline__ bool scatter(const DScene &s, const DMaterial &m, con
     default:
       return false;
   }
+}
+
+__device__ __forceinline__ bool scatter(const DScene &s, const DMaterial &m, const RayQ &ray, float t, const Surface &sf,
+                                        const PathKey &pk, int depth, V3 *att, RayQ *out) {
+  return scatter_with(s, m, ray, t, sf, [&](float *l) { return ball_rejection(pk, depth, l); }, att, out);
+}
+
+// Does Scatter draw a ball sample for this hit?  (lambertian.cu:36, metal.cu:15,20: front face only; Metal only with fuzz)
+__device__ __forceinline__ bool scatter_needs_ball(const DMaterial &m, const RayQ &ray, const Surface &sf) {
+  if (m.type == RT_MAT_LAMBERTIAN) return !(dot(ray.d, sf.normal) >= 0);
+  if (m.type == RT_MAT_METAL) return !(dot(ray.d, sf.normal) >= 0) && m.color_fuzz.w > 0;
+  return false;
+}
+
+// ball_rejection for the lanes of a (partly) converged warp: the same Philox blocks, the same first accepted
+// iteration, so the same sample — but the iterations of the lanes that still `need` one are spread over ALL calling
+// lanes.  In the per-lane loop a warp runs max(trip count) rounds (5.2 for 19 Lambertian lanes, acceptance 0.52) with
+// 8 of 32 lanes busy (profiles/r01_x_cornell_boxlist_ncu_summary.txt: philox + ball_rejection = 17 % of all warp
+// instructions at 8 lanes).  Here every lane that needs no sample (light / sky / dielectric hit, finished pixel, or a
+// lane already served) tries a LATER iteration of the first needy lane above it: lane L's run = the calling lanes
+// between the previous needy lane and L; L itself tries iteration base, the run below it base + 1, base + 2, ...
+// (by decreasing lane); L takes the accepted candidate of lowest iteration, or moves base past the run.
+// Every lane that is converged at the call must call (need = false to help only).
+__device__ __forceinline__ V3 ball_rejection_coop(bool need, const PathKey &pk, int depth, float *out_l) {
+  const unsigned act = __activemask();
+  const int lane = threadIdx.x & 31;
+  const unsigned le = (2u << lane) - 1u;  // lanes <= this one
+  float x = 0, y = 0, z = 0, l = 0;
+  uint32_t base = 0;
+  bool exhausted = false;
+  unsigned needy = __ballot_sync(act, need);
+  while (needy) {
+    const bool self = (needy >> lane) & 1u;
+    const unsigned above = needy & ~le;
+    const int tgt = self ? lane : (above ? __ffs(above) - 1 : -1);
+    const uint32_t off = self ? 0u : 1u + (uint32_t)__popc(act & ~le & ((1u << (tgt & 31)) - 1u));
+    const int src = tgt < 0 ? lane : tgt;
+    const uint32_t c0 = __shfl_sync(act, pk.pixel, src), c1 = __shfl_sync(act, pk.sample, src);
+    const uint32_t c2 = __shfl_sync(act, (uint32_t)(1 + depth), src), c3 = __shfl_sync(act, base, src) + off;
+    float cx = 0, cy = 0, cz = 0, cl = 2.f;
+    if (tgt >= 0 && c3 < (uint32_t)MAX_REJECT_ITER) {
+      uint32_t o[4];
+      philox4x32_10(c0, c1, c2, c3, pk.k0, pk.k1, o);
+      cx = u01(o[0]) * 2.0f + -1.0f;
+      cy = u01(o[1]) * 2.0f + -1.0f;
+      cz = u01(o[2]) * 2.0f + -1.0f;
+      cl = sqrtf(cx * cx + cy * cy + cz * cz);
+    }
+    const unsigned okm = __ballot_sync(act, !(cl > 1));
+    const unsigned below = needy & (le >> 1);  // needy lanes < this one
+    const unsigned run = act & le & ~(below ? (2u << (31 - __clz(below))) - 1u : 0u);
+    const unsigned sel = okm & run;
+    const int from = sel ? 31 - __clz(sel) : lane;  // highest lane of the run = lowest iteration
+    const float gx = __shfl_sync(act, cx, from), gy = __shfl_sync(act, cy, from);
+    const float gz = __shfl_sync(act, cz, from), gl = __shfl_sync(act, cl, from);
+    if (self) {
+      if (sel) {
+        x = gx, y = gy, z = gz, l = gl;
+        need = false;
+      } else {
+        base += (uint32_t)__popc(run);
+        if (base >= (uint32_t)MAX_REJECT_ITER) exhausted = true, need = false;
+      }
+    }
+    needy = __ballot_sync(act, need);
+  }
+  if (exhausted) return ball_rejection(pk, depth, out_l);  // 0.48^64: the serial loop's own answer
+  *out_l = l;
+  return mk(x, y, z);
 }
 
 // Material::Emit (diffuse_light.cu:11-13, sky.cu:9-14, material.cu:3-6)

@@ -181,6 +181,60 @@ __device__ __forceinline__ bool shade_hit(const DScene &s, RayQ &ray, const Hit 
   return true;
 }
 
+// shade_hit in two halves around a converged point (RT_TRAV=23: cooperative ball rejection, rt_device.cuh).
+// shade_prepare: everything up to the Scatter call; returns true when a Scatter is pending (ShadePending filled,
+// need_ball = Scatter will draw a ball sample), false when the path ended here (emission added).
+struct ShadePending {
+  DMaterial m;
+  Surface sf;
+  float t;
+};
+__device__ __forceinline__ bool shade_prepare(const DScene &s, const RayQ &ray, const Hit &h, const V3 &T, V3 &color,
+                                              ShadePending &sp, bool &need_ball) {
+  int mat_id;
+  if (h.rec == REC_SKY) {
+    mat_id = s.sky_mat;
+  } else {
+    const float4 *recs = h.seq ? s.recs_seq : s.recs;
+    mat_id = (int)(__float_as_uint(__ldg(recs + 3 * (size_t)h.rec + 2).w) >> KIND_BITS);
+  }
+  DMaterial &m = sp.m;
+  {
+    const float4 *mp = reinterpret_cast<const float4 *>(s.mats + mat_id);
+    float4 a = __ldg(mp), b = __ldg(mp + 1);
+    m.color_fuzz = a;
+    m.type = __float_as_int(b.x);
+    m.texture = __float_as_int(b.y);
+    m.eta_in = b.z;
+    m.eta_out = b.w;
+  }
+  const bool need_uv = material_needs_uv(m);
+  sp.t = float(h.t);
+  if (m.type == RT_MAT_SKY || m.type == RT_MAT_DIFFUSE_LIGHT) {
+    float u = 0.f, v = 0.f;
+    if (need_uv) {
+      Surface sf = surface_at(s, ray, h, true);
+      u = sf.u;
+      v = sf.v;
+    }
+    V3 p = ray.o + sp.t * ray.d;
+    color = color + T * emit(s, m, u, v, p);
+    return false;
+  }
+  sp.sf = surface_at(s, ray, h, need_uv);
+  need_ball = scatter_needs_ball(m, ray, sp.sf);
+  return true;
+}
+__device__ __forceinline__ bool shade_finish(const DScene &s, RayQ &ray, const ShadePending &sp, V3 ball, float ball_l,
+                                             V3 &T) {
+  V3 att;
+  RayQ out;
+  if (!scatter_with(s, sp.m, ray, sp.t, sp.sf, [&](float *l) { *l = ball_l; return ball; }, &att, &out)) return false;
+  T = T * att;
+  ray = out;
+  return true;
+}
+
 __device__ __forceinline__ void flush_counters(RenderCounters *ctr, unsigned long long samples,
                                                unsigned long long rays, unsigned long long rays_ref,
                                                unsigned long long nodes, unsigned long long prims) {
@@ -239,7 +293,7 @@ static __device__ __noinline__ Hit trav_finish_call(const DScene &s, Trav tv, Ra
 template <bool STATS, int TRAV, int MINB = 5>
 __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera cam, RenderArgs a, float *__restrict__ accum,
                                                       RenderCounters *ctr,
-                                                      typename FlatParamT<TRAV == 20>::type fl = {}) {
+                                                      typename FlatParamT<TRAV == 20 || TRAV == 23>::type fl = {}) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
   const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -274,11 +328,13 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
     }
     n_rays_ref++;
     bool alive = depth < a.max_depth;  // ray_tracing.cu:23: the query at depth == limit yields 0
+    ShadePending spend;
+    bool pending = false, need_ball = false;
     if (alive) {
       Hit h;
       if constexpr (TRAV == 21 || TRAV == 22)  // if-if over the compact 4-/8-wide tree (rt_cwide.cuh)
         h = world_hit_cwide<STATS, TRAV == 21 ? 4 : 8>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
-      else if constexpr (TRAV == 20)  // box list (<= 32 primitives)
+      else if constexpr (TRAV == 20 || TRAV == 23)  // box list (<= 32 primitives)
         h = world_hit_flat<STATS>(s, fl, ray, 1e-3, (double)CUDART_INF_F, &ts);
       else if constexpr (TRAV >= 18)  // while-while over the 4-/8-wide tree, per lane
         h = world_hit_wide<STATS, false, TRAV == 18 ? 4 : 8>(s, ray, true, 1e-3, (double)CUDART_INF_F, nullptr, &ts);
@@ -292,7 +348,10 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
         n_prims += ts.prims;
         ts.nodes = ts.prims = 0;
       }
-      if constexpr (MINB >= 8) {
+      if constexpr (TRAV == 23) {  // shading in two halves around the converged point below
+        alive = false;
+        if (h.rec != REC_NONE) pending = shade_prepare(s, ray, h, T, color, spend, need_ball);
+      } else if constexpr (MINB >= 8) {
         alive = false;
         if (h.rec != REC_NONE) {
           ShadeRet sr = shade_hit_call(s, ray, h, pk, depth, T, color);
@@ -304,6 +363,13 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
       } else {
         alive = h.rec != REC_NONE && shade_hit(s, ray, h, pk, depth, T, color);
       }
+    }
+    if constexpr (TRAV == 23) {
+      // every lane still rendering passes here converged: lanes without a pending ball sample try later
+      // rejection iterations of their neighbours (ball_rejection_coop)
+      float bl;
+      const V3 br = ball_rejection_coop(need_ball, pk, depth, &bl);
+      if (pending) alive = shade_finish(s, ray, spend, br, bl, T);
     }
     if (alive) {
       depth++;
@@ -1107,7 +1173,8 @@ int trav_variant(const rt_ctx *ctx) {
   if (ctx->flat.n > 0) dflt = 20;  // <= 32 primitives: box list (rt_flat.cuh), +37 % on Cornell, +20 % on birthday
   int v = e ? atoi(e) : dflt;
   if (v == 20 && ctx->flat.n == 0) v = dflt;  // no box list for this scene
-  return (v < 0 || v > 22) ? dflt : v;
+  if (v == 23 && ctx->flat.n == 0) v = dflt;
+  return (v < 0 || v > 23) ? dflt : v;
 }
 
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
@@ -1316,6 +1383,13 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
         RT_CWIDE_CASE(22)
       }
 #undef RT_CWIDE_CASE
+    } else if (trav == 23) {  // box list + cooperative ball rejection
+      if (stats_on)
+        k_render_fused<true, 23><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr, ctx->flat);
+      else if (minb == 6)
+        k_render_fused<false, 23, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr, ctx->flat);
+      else
+        k_render_fused<false, 23><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr, ctx->flat);
     } else if (trav == 20) {  // box list
       if (stats_on)
         k_render_fused<true, 20><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr, ctx->flat);

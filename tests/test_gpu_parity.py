@@ -258,7 +258,7 @@ def test_render_kernel_variants_bit_exact(ctx, name, hw, spp, monkeypatch):
     s, cam, o = _setup(ctx, name)
     H, W = hw
     want, cnt = o.render_product(H, W, 0, spp, 99)
-    for trav in range(23):
+    for trav in range(24):
         monkeypatch.setenv("RT_TRAV", str(trav))
         got, _, st = ctx.render_host(H, W, spp, seed=99, flags=abi.RT_RENDER_FUSED)
         assert (got.view(np.uint32) == want.view(np.uint32)).all(), trav
