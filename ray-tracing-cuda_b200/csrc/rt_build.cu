@@ -429,6 +429,91 @@ inline HostRec tri_rec(const float p0[3], const float p1[3], const float p2[3], 
 
 }  // namespace
 
+// Wide / compact trees are derived from the binary tree ON DEMAND: rt_scene_commit asks for the tree of the scene's
+// default traversal (none for the box list, the binary loops and the soups), rt_render / rt_trace_closest for the
+// tree of an explicitly selected variant.  The collapse runs level by level; its two queues live in scratch[6] / [7]
+// (bp_lo / bp_hi of the build, dead after k_emit and sized for one entry per build primitive).
+int rtc::ensure_trees(rt_ctx *ctx, unsigned need, cudaStream_t st) {
+  if (need & RT_TREE_C8) need |= RT_TREE_W8;
+  if (need & RT_TREE_C4) need |= RT_TREE_W4;
+  need &= ~ctx->trees;
+  if (!need || ctx->scene.n_recs <= 0) return RT_OK;
+  if ((size_t)ctx->scene.n_recs > (size_t)WLEAF_FIRST_MASK) {
+    set_error("wide trees: too many records for the wide-node leaf encoding");
+    return RT_ERR_LIMIT;
+  }
+  DevBuf *S = ctx->scratch;
+  RT_CUDA(S[10].reserve(32));
+  uint32_t *cnt = S[10].as<uint32_t>();
+  for (int width = 8; width >= 4; width -= 4) {
+    const unsigned wbit = width == 8 ? RT_TREE_W8 : RT_TREE_W4, cbit = width == 8 ? RT_TREE_C8 : RT_TREE_C4;
+    DevBuf &wbuf = width == 8 ? ctx->wnodes : ctx->wnodes4;
+    if (need & wbit) {
+      const int f4 = width == 8 ? WideLayout<8>::F4 : WideLayout<4>::F4;
+      int n_w = 0;
+      for (int pass = 0; pass < 2; pass++) {
+        uint2 *in = S[6].as<uint2>(), *out = S[7].as<uint2>();
+        uint2 seed = make_uint2(0u, 0u);
+        uint32_t c[2] = {0u, 1u};
+        RT_CUDA(cudaMemcpyAsync(in, &seed, sizeof(seed), cudaMemcpyHostToDevice, st));
+        RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
+        int n_in = 1, levels = 0;
+        while (n_in > 0) {
+          const float4 *bn = ctx->nodes.as<float4>();
+          float4 *wn = pass ? wbuf.as<float4>() : nullptr;
+          if (width == 8) {
+            if (pass == 0) k_wide_expand<false, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
+            else k_wide_expand<true, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
+          } else {
+            if (pass == 0) k_wide_expand<false, 4><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
+            else k_wide_expand<true, 4><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
+          }
+          RT_CUDA(cudaMemcpyAsync(c, cnt, sizeof(c), cudaMemcpyDeviceToHost, st));
+          RT_CUDA(cudaStreamSynchronize(st));
+          n_in = (int)c[0];
+          c[0] = 0;
+          RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
+          std::swap(in, out);
+          levels++;
+        }
+        if (pass == 0) {
+          n_w = (int)c[1];
+          RT_CUDA(wbuf.reserve((size_t)n_w * f4 * 16));
+        } else if ((int)c[1] != n_w) {
+          set_error("wide trees: collapse passes disagree");
+          return RT_ERR_CUDA;
+        }
+        if (width == 8) ctx->build_stats.wide_depth = levels;
+      }
+      ctx->n_wide[width == 8 ? 0 : 1] = n_w;
+      if (width == 8) {
+        ctx->scene.wnodes = wbuf.as<float4>();
+        ctx->scene.n_wnodes = n_w;
+        ctx->build_stats.n_wide_nodes = n_w;
+      } else {
+        ctx->scene.wnodes4 = wbuf.as<float4>();
+      }
+      ctx->trees |= wbit;
+    }
+    if (need & cbit) {  // compact copy of the same tree (same node indices): RT_TRAV=21 / 22
+      const int n_w = ctx->n_wide[width == 8 ? 0 : 1];
+      DevBuf &cbuf = width == 8 ? ctx->cnodes8 : ctx->cnodes4;
+      RT_CUDA(cbuf.reserve((size_t)n_w * (width == 8 ? CWideLayout<8>::U4 : CWideLayout<4>::U4) * 16));
+      if (width == 8) {
+        k_wide_compress<8><<<nblk(n_w), 256, 0, st>>>(wbuf.as<float4>(), n_w, cbuf.as<uint4>());
+        ctx->scene.cnodes8 = cbuf.as<uint4>();
+      } else {
+        k_wide_compress<4><<<nblk(n_w), 256, 0, st>>>(wbuf.as<float4>(), n_w, cbuf.as<uint4>());
+        ctx->scene.cnodes4 = cbuf.as<uint4>();
+      }
+      ctx->trees |= cbit;
+    }
+  }
+  RT_CUDA(cudaGetLastError());
+  return RT_OK;
+}
+
+
 extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_stats *stats) {
   if (!ctx || !d) {
     set_error("rt_scene_commit: null argument");
@@ -630,7 +715,7 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
     n_bp = (int)(last_flag + last_pos);
   }
   size_t n_recs = 0;
-  int n_nodes = 0, max_depth = 0, n_wnodes = 0, wide_depth = 0;
+  int n_nodes = 0, max_depth = 0;
   float sah = 0.f;
   uint32_t root_words[2] = {0, LEAF_FLAG};
   if (n_bp > 0) {
@@ -704,73 +789,15 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
     memcpy(&root_words[0], &root[0].w, 4);
     memcpy(&root_words[1], &root[1].w, 4);
 
-    // ---- wide collapse, level by level (bp_lo / bp_hi are dead: their storage holds the two queues) ----
-    if (n_recs > (size_t)WLEAF_FIRST_MASK) {
-      set_error("rt_scene_commit: too many records for the wide-node leaf encoding");
-      return RT_ERR_LIMIT;
-    }
-    uint32_t *cnt = S[10].as<uint32_t>();
-    for (int width = 8; width >= 4; width -= 4) {
-      DevBuf &wbuf = width == 8 ? ctx->wnodes : ctx->wnodes4;
-      const int f4 = width == 8 ? WideLayout<8>::F4 : WideLayout<4>::F4;
-      int n_w = 0;
-      for (int pass = 0; pass < 2; pass++) {
-        uint2 *in = S[6].as<uint2>(), *out = S[7].as<uint2>();
-        uint2 seed = make_uint2(0u, 0u);
-        uint32_t c[2] = {0u, 1u};
-        RT_CUDA(cudaMemcpyAsync(in, &seed, sizeof(seed), cudaMemcpyHostToDevice, st));
-        RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
-        int n_in = 1, levels = 0;
-        while (n_in > 0) {
-          const float4 *bn = ctx->nodes.as<float4>();
-          float4 *wn = pass ? wbuf.as<float4>() : nullptr;
-          if (width == 8) {
-            if (pass == 0) k_wide_expand<false, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
-            else k_wide_expand<true, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
-          } else {
-            if (pass == 0) k_wide_expand<false, 4><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
-            else k_wide_expand<true, 4><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
-          }
-          RT_CUDA(cudaMemcpyAsync(c, cnt, sizeof(c), cudaMemcpyDeviceToHost, st));
-          RT_CUDA(cudaStreamSynchronize(st));
-          n_in = (int)c[0];
-          c[0] = 0;
-          RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
-          std::swap(in, out);
-          levels++;
-        }
-        if (pass == 0) {
-          n_w = (int)c[1];
-          RT_CUDA(wbuf.reserve((size_t)n_w * f4 * 16));
-        } else if ((int)c[1] != n_w) {
-          set_error("rt_scene_commit: wide collapse passes disagree");
-          return RT_ERR_CUDA;
-        }
-        if (width == 8) wide_depth = levels;
-      }
-      // compact copy of the same tree (same node indices): RT_TRAV=21 / 22
-      DevBuf &cbuf = width == 8 ? ctx->cnodes8 : ctx->cnodes4;
-      RT_CUDA(cbuf.reserve((size_t)n_w * (width == 8 ? CWideLayout<8>::U4 : CWideLayout<4>::U4) * 16));
-      if (width == 8)
-        k_wide_compress<8><<<nblk(n_w), 256, 0, st>>>(wbuf.as<float4>(), n_w, cbuf.as<uint4>());
-      else
-        k_wide_compress<4><<<nblk(n_w), 256, 0, st>>>(wbuf.as<float4>(), n_w, cbuf.as<uint4>());
-      if (width == 8) n_wnodes = n_w;
-    }
     RT_CUDA(cudaGetLastError());
   }
-  RT_CUDA(cudaEventRecord(ctx->ev1, st));
-  RT_CUDA(cudaEventSynchronize(ctx->ev1));
-  float ms = 0.f;
-  cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
-
   DScene &s = ctx->scene;
   s.nodes = ctx->nodes.as<float4>();
-  s.wnodes = n_wnodes > 0 ? ctx->wnodes.as<float4>() : nullptr;
-  s.wnodes4 = n_wnodes > 0 ? ctx->wnodes4.as<float4>() : nullptr;
-  s.cnodes8 = n_wnodes > 0 ? ctx->cnodes8.as<uint4>() : nullptr;
-  s.cnodes4 = n_wnodes > 0 ? ctx->cnodes4.as<uint4>() : nullptr;
-  s.n_wnodes = n_wnodes;
+  s.wnodes = s.wnodes4 = nullptr;  // derived trees: built on demand (ensure_trees)
+  s.cnodes8 = s.cnodes4 = nullptr;
+  s.n_wnodes = 0;
+  ctx->trees = 0;
+  ctx->n_wide[0] = ctx->n_wide[1] = 0;
   s.recs = ctx->recs.as<float4>();
   s.recs_seq = recs_seq;
   s.face_uv = any_uv ? ctx->face_uv.as<float>() : nullptr;
@@ -809,6 +836,20 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   ctx->has_scene = true;
 
   rt_build_stats &bs = ctx->build_stats;
+  bs.n_wide_nodes = 0;
+  bs.wide_depth = 0;
+  // the tree of the traversal this scene renders with by default (RT_TRAV honoured); part of the build time
+  {
+    int rc = ensure_trees(ctx, trees_for_trav(trav_variant(ctx)), st);
+    if (rc) {
+      ctx->has_scene = false;
+      return rc;
+    }
+  }
+  RT_CUDA(cudaEventRecord(ctx->ev1, st));
+  RT_CUDA(cudaEventSynchronize(ctx->ev1));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
   bs.n_prims = n_bp;
   bs.n_nodes = n_nodes;
   bs.n_spheres = n_spheres;
@@ -818,8 +859,6 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   bs.build_ms = ms;
   bs.upload_ms = 0.f;
   bs.sah_cost = sah;
-  bs.n_wide_nodes = n_wnodes;
-  bs.wide_depth = wide_depth;
   if (stats) *stats = bs;
   return RT_OK;
 }

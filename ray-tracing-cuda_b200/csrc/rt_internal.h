@@ -43,10 +43,21 @@ struct DevBuf {
   }
 };
 
+// derived trees (rt_ctx::trees): built on demand by ensure_trees
+enum : unsigned { RT_TREE_W8 = 1u, RT_TREE_W4 = 2u, RT_TREE_C8 = 4u, RT_TREE_C4 = 8u };
+
 struct RenderCounters {  // device-side counters of one rt_render call
   unsigned long long samples, rays, rays_ref, nodes, prims, seq_fallbacks, sched_iters, sched_lanes;
 };
 
+}  // namespace rtc
+
+struct rt_ctx;
+namespace rtc {
+int trav_variant(const rt_ctx *ctx);                  // rt_render.cu: RT_TRAV or the scene's default
+unsigned trees_for_trav(int trav);                    // which derived trees a render variant walks
+unsigned trees_for_mode(int mode);                    // ... and a rt_trace_closest mode
+int ensure_trees(rt_ctx *ctx, unsigned need, cudaStream_t st);  // rt_build.cu
 }  // namespace rtc
 
 struct rt_ctx {
@@ -54,6 +65,8 @@ struct rt_ctx {
   bool has_scene = false, has_camera = false;
   rtc::DScene scene{};
   rtc::DCamera camera{};
+  unsigned trees = 0;  // RT_TREE_* present for the committed scene
+  int n_wide[2] = {0, 0};  // 8-wide / 4-wide node counts
   rtc::FlatItems flat{};  // box list of scenes with <= FLAT_MAX primitives (flat.n = 0: none)
   rt_camera camera_host{};
   // scene storage

@@ -1166,16 +1166,6 @@ inline int nblk(size_t n, int b) { return (int)((n + b - 1) / b); }
 //   meshes up to 500 k records (bunny): 8-wide tree, per-lane if-if loop — 4-5 dependent steps instead of 12,
 //      +13 % over the binary if-if loop;
 //   larger (soups): binary tree, if-if loop at 64 registers — latency bound, 32 warps/SM beat fewer, fatter steps.
-int trav_variant(const rt_ctx *ctx) {
-  const char *e = getenv("RT_TRAV");
-  int dflt = ctx->scene.n_recs <= 4096 ? 1 : (ctx->scene.n_recs < 500000 ? 17 : 0);
-  if (ctx->scene.n_recs <= 64 && !ctx->scene.has_spheres) dflt = 18;
-  if (ctx->flat.n > 0) dflt = 20;  // <= 32 primitives: box list (rt_flat.cuh), +37 % on Cornell, +20 % on birthday
-  int v = e ? atoi(e) : dflt;
-  if (v == 20 && ctx->flat.n == 0) v = dflt;  // no box list for this scene
-  if (v == 23 && ctx->flat.n == 0) v = dflt;
-  return (v < 0 || v > 23) ? dflt : v;
-}
 
 int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
   if (!ctx) {
@@ -1194,6 +1184,36 @@ int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
 }
 }  // namespace
 
+int rtc::trav_variant(const rt_ctx *ctx) {
+  const char *e = getenv("RT_TRAV");
+  int dflt = ctx->scene.n_recs <= 4096 ? 1 : (ctx->scene.n_recs < 500000 ? 17 : 0);
+  if (ctx->scene.n_recs <= 64 && !ctx->scene.has_spheres) dflt = 18;
+  if (ctx->flat.n > 0) dflt = 20;  // <= 32 primitives: box list (rt_flat.cuh), +37 % on Cornell, +20 % on birthday
+  int v = e ? atoi(e) : dflt;
+  if (v == 20 && ctx->flat.n == 0) v = dflt;  // no box list for this scene
+  if (v == 23 && ctx->flat.n == 0) v = dflt;
+  return (v < 0 || v > 23) ? dflt : v;
+}
+
+unsigned rtc::trees_for_trav(int trav) {
+  switch (trav) {
+    case 10: case 11: case 13: case 17: case 19: return RT_TREE_W8;
+    case 15: case 16: case 18: return RT_TREE_W4;
+    case 21: return RT_TREE_C4;
+    case 22: return RT_TREE_C8;
+    default: return 0u;
+  }
+}
+unsigned rtc::trees_for_mode(int mode) {
+  switch (mode) {
+    case 8: case 9: return RT_TREE_W8;
+    case 11: return RT_TREE_W4;
+    case 13: return RT_TREE_C4;
+    case 14: return RT_TREE_C8;
+    default: return 0u;
+  }
+}
+
 extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t n, double t_from, double t_to, int mode,
                                        rt_hit *d_hits, void *stream) {
   int rc = check_ready(ctx, false, "rt_trace_closest");
@@ -1204,6 +1224,8 @@ extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t
   }
   if (n == 0) return RT_OK;
   RT_CUDA(cudaSetDevice(ctx->device));
+  rc = ensure_trees(ctx, trees_for_mode(mode), (cudaStream_t)stream);
+  if (rc) return rc;
   if (mode == 12 && ctx->flat.n == 0 && ctx->scene.n_recs > 0) {
     set_error("rt_trace_closest: mode 12 (box list) needs a scene of at most 32 primitives");
     return RT_ERR_INVALID;
@@ -1348,6 +1370,10 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     fused = env ? strcmp(env, "wavefront") != 0 : true;
   }
   uint32_t iterations = 0, launches = 0;
+  if (fused) {  // a variant selected by RT_TRAV after the commit: derive its tree now (outside the timed region)
+    int rc_t = ensure_trees(ctx, trees_for_trav(trav_variant(ctx)), st);
+    if (rc_t) return rc_t;
+  }
   RT_CUDA(cudaEventRecord(ctx->ev0, st));
   if (fused) {
     dim3 grid((p->width + 15) / 16, (p->height + 7) / 8);
