@@ -15,6 +15,7 @@ RT_RENDER_PROFILE = 2
 RT_RENDER_FUSED = 4
 RT_RENDER_SORT = 8
 RT_RENDER_WAVEFRONT = 16
+RT_RENDER_SPLIT = 32
 
 material_dtype = np.dtype(
     {

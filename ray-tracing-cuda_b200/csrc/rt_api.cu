@@ -55,8 +55,12 @@ extern "C" int rt_ctx_destroy(rt_ctx *c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   DevBuf *bufs[] = {&c->nodes, &c->wnodes, &c->wnodes4, &c->cnodes8, &c->cnodes4, &c->recs, &c->recs_seq, &c->face_uv, &c->face_uv_seq, &c->mats, &c->textures,
-                    &c->tex_pixels, &c->counters, &c->accum_tmp, &c->rgb_tmp, &c->rgb8_tmp, &c->rays_tmp, &c->hits_tmp};
+                    &c->tex_pixels, &c->counters, &c->accum_tmp, &c->rgb_tmp, &c->rgb8_tmp, &c->rays_tmp, &c->hits_tmp, &c->slice_sums};
   for (DevBuf *b : bufs) b->release();
+  for (cudaStream_t s : c->slice_st)
+    if (s) cudaStreamDestroy(s);
+  for (cudaEvent_t e : c->slice_ev)
+    if (e) cudaEventDestroy(e);
   for (DevBuf &b : c->scratch) b.release();
   for (DevBuf &b : c->wf) b.release();
   for (void *p : c->tex_allocs) cudaFree(p);

@@ -1147,6 +1147,16 @@ __global__ void k_resolve(const float *__restrict__ accum, int64_t n, int spp_to
   if (rgb8) rgb8[i] = (uint8_t)(c * 255);
 }
 
+// RT_RENDER_SPLIT: adds the sums of slices 1..S-1 to the image in slice order, so that the result is the one of S
+// consecutive rt_render calls over the sample sub-ranges (slice 0 has already been added by its own kernel).
+__global__ void k_slice_sum(float *__restrict__ accum, const float *__restrict__ sums, int64_t n, int n_extra) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float c = accum[i];
+  for (int z = 0; z < n_extra; z++) c += sums[(int64_t)z * n + i];
+  accum[i] = c;
+}
+
 }  // namespace rtc
 
 // =================================================================================================
@@ -1382,6 +1392,46 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     // (profiles/r01_d_occupancy_sweep.txt): 6 for small scenes, 8 for >= 500k records (latency bound), else 5
     const char *mb = getenv("RT_MINB");
     int minb = mb ? atoi(mb) : (ctx->scene.n_recs <= 4096 ? 6 : (ctx->scene.n_recs >= 500000 ? 8 : 5));
+    // RT_RENDER_SPLIT: an image of fewer than 8 waves of blocks (spheres 400x225: 725 blocks on 888 slots, one wave whose
+    // length is the slowest warp's 16 samples) is rendered as S sample slices on S streams, so that the block scheduler
+    // has S times the blocks of 1/S the length to balance.  Slice sums are added in slice order: the image is the one
+    // of S consecutive calls over [begin + z*chunk, begin + (z+1)*chunk).
+    int S = 1, chunk = p->spp_count;
+    if ((p->flags & RT_RENDER_SPLIT) && p->spp_count >= 2) {
+      int n_sm = 148;
+      cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, ctx->device);
+      const long long blocks = (long long)grid.x * grid.y, slots = (long long)n_sm * minb;
+      const char *es = getenv("RT_SPLIT");
+      const char *ew = getenv("RT_SPLIT_WAVES");
+      const long long waves = ew ? atoll(ew) : 16;  // measured on spheres 400x225x16: 8 slices 1338, 16 slices 1400 Msamples/s
+      long long want = es ? atoll(es) : (blocks >= 8 * slots ? 1 : (waves * slots + blocks - 1) / blocks);
+      const char *em = getenv("RT_SPLIT_MINCHUNK");
+      const int min_chunk = em ? std::max(1, atoi(em)) : 1;
+      want = std::min<long long>(std::min<long long>(want, rt_ctx::kMaxSlices), p->spp_count / min_chunk);
+      if (want > 1) {
+        chunk = (p->spp_count + (int)want - 1) / (int)want;
+        S = (p->spp_count + chunk - 1) / chunk;
+      }
+    }
+    const RenderArgs a_all = a;
+    float *const accum_all = d_accum_rgb;
+    const cudaStream_t st_all = st;
+    if (S > 1) {
+      for (int z = 0; z < S; z++)
+        if (!ctx->slice_ev[z]) RT_CUDA(cudaEventCreateWithFlags(&ctx->slice_ev[z], cudaEventDisableTiming));
+      for (int z = 0; z + 1 < S; z++)
+        if (!ctx->slice_st[z]) RT_CUDA(cudaStreamCreateWithFlags(&ctx->slice_st[z], cudaStreamNonBlocking));
+      RT_CUDA(ctx->slice_sums.reserve((size_t)(S - 1) * n * 12));
+      RT_CUDA(cudaMemsetAsync(ctx->slice_sums.p, 0, (size_t)(S - 1) * n * 12, st_all));
+      RT_CUDA(cudaEventRecord(ctx->slice_ev[0], st_all));
+    }
+    for (int z = 0; z < S; z++) {
+      RenderArgs a = a_all;
+      a.spp_begin = a_all.spp_begin + z * chunk;
+      a.spp_end = std::min(a_all.spp_end, a.spp_begin + chunk);
+      float *d_accum_rgb = z ? ctx->slice_sums.as<float>() + (size_t)(z - 1) * n * 3 : accum_all;
+      const cudaStream_t st = z ? ctx->slice_st[z - 1] : st_all;
+      if (z) RT_CUDA(cudaStreamWaitEvent(st, ctx->slice_ev[0], 0));
 #define RT_FUSED_CASE(T)                                                                               \
   case T:                                                                                              \
     if (stats_on)                                                                                      \
@@ -1532,10 +1582,17 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
       default:
       RT_FUSED_CASE(4)
     }
+      if (z) {
+        RT_CUDA(cudaEventRecord(ctx->slice_ev[z], st));
+        RT_CUDA(cudaStreamWaitEvent(st_all, ctx->slice_ev[z], 0));
+      }
+    }
 #undef RT_FUSED_CASE
+    if (S > 1)
+      k_slice_sum<<<nblk(n * 3, 256), 256, 0, st_all>>>(accum_all, ctx->slice_sums.as<float>(), (int64_t)n * 3, S - 1);
     RT_CUDA(cudaGetLastError());
-    launches = 1;
-    iterations = 1;
+    launches = S > 1 ? S + 1 : 1;
+    iterations = S;  // sample slices (1: no split)
   } else {
     rc = render_wavefront(ctx, a, stats_on, (p->flags & RT_RENDER_SORT) != 0, d_accum_rgb, ctr, st, &iterations, &launches);
     if (rc) return rc;

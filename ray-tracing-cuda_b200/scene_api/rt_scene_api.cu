@@ -481,7 +481,7 @@ void RenderWorld(curandState **d_states, Camera **d_camera, HitableList **d_worl
   p.spp_begin = spp_begin;
   p.spp_count = local_spp;
   p.max_depth = o.max_depth;
-  p.flags = RT_RENDER_CLEAR;
+  p.flags = RT_RENDER_CLEAR | RT_RENDER_SPLIT;  // small images: concurrent sample slices (rtcore.h)
   p.seed = o.seed;
   rt_render_stats rs;
   float *accum = reinterpret_cast<float *>(*d_image);

@@ -4,6 +4,7 @@ draws, same arithmetic); the one exception is sphere u,v (acosf/atan2f differ be
 glibc's libm by design), so image-textured spheres are compared by mismatch fraction."""
 import math
 
+import os
 import numpy as np
 import pytest
 
@@ -263,6 +264,43 @@ def test_render_kernel_variants_bit_exact(ctx, name, hw, spp, monkeypatch):
         got, _, st = ctx.render_host(H, W, spp, seed=99, flags=abi.RT_RENDER_FUSED)
         assert (got.view(np.uint32) == want.view(np.uint32)).all(), trav
         assert (st.samples, st.rays, st.rays_ref_equiv) == tuple(int(x) for x in cnt), trav
+
+
+@pytest.mark.parametrize("name,hw,spp", [("spheres", (54, 96), 8), ("cornell_box", (72, 128), 7)])
+def test_render_split_sample_slices(ctx, name, hw, spp):
+    """RT_RENDER_SPLIT (what Main / DistributedMain pass): a small image is rendered as S concurrent sample slices on S
+    streams and the slice sums are added in slice order, so the image is bit-identical to S consecutive calls over
+    the sub-ranges (oracle run the same way), with the counters of the whole range.  Large images are not split."""
+    s, cam, o = _setup(ctx, name)
+    H, W = hw
+    _, cnt = o.render_product(H, W, 0, spp, 77)
+    # scene default (box list on Cornell) and the binary while-while loop with the automatic slice count (one sample per
+    # slice at these sizes), then a forced count of 3 (ragged last slice for 7 and 8 samples)
+    for trav, forced in ((None, None), ("1", None), (None, "3")):
+        env = {"RT_TRAV": trav, "RT_SPLIT": forced}
+        for k, v in env.items():
+            if v is not None:
+                os.environ[k] = v
+        try:
+            got, _, st = ctx.render_host(H, W, spp, seed=77, flags=abi.RT_RENDER_FUSED | abi.RT_RENDER_SPLIT)
+        finally:
+            for k in env:
+                os.environ.pop(k, None)
+        S = st.iterations
+        assert 1 < S <= 16 and st.kernel_launches == S + 1, (S, st.kernel_launches)
+        assert forced is None or S == int(forced)
+        chunk = -(-spp // S)
+        want = None
+        for z in range(S):
+            n = min(chunk, spp - z * chunk)
+            want, _ = o.render_product(H, W, z * chunk, n, 77, accum=want)
+        assert (got.view(np.uint32) == want.view(np.uint32)).all(), (trav, S)
+        assert (st.samples, st.rays, st.rays_ref_equiv) == tuple(int(x) for x in cnt)
+    # one sample per pixel and full-size frames stay whole
+    _, _, st = ctx.render_host(H, W, 1, seed=77, flags=abi.RT_RENDER_SPLIT)
+    assert st.iterations == 1 and st.kernel_launches == 1
+    _, _, st = ctx.render_host(1080, 1920, 4, seed=77, flags=abi.RT_RENDER_SPLIT)
+    assert st.iterations == 1 and st.kernel_launches == 1
 
 
 def test_render_textured_sphere_close(ctx):
