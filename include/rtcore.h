@@ -208,10 +208,13 @@ enum {
   RT_RENDER_SORT = 8,      /* wavefront: material-sorted shade queues (one Scatter/Emit body per warp) instead of one queue;
                               same sums, measured 6-9 % slower (profiles/r01_t_wavefront_sorted_queues.txt) */
   RT_RENDER_WAVEFRONT = 16, /* force the wavefront pipeline (logic/shade -> extend over compacted queues) */
-  RT_RENDER_SPLIT = 32      /* fused kernel, images of fewer than 8 waves of thread blocks (e.g. 400x225): render the
-                               sample range as S <= 16 concurrent slices (about 16 waves of blocks in all) of chunk = ceil(spp_count/S) samples and add
-                               the slice sums in slice order.  The image equals S consecutive rt_render calls over
-                               [spp_begin + z*chunk, ...); rt_render_stats.iterations reports S (1: not split). */
+  RT_RENDER_SPLIT = 32      /* fused kernel: render the sample range as S <= 32 concurrent slices of
+                               chunk = ceil(spp_count/S) samples (side streams) and add the slice sums in slice order.
+                               Used for images of fewer than 8 waves of thread blocks (e.g. 400x225: S chosen for
+                               about 16 waves) and for meshes behind a tree (4 k - 500 k records: S = min(32, spp_count);
+                               the frame otherwise ends in a long tail of the blocks that cover the mesh).  The image
+                               equals S consecutive rt_render calls over [spp_begin + z*chunk, ...);
+                               rt_render_stats.iterations reports S (1: not split).  Holds (S-1) frames of scratch. */
 };
 
 /* Replaces the PathTracing<<<>>> launch with post_processing=false (ray_tracing.cu:56-85,

@@ -79,7 +79,7 @@ struct rt_ctx {
   rtc::DevBuf wf[16];  // wavefront path state
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
   // RT_RENDER_SPLIT: side streams of the sample slices, fork / join events, per-slice sums (created on first use)
-  static constexpr int kMaxSlices = 16;
+  static constexpr int kMaxSlices = 32;
   cudaStream_t slice_st[kMaxSlices - 1] = {};
   cudaEvent_t slice_ev[kMaxSlices] = {};
   rtc::DevBuf slice_sums;

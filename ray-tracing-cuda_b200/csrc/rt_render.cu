@@ -1404,10 +1404,18 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
       const char *es = getenv("RT_SPLIT");
       const char *ew = getenv("RT_SPLIT_WAVES");
       const long long waves = ew ? atoll(ew) : 16;  // measured on spheres 400x225x16: 8 slices 1338, 16 slices 1400 Msamples/s
-      long long want = es ? atoll(es) : (blocks >= 8 * slots ? 1 : (waves * slots + blocks - 1) / blocks);
+      long long want = blocks >= 8 * slots ? 1 : (waves * slots + blocks - 1) / blocks;
+      // Meshes behind a tree (4 k - 500 k records): block cost follows the image (bunny 1080p: 1.17 rays per sample on
+      // average, an order of magnitude more on the mesh), so a frame ends with a long tail of heavy blocks whatever the
+      // wave count - measured 77 % of the bunny frame (S = 1 / 2 / 4 / 8 / 16 / 32: 2 785 / 4 541 / 6 636 / 8 575 / 10 033 /
+      // 10 784 Msamples/s).  As many slices as there are: the tail shrinks by S.  Not for the box-list scenes (Cornell
+      // -2 % at 16, -5 % at 32 slices) nor the soups (uniform images: 423 -> 384 at 16), profiles/r01_ab_sample_slices.txt.
+      if (ctx->flat.n == 0 && ctx->scene.n_recs > 4096 && ctx->scene.n_recs < 500000) want = rt_ctx::kMaxSlices;
+      if (es) want = atoll(es);
       const char *em = getenv("RT_SPLIT_MINCHUNK");
       const int min_chunk = em ? std::max(1, atoi(em)) : 1;
       want = std::min<long long>(std::min<long long>(want, rt_ctx::kMaxSlices), p->spp_count / min_chunk);
+      want = std::min<long long>(want, 1 + (long long)((2ull << 30) / (n * 12)));  // slice sums: at most 2 GiB
       if (want > 1) {
         chunk = (p->spp_count + (int)want - 1) / (int)want;
         S = (p->spp_count + chunk - 1) / chunk;
