@@ -113,3 +113,43 @@ def test_sample_partition_and_reduce_two_gloo_ranks(tmp_path):
     outs = [p.communicate(timeout=240) for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
     assert "GLOO_OK" in outs[0][0]
+
+
+def test_image_writers_round_trip(tmp_path):
+    """rt_write_ppm / rt_write_pfm / rt_write_jpeg (the WriteImage replacement, utils.cu:87-96): PPM and PFM
+    read back exactly, the baseline JPEG at quality 100 decodes (PIL) to within a few levels of the input,
+    and a bad path is an error code, not an abort."""
+    rng = np.random.default_rng(5)
+    h, w = 37, 53  # not multiples of the 8x8 JPEG block: exercises edge padding
+    yy, xx = np.mgrid[0:h, 0:w]
+    rgb8 = np.stack([(xx * 255 // (w - 1)), (yy * 255 // (h - 1)), ((xx + yy) * 255 // (h + w - 2))], -1).astype(np.uint8)
+
+    p = str(tmp_path / "a.ppm")
+    rt.write_image(p, rgb8)
+    raw = open(p, "rb").read()
+    head = f"P6\n{w} {h}\n255\n".encode()
+    assert raw.startswith(b"P6") and len(raw) >= w * h * 3
+    assert np.array_equal(np.frombuffer(raw[-w * h * 3:], np.uint8).reshape(h, w, 3), rgb8)
+    assert raw[: len(raw) - w * h * 3].split() == head.split()
+
+    f = rng.standard_normal((h, w, 3)).astype(np.float32)
+    p = str(tmp_path / "a.pfm")
+    rt.write_pfm(p, f)
+    raw = open(p, "rb").read()
+    toks = raw[: len(raw) - w * h * 12].split()
+    assert toks[0] == b"PF" and [int(toks[1]), int(toks[2])] == [w, h] and float(toks[3]) < 0  # little endian
+    back = np.frombuffer(raw[-w * h * 12:], "<f4").reshape(h, w, 3)[::-1]  # PFM rows are bottom-to-top
+    assert np.array_equal(back.view(np.uint32), f.view(np.uint32))
+
+    PIL = pytest.importorskip("PIL.Image")
+    p = str(tmp_path / "a.jpeg")
+    rt.write_image(p, rgb8)
+    dec = np.asarray(PIL.open(p).convert("RGB"))
+    assert dec.shape == rgb8.shape
+    err = np.abs(dec.astype(np.int32) - rgb8.astype(np.int32))
+    assert err.mean() < 2.0 and err.max() <= 12, (err.mean(), err.max())
+
+    with pytest.raises(rt.RtError):
+        rt.write_image(str(tmp_path / "no_such_dir" / "a.ppm"), rgb8)
+    with pytest.raises(rt.RtError):
+        rt.write_pfm(str(tmp_path / "no_such_dir" / "a.pfm"), f)
