@@ -1,0 +1,128 @@
+"""Hand-derived known answers for the closest-hit query ("unit sphere at origin, axis-aligned unit
+triangle, t == t_to, det ~ eps").  The expected values are worked out on paper from the reference's formulas
+(sphere.cu:11-44, utils.cu:49-85, hitable_list.cu:7-25) — they pin the oracle independently of oracle/_ref,
+and the same table is then asked of the reference's own sources (when built) and of the CUDA path.
+
+Sphere, centre 0, radius 1, ray (0,0,-3) -> +z:  a = 1, b = -6, c = 8, disc = 4, roots t = 2 and t = 4.
+Triangle (0,0,0) (1,0,0) (0,1,0), ray (x,y,-1) -> +z:  pvec = (-1,0,0), det = -1, u = x, v = y, t = 1,
+geometric normal (0,0,1) flipped against the ray to (0,0,-1)."""
+import math
+
+import numpy as np
+import pytest
+
+import checkers as ck
+
+scenes = ck.pkg.scenes
+abi = ck.pkg.abi
+rt = ck.pkg
+
+INF = float("inf")
+MISS = None
+
+
+def _mats():
+    return np.stack([scenes._mat(abi.RT_MAT_LAMBERTIAN, (0.5, 0.5, 0.5))])
+
+
+def _sphere_scene():
+    return abi.SceneData(np.stack([scenes._hit(abi.RT_HIT_SPHERE, 0, [[0, 0, 0]], radius=1.0)]), _mats())
+
+
+def _triangle_scene(p1x=1.0):
+    return abi.SceneData(np.stack([scenes._hit(abi.RT_HIT_TRIANGLE, 0, [[0, 0, 0], [p1x, 0, 0], [0, 1, 0]])]), _mats())
+
+
+def _two_triangles_same_t():
+    # two coincident triangles: HitableList::Hit keeps the FIRST on a tie (strict '<', hitable_list.cu:18)
+    tri = [[0, 0, 0], [1, 0, 0], [0, 1, 0]]
+    return abi.SceneData(np.stack([scenes._hit(abi.RT_HIT_TRIANGLE, 0, tri), scenes._hit(abi.RT_HIT_TRIANGLE, 0, tri)]), _mats())
+
+
+BELOW_1 = float(np.nextafter(np.float32(1), np.float32(0)))
+ABOVE_1 = float(np.nextafter(np.float32(1), np.float32(2)))
+
+# (scene factory, ray origin, ray direction, t_from, t_to, expected): expected = MISS or
+# dict(t=, normal=, obj=, u=, v=) — only the listed keys are checked; t and normal exactly.
+CASES = [
+    # --- sphere.cu:11-44 -------------------------------------------------------------------------------------
+    ("sphere near root", _sphere_scene, (0, 0, -3), (0, 0, 1), 1e-3, INF, dict(t=2.0, normal=(0, 0, -1), obj=0)),
+    ("sphere t == t_to is inside the range", _sphere_scene, (0, 0, -3), (0, 0, 1), 1e-3, 2.0, dict(t=2.0, normal=(0, 0, -1))),
+    ("sphere t == t_from is inside the range", _sphere_scene, (0, 0, -3), (0, 0, 1), 2.0, INF, dict(t=2.0)),
+    ("sphere near root cut off, far root beyond t_to", _sphere_scene, (0, 0, -3), (0, 0, 1), 1e-3, 1.999, MISS),
+    ("sphere far root when the near one is before t_from", _sphere_scene, (0, 0, -3), (0, 0, 1), 2.5, INF, dict(t=4.0, normal=(0, 0, 1))),
+    ("sphere from the centre: far root", _sphere_scene, (0, 0, 0), (0, 0, 1), 1e-3, INF, dict(t=1.0, normal=(0, 0, 1))),
+    ("sphere behind the ray", _sphere_scene, (0, 0, 3), (0, 0, 1), 1e-3, INF, MISS),
+    ("sphere missed, negative discriminant", _sphere_scene, (2, 0, -3), (0, 0, 1), 1e-3, INF, MISS),
+    # (a tangent ray has no paper answer: c goes through the float sqrt of length() and back, sphere.cu:15-16,
+    #  so its discriminant is +-1e-7 rather than 0 — left to the bit-exact comparisons against oracle/_ref)
+    # --- utils.cu:49-85 --------------------------------------------------------------------------------------
+    ("triangle interior", _triangle_scene, (0.25, 0.25, -1), (0, 0, 1), 1e-3, INF, dict(t=1.0, normal=(0, 0, -1), u=0.25, v=0.25, obj=0)),
+    ("triangle from behind: normal faces the ray", _triangle_scene, (0.25, 0.25, 1), (0, 0, -1), 1e-3, INF, dict(t=1.0, normal=(0, 0, 1), u=0.25, v=0.25)),
+    ("triangle hypotenuse u + v == 1 is inside", _triangle_scene, (0.5, 0.5, -1), (0, 0, 1), 1e-3, INF, dict(t=1.0, u=0.5, v=0.5)),
+    ("triangle edge u == 0 is inside", _triangle_scene, (0, 0.5, -1), (0, 0, 1), 1e-3, INF, dict(t=1.0, v=0.5)),
+    ("triangle edge v == 0 is inside", _triangle_scene, (0.5, 0, -1), (0, 0, 1), 1e-3, INF, dict(t=1.0, u=0.5)),
+    ("triangle vertex 0", _triangle_scene, (0, 0, -1), (0, 0, 1), 1e-3, INF, dict(t=1.0)),
+    ("triangle u + v > 1", _triangle_scene, (0.75, 0.5, -1), (0, 0, 1), 1e-3, INF, MISS),
+    ("triangle u < 0", _triangle_scene, (-0.25, 0.5, -1), (0, 0, 1), 1e-3, INF, MISS),
+    ("triangle v < 0", _triangle_scene, (0.5, -0.25, -1), (0, 0, 1), 1e-3, INF, MISS),
+    ("triangle t == t_to is inside the range", _triangle_scene, (0.25, 0.25, -1), (0, 0, 1), 1e-3, 1.0, dict(t=1.0)),
+    ("triangle t one ulp beyond t_to", _triangle_scene, (0.25, 0.25, -1), (0, 0, 1), 1e-3, BELOW_1, MISS),
+    ("triangle t == t_from is inside the range", _triangle_scene, (0.25, 0.25, -1), (0, 0, 1), 1.0, INF, dict(t=1.0)),
+    ("triangle t one ulp before t_from", _triangle_scene, (0.25, 0.25, -1), (0, 0, 1), ABOVE_1, INF, MISS),
+    ("triangle behind the ray", _triangle_scene, (0.25, 0.25, 1), (0, 0, 1), 1e-3, INF, MISS),
+    ("triangle parallel ray: det == 0", _triangle_scene, (-1, 0.25, 0), (1, 0, 0), 1e-3, INF, MISS),
+    ("triangle |det| = 5e-8 < eps = 1e-7 is rejected", lambda: _triangle_scene(5e-8), (1e-8, 0.25, -1), (0, 0, 1), 1e-3, INF, MISS),
+    ("triangle |det| = 2e-7 > eps is tested", lambda: _triangle_scene(2e-7), (5e-8, 0.25, -1), (0, 0, 1), 1e-3, INF,
+     dict(t_close=1.0, normal=(0, 0, -1), obj=0)),
+    # --- hitable_list.cu:7-25 --------------------------------------------------------------------------------
+    ("two coincident triangles: the first appended wins the tie", _two_triangles_same_t, (0.25, 0.25, -1), (0, 0, 1), 1e-3, INF,
+     dict(t=1.0, obj=0)),
+]
+
+
+def _check(trace, label):
+    for name, make, o, d, t_from, t_to, want in CASES:
+        ray = np.array([list(o) + list(d)], np.float32)
+        h = trace(make(), ray, t_from, t_to)[0]
+        where = f"{label}: {name}"
+        if want is MISS:
+            assert h["obj"] == -1, (where, h)
+            continue
+        assert h["obj"] >= 0, (where, "expected a hit", h)
+        if "t" in want:
+            assert float(h["t"]) == want["t"], (where, float(h["t"]).hex())
+        if "t_close" in want:
+            assert math.isclose(float(h["t"]), want["t_close"], rel_tol=1e-5), (where, float(h["t"]))
+        if "obj" in want:
+            assert h["obj"] == want["obj"], (where, h["obj"])
+        if "normal" in want:
+            assert np.array_equal(h["normal"] + np.float32(0), np.asarray(want["normal"], np.float32)), (where, h["normal"])
+        for k in ("u", "v"):
+            if k in want:
+                assert float(h[k]) == want[k], (where, k, float(h[k]))
+        assert h["material"] == 0, where
+
+
+def test_oracle_known_answers():
+    _check(lambda s, r, a, b: ck.OracleScene(s).trace(r, a, b, quirks=1), "oracle")
+    _check(lambda s, r, a, b: ck.OracleScene(s).trace(r, a, b, quirks=0), "oracle, exact visibility")
+
+
+def test_reference_sources_known_answers():
+    """The same table asked of the reference's own .cu sources compiled for the host (oracle/_ref)."""
+    if not ck.have_ref():
+        pytest.skip("oracle/_ref not built (no /root/reference on this machine)")
+    _check(lambda s, r, a, b: ck.RefScene.from_scene(s).trace(r, a, b), "reference")
+
+
+@pytest.mark.gpu
+def test_cuda_core_known_answers():
+    ctx = rt.Context(0)
+    try:
+        def trace(s, r, a, b):
+            ctx.commit(s)
+            return ctx.trace_closest(r, a, b)
+        _check(trace, "librtcore")
+    finally:
+        ctx.close()
