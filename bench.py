@@ -242,6 +242,8 @@ def main():
     ap.add_argument("--strategy", default="auto", choices=["auto", "fused", "wavefront"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-split", action="store_true", help="do not pass RT_RENDER_SPLIT (diagnostic)")
+    ap.add_argument("--ordered", action="store_true",
+                    help="pass RT_RENDER_ORDERED (experimental: heaviest tile first on meshes; off by default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
@@ -272,6 +274,8 @@ def main():
     flags = {"auto": 0, "fused": rt.abi.RT_RENDER_FUSED, "wavefront": rt.abi.RT_RENDER_WAVEFRONT}[args.strategy]
     if not args.no_split:  # what Main / DistributedMain pass: small images render as concurrent sample slices
         flags |= rt.abi.RT_RENDER_SPLIT
+    if args.ordered:
+        flags |= rt.abi.RT_RENDER_ORDERED
     stream = torch.cuda.current_stream()
     sp = stream.cuda_stream
     accum = torch.zeros(H, W, 3, device=dev)
@@ -404,7 +408,7 @@ def main():
            "config": {"workload": label, "partition": f"spp/{world}",
                       "l2": "flushed between timed steps (256 MiB write)", "strategy": args.strategy,
                       "prims": build.n_prims, "nodes": build.n_nodes,
-                      "sample_slices": int(st.iterations) if fused_run else 1},
+                      "sample_slices": int(st.iterations) if fused_run else 1, "ordered_tiles": bool(args.ordered)},
            "mrays_per_s": float(rays[0].item()) / ms / 1e3, "mrays_ref_equiv_per_s": float(rays[1].item()) / ms / 1e3,
            "rays_per_sample": float(rays[0].item()) / samples,
            "e2e": {"value": samples / ms_e2e / 1e3, "unit": "Msamples/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,

@@ -208,13 +208,19 @@ enum {
   RT_RENDER_SORT = 8,      /* wavefront: material-sorted shade queues (one Scatter/Emit body per warp) instead of one queue;
                               same sums, measured 6-9 % slower (profiles/r01_t_wavefront_sorted_queues.txt) */
   RT_RENDER_WAVEFRONT = 16, /* force the wavefront pipeline (logic/shade -> extend over compacted queues) */
-  RT_RENDER_SPLIT = 32      /* fused kernel: render the sample range as S <= 32 concurrent slices of
+  RT_RENDER_SPLIT = 32,     /* fused kernel: render the sample range as S <= 32 concurrent slices of
                                chunk = ceil(spp_count/S) samples (side streams) and add the slice sums in slice order.
                                Used for images of fewer than 8 waves of thread blocks (e.g. 400x225: S chosen for
                                about 16 waves) and for meshes behind a tree (4 k - 500 k records: S = min(32, spp_count);
                                the frame otherwise ends in a long tail of the blocks that cover the mesh).  The image
                                equals S consecutive rt_render calls over [spp_begin + z*chunk, ...);
                                rt_render_stats.iterations reports S (1: not split).  Holds (S-1) frames of scratch. */
+  RT_RENDER_ORDERED = 64    /* fused kernel over the 8-wide tree (meshes): thread blocks are issued heaviest tile
+                               first — a 1-ray-per-pixel probe counts the node steps of every 16x8 tile, the tiles are
+                               sorted by that cost and the render kernel maps blockIdx through the sorted list, so the
+                               frame does not end on the few blocks that cover the mesh.  Same image bit for bit.
+                               EXPERIMENTAL, off by default: added after the round-1 GPU budget was spent, unmeasured
+                               (composes with RT_RENDER_SPLIT; ignored for other traversals). */
 };
 
 /* Replaces the PathTracing<<<>>> launch with post_processing=false (ray_tracing.cu:56-85,

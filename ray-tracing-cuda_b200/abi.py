@@ -16,6 +16,7 @@ RT_RENDER_FUSED = 4
 RT_RENDER_SORT = 8
 RT_RENDER_WAVEFRONT = 16
 RT_RENDER_SPLIT = 32
+RT_RENDER_ORDERED = 64
 
 material_dtype = np.dtype(
     {

@@ -55,7 +55,7 @@ extern "C" int rt_ctx_destroy(rt_ctx *c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   DevBuf *bufs[] = {&c->nodes, &c->wnodes, &c->wnodes4, &c->cnodes8, &c->cnodes4, &c->recs, &c->recs_seq, &c->face_uv, &c->face_uv_seq, &c->mats, &c->textures,
-                    &c->tex_pixels, &c->counters, &c->accum_tmp, &c->rgb_tmp, &c->rgb8_tmp, &c->rays_tmp, &c->hits_tmp, &c->slice_sums};
+                    &c->tex_pixels, &c->counters, &c->accum_tmp, &c->rgb_tmp, &c->rgb8_tmp, &c->rays_tmp, &c->hits_tmp, &c->slice_sums, &c->tile_cost, &c->tile_order};
   for (DevBuf *b : bufs) b->release();
   for (cudaStream_t s : c->slice_st)
     if (s) cudaStreamDestroy(s);

@@ -83,6 +83,9 @@ struct rt_ctx {
   cudaStream_t slice_st[kMaxSlices - 1] = {};
   cudaEvent_t slice_ev[kMaxSlices] = {};
   rtc::DevBuf slice_sums;
+  // RT_RENDER_ORDERED: per-tile probe cost and the tile list sorted by it
+  rtc::DevBuf tile_cost, tile_order;
+  std::vector<uint32_t> tile_cost_host, tile_order_host;
   rt_build_stats build_stats{};
   // nccl (loaded lazily)
   void *nccl_comm = nullptr;

@@ -24,6 +24,8 @@ struct RenderArgs {
   int32_t spp_begin, spp_end;
   int32_t max_depth;
   uint32_t k0, k1;
+  int32_t tiles_x = 0;                   // RT_RENDER_ORDERED: tiles per image row ...
+  const uint32_t *tile_order = nullptr;  // ... and the tile each block renders (heaviest first)
 };
 
 // rt_hit of a query result (what HitRecord carries, hitable.cuh:13-17)
@@ -290,13 +292,20 @@ static __device__ __noinline__ Hit trav_finish_call(const DScene &s, Trav tv, Ra
 // ---- fused kernel: one thread per pixel, paths regenerated in registers ---------------------------
 // Each lane runs its pixel's samples in increasing order and starts the next sample the moment the
 // current path ends, so a warp stays full until its pixels run out of samples.  No queue traffic.
-template <bool STATS, int TRAV, int MINB = 5>
+// ORDERED (RT_RENDER_ORDERED): a 1-D grid whose block b renders tile a.tile_order[b] (heaviest tile first).
+template <bool STATS, int TRAV, int MINB = 5, bool ORDERED = false>
 __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera cam, RenderArgs a, float *__restrict__ accum,
                                                       RenderCounters *ctr,
                                                       typename FlatParamT<TRAV == 20 || TRAV == 23>::type fl = {}) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
-  const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+  int bx = blockIdx.x, by = blockIdx.y;
+  if constexpr (ORDERED) {
+    const uint32_t tile = a.tile_order[blockIdx.x];
+    bx = (int)(tile % (uint32_t)a.tiles_x);
+    by = (int)(tile / (uint32_t)a.tiles_x);
+  }
+  const int j = bx * 16 + (warp & 1) * 8 + (lane & 7);
+  const int i = by * 8 + (warp >> 1) * 4 + (lane >> 3);
   const bool inside = i < a.height && j < a.width;
   const int idx = i * a.width + j;
   PathKey pk;
@@ -386,6 +395,30 @@ __global__ void __launch_bounds__(128, MINB) k_render_fused(DScene s, DCamera ca
   flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims);
 }
 
+
+// RT_RENDER_ORDERED probe: one primary ray per pixel (the first sample of the call) through the 8-wide tree; the
+// cost of a 16x8 tile is the node steps + record tests of its 128 rays (a sky or ground tile: a few steps; a tile
+// on the mesh: tens per ray, and its paths go on to bounce).  Only the ORDER of the blocks depends on it.
+__global__ void __launch_bounds__(128) k_tile_cost(DScene s, DCamera cam, RenderArgs a, uint32_t *__restrict__ cost) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+  const int i = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+  uint32_t c = 0;
+  if (i < a.height && j < a.width) {
+    PathKey pk;
+    pk.pixel = (uint32_t)(i * a.width + j);
+    pk.k0 = a.k0;
+    pk.k1 = a.k1;
+    pk.sample = (uint32_t)a.spp_begin;
+    const RayQ ray = camera_sample(cam, i, j, a.height, a.width, pk);
+    TravStats ts;
+    ts.nodes = ts.prims = 0;
+    const Hit h = world_hit_wide_ifif<true, 8>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
+    c = (uint32_t)ts.nodes + (uint32_t)ts.prims + (h.rec != REC_NONE && h.rec != REC_SKY ? 64u : 0u);
+  }
+  c = __reduce_add_sync(0xffffffffu, c);
+  if (lane == 0 && c) atomicAdd(&cost[blockIdx.y * gridDim.x + blockIdx.x], c);
+}
 
 // ---- warp-synchronous kernel: the fused kernel over the wide tree / with cooperative record tests ----
 // Same path bookkeeping as k_render_fused (one lane per pixel, samples in increasing order, a path is
@@ -1421,6 +1454,28 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
         S = (p->spp_count + chunk - 1) / chunk;
       }
     }
+    // RT_RENDER_ORDERED: probe, sort the tiles by cost on the host (16 200 tiles at 1080p; one small round trip per
+    // call, before the first slice is launched), hand the list to the render kernel.
+    const bool ordered = (p->flags & RT_RENDER_ORDERED) && trav == 17 && !stats_on && (minb == 5 || minb == 6);
+    if (ordered) {
+      const uint32_t n_tiles = grid.x * grid.y;
+      RT_CUDA(ctx->tile_cost.reserve((size_t)n_tiles * 4));
+      RT_CUDA(ctx->tile_order.reserve((size_t)n_tiles * 4));
+      RT_CUDA(cudaMemsetAsync(ctx->tile_cost.p, 0, (size_t)n_tiles * 4, st));
+      k_tile_cost<<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctx->tile_cost.as<uint32_t>());
+      ctx->tile_cost_host.resize(n_tiles);
+      ctx->tile_order_host.resize(n_tiles);
+      RT_CUDA(cudaMemcpyAsync(ctx->tile_cost_host.data(), ctx->tile_cost.p, (size_t)n_tiles * 4, cudaMemcpyDeviceToHost, st));
+      RT_CUDA(cudaStreamSynchronize(st));
+      for (uint32_t t = 0; t < n_tiles; t++) ctx->tile_order_host[t] = t;
+      const uint32_t *cost = ctx->tile_cost_host.data();
+      std::stable_sort(ctx->tile_order_host.begin(), ctx->tile_order_host.end(),
+                       [cost](uint32_t x, uint32_t y) { return cost[x] > cost[y]; });
+      RT_CUDA(cudaMemcpyAsync(ctx->tile_order.p, ctx->tile_order_host.data(), (size_t)n_tiles * 4, cudaMemcpyHostToDevice, st));
+      RT_CUDA(cudaStreamSynchronize(st));  // the host list is reused by the next call
+      a.tiles_x = (int32_t)grid.x;
+      a.tile_order = ctx->tile_order.as<uint32_t>();
+    }
     const RenderArgs a_all = a;
     float *const accum_all = d_accum_rgb;
     const cudaStream_t st_all = st;
@@ -1493,7 +1548,13 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     k_render_fused<false, T, 8><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);             \
   else                                                                                                           \
     k_render_fused<false, T><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
-      if (trav == 16) {
+      if (ordered) {  // trav 17, heaviest tile first
+        const dim3 ogrid(grid.x * grid.y);
+        if (minb == 6)
+          k_render_fused<false, 17, 6, true><<<ogrid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+        else
+          k_render_fused<false, 17, 5, true><<<ogrid, 128, 0, st>>>(ctx->scene, ctx->camera, a, d_accum_rgb, ctr);
+      } else if (trav == 16) {
         RT_WIDE_IFIF_CASE(16)
       } else if (trav == 17) {
         RT_WIDE_IFIF_CASE(17)
@@ -1599,7 +1660,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
     if (S > 1)
       k_slice_sum<<<nblk(n * 3, 256), 256, 0, st_all>>>(accum_all, ctx->slice_sums.as<float>(), (int64_t)n * 3, S - 1);
     RT_CUDA(cudaGetLastError());
-    launches = S > 1 ? S + 1 : 1;
+    launches = (S > 1 ? S + 1 : 1) + (ordered ? 1 : 0);
     iterations = S;  // sample slices (1: no split)
   } else {
     rc = render_wavefront(ctx, a, stats_on, (p->flags & RT_RENDER_SORT) != 0, d_accum_rgb, ctr, st, &iterations, &launches);

@@ -126,3 +126,27 @@ def test_cuda_core_known_answers():
         _check(trace, "librtcore")
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+def test_cost_ordered_tiles_same_image():
+    """RT_RENDER_ORDERED (experimental; heaviest 16x8 tile first, from a 1-ray-per-pixel probe) only permutes the thread
+    blocks: image and counters are those of the raster-order launch bit for bit, alone and under sample slices, and at a
+    size whose last tile row / column is ragged."""
+    ctx = rt.Context(0)
+    try:
+        s, c = scenes.bunny(scenes.bunny_mesh(9000))
+        ctx.commit(s)
+        ctx.set_camera(rt.core.camera_look_at(c))
+        for (H, W, spp) in ((67, 125, 6), (135, 240, 4)):
+            base = abi.RT_RENDER_FUSED
+            want, _, st0 = ctx.render_host(H, W, spp, seed=9, flags=base)
+            got, _, st1 = ctx.render_host(H, W, spp, seed=9, flags=base | abi.RT_RENDER_ORDERED)
+            assert np.array_equal(want.view(np.uint32), got.view(np.uint32))
+            assert st1.rays == st0.rays and st1.samples == st0.samples
+            assert st1.kernel_launches == st0.kernel_launches + 1  # the probe
+            want_s, _, _ = ctx.render_host(H, W, spp, seed=9, flags=base | abi.RT_RENDER_SPLIT)
+            got_s, _, _ = ctx.render_host(H, W, spp, seed=9, flags=base | abi.RT_RENDER_SPLIT | abi.RT_RENDER_ORDERED)
+            assert np.array_equal(want_s.view(np.uint32), got_s.view(np.uint32))
+    finally:
+        ctx.close()
