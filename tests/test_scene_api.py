@@ -131,3 +131,74 @@ def test_distributed_main_two_ranks_matches_one(tmp_path):
     assert st2["world_size"] == 2 and st2["local_spp"] == 5
     d = np.abs(one.astype(int) - two.astype(int))
     assert d.max() <= 1 and (d > 0).mean() < 0.05, (d.max(), (d > 0).mean())
+
+
+_OBJ = """# quads, a pentagon, every corner syntax, negative indices, two materials (one textured, revisited)
+mtllib a.mtl
+v 0 0 0
+v 1 0 0
+v 1 1 0
+v 0 1 0
+v 0.5 1.5 0.25
+vt 0 0
+vt 1 0
+vt 1 1
+vt 0 1
+vn 0 0 1
+usemtl red
+f 1/1 2/2 3/3 4/4
+usemtl plain
+f 1//1 2//1 3//1
+f -5/-4/1 -4/-3/1 -3/-2/1 -2/-1/1 -1/1/1
+usemtl red
+f 1 3 5
+"""
+
+
+@pytest.mark.skipif(not _have_reference(), reason="glm / stb come from the reference's third_party by include path")
+def test_model_obj_import(tmp_path):
+    """Model<HasTexCoord> (SURVEY §8 f1; model.h:14-114 without assimp): fan triangulation of polygons, v / v/vt / v//vn /
+    v/vt/vn corners, negative indices, one mesh per material in order of first use (texture slot = mesh index),
+    host-side transform, the 60- / 36-byte Face layouts, and the diffuse texture looked up at
+    <model dir>/../textures/<basename of map_Kd> (model.h:80-88) and expanded to RGBA8."""
+    subprocess.run(["make", "-s", "-C", API, "build/libray_tracing.a"], check=True)
+    exe = str(tmp_path / "obj_dump")
+    ref = "/root/reference/third_party"
+    subprocess.run(["nvcc", "-std=c++17", "-O1", "-gencode", "arch=compute_100a,code=sm_100a", "--expt-relaxed-constexpr",
+                    "--expt-extended-lambda", "-w", "-I" + API, f"-I{ref}/glm", f"-I{ref}/stb", "-o", exe,
+                    os.path.join(ROOT, "tests", "obj_dump.cu"), os.path.join(BUILD, "libray_tracing.a"),
+                    "-L" + os.path.dirname(API), "-lrtcore", "-Xlinker", "-rpath", "-Xlinker", os.path.dirname(API)], check=True)
+    (tmp_path / "r" / "models").mkdir(parents=True)
+    (tmp_path / "r" / "textures").mkdir()
+    (tmp_path / "r" / "models" / "a.obj").write_text(_OBJ)
+    (tmp_path / "r" / "models" / "a.mtl").write_text("newmtl red\nKd 1 0 0\nmap_Kd some/dir/tex.ppm\nnewmtl plain\nKd 1 1 1\n")
+    (tmp_path / "r" / "textures" / "tex.ppm").write_bytes(b"P6\n2 1\n255\n" + bytes([1, 2, 3, 10, 11, 12]))
+    out = subprocess.run([exe, str(tmp_path / "r" / "models" / "a.obj")], capture_output=True, text=True, check=True).stdout
+    lines = out.strip().split("\n")
+
+    v = np.array([[0, 0, 0], [1, 0, 0], [1, 1, 0], [0, 1, 0], [0.5, 1.5, 0.25]], np.float32) * np.float32(2) + \
+        np.array([1, 2, 3], np.float32)  # the tool's transform: translate(1,2,3) * scale(2); exact in float
+    vt = np.array([[0, 0], [1, 0], [1, 1], [0, 1]], np.float32)
+    z = None  # no texcoord on the corner -> (0, 0)
+    red = [((0, 0), (1, 1), (2, 2)), ((0, 0), (2, 2), (3, 3)), ((0, z), (2, z), (4, z))]
+    plain = [((0, z), (1, z), (2, z)), ((0, 0), (1, 1), (2, 2)), ((0, 0), (2, 2), (3, 3)), ((0, 0), (3, 3), (4, 0))]
+
+    def expect(faces, with_uv):
+        rows = []
+        for f in faces:
+            for vi, ti in f:
+                uv = vt[ti] if ti is not None else np.zeros(2, np.float32)
+                rows.append(list(v[vi]) + (list(uv) if with_uv else []))
+        return np.array(rows, np.float32)
+
+    assert lines[0].split() == ["2", "2"]
+    at = 1
+    for with_uv in (True, False):
+        for faces, tex_id in ((red, 0), (plain, -1)):
+            assert lines[at].split() == ["mesh", str(len(faces)), str(tex_id)], lines[at]
+            got = np.array([[float.fromhex(x) for x in l.split()] for l in lines[at + 1: at + 1 + 3 * len(faces)]], np.float32)
+            assert np.array_equal(got, expect(faces, with_uv)), (with_uv, tex_id)
+            at += 1 + 3 * len(faces)
+    assert lines[at].split() == ["tex", "1", "2", "8", "1", "2", "3", "255", "10", "11", "12", "255"], lines[at]
+    assert lines[at + 1].split() == ["tex", "0", "0", "0"]
+    assert lines[at + 2].split() == ["sizes", "60", "36"]  # bvh.cuh:35-65: Face<true> / Face<false>
