@@ -166,3 +166,21 @@ def test_pow_rounding_is_the_only_sphere_difference():
     assert np.all(a["obj"][bad] >= 0) and np.all(s.hitables["type"][a["obj"][bad]] == abi.RT_HIT_SPHERE)
     assert np.all(np.abs(a["t"][bad] - b["t"][bad]) <= 1e-13 * np.abs(b["t"][bad]))
     print("sphere t differing from libm-pow build:", len(bad), "of", len(rays))
+
+
+def test_render_defocus_camera_with_reference_streams():
+    """The thin-lens branch of Camera::RayAt (camera.cu:57-77; no shipped scene uses it): two extra XORWOW draws
+    per sample through DiskRand (camera.cu:74-77), origin moved on the lens.  The restatement equals the reference's
+    PathTracing on the host pixel for pixel, and the lens does change the image."""
+    s, c, _ = scenes.spheres(10086, "rtl")
+    spec = scenes.CameraSpec(c.position, c.look_at, c.up, c.fov, c.aspect, aperture=0.6, focus_distance=10.0)
+    cam = ck.camera_from_spec(ck.oracle_lib().ro_camera_look_at, spec)
+    assert cam["is_defocus"] == 1 and float(cam["lens_radius"]) == 0.3
+    o, ref = ck.OracleScene(s, cam), ck.RefScene.from_scene(s, cam)
+    H, W, spp = 27, 48, 3
+    a = ref.render(H, W, spp, post=0)
+    b, _ = o.render_reference(H, W, spp, 0, quirks=1, post=0)  # ref_scene_create seeds its streams with 0
+    assert (a.view(np.uint32) == b.view(np.uint32)).all()
+    pin = ck.OracleScene(s, ck.camera_from_spec(ck.oracle_lib().ro_camera_look_at, c))
+    p, _ = pin.render_reference(H, W, spp, 0, quirks=1, post=0)
+    assert (p != b).any()
