@@ -248,3 +248,19 @@ def hits_equal(a, b, fields=("t", "obj", "sub", "u", "v", "normal", "material"))
             d = d.any(axis=1)
         bad |= d
     return np.nonzero(bad)[0]
+
+
+def textured_mesh_scene(n_faces=3000, seed=7):
+    """A Face<true> mesh (bvh.cuh:35-48: per-corner texcoords, interpolated with the hit's barycentrics) behind a
+    Lambertian(ImageTexture) — texcoords in [-0.5, 1.5] so that the wrap rule of image_texture.cu:9-38 is exercised —
+    plus the sky.  No shipped scene has one (birthday textures a sphere), so this is the only coverage of that path."""
+    scenes, abi = pkg.scenes, pkg.abi
+    rng = np.random.RandomState(seed)
+    f9 = scenes.soup_mesh(n_faces, seed=5) * np.float32(2.0)
+    uv = rng.uniform(-0.5, 1.5, (len(f9), 6)).astype(np.float32)
+    tex = rng.randint(0, 256, (16, 32, 4)).astype(np.uint8)
+    mats = [scenes._mat(abi.RT_MAT_LAMBERTIAN, (0, 0, 0), texture=0), scenes._mat(abi.RT_MAT_SKY)]
+    hs = [scenes._hit(abi.RT_HIT_MESH, 0, mesh=0), scenes._hit(abi.RT_HIT_SKY, 1)]
+    scene = abi.SceneData(np.stack(hs), np.stack(mats), meshes=[np.concatenate([f9, uv], 1)], textures=[tex])
+    spec = scenes.CameraSpec((0, 0, -6), (0, 0, 0), (0, 1, 0), 0.7, 16 / 9)
+    return scene, spec

@@ -184,3 +184,20 @@ def test_render_defocus_camera_with_reference_streams():
     pin = ck.OracleScene(s, ck.camera_from_spec(ck.oracle_lib().ro_camera_look_at, c))
     p, _ = pin.render_reference(H, W, spp, 0, quirks=1, post=0)
     assert (p != b).any()
+
+
+def test_textured_mesh_face_texcoords():
+    """Face<true>::Hit (bvh.cuh:35-48) + ImageTexture::Value (image_texture.cu:9-15): interpolated texcoords of the
+    hit and the image rendered through them equal the reference's, bit for bit."""
+    s, spec = ck.textured_mesh_scene()
+    cam = ck.camera_from_spec(ck.oracle_lib().ro_camera_look_at, spec)
+    o, ref = ck.OracleScene(s, cam), ck.RefScene.from_scene(s, cam)
+    rays = ck.random_rays(30000, 5, -4, 4, toward=(0, 0, 0), spread=1.5)
+    a, b = o.trace(rays, quirks=1), ref.trace(rays)
+    on_mesh = a["obj"] == 0
+    assert on_mesh.mean() > 0.1 and (a["u"][on_mesh] != 0).any() and (a["u"][on_mesh] < 0).any() and (a["u"][on_mesh] > 1).any()
+    assert len(ck.hits_equal(a, b)) == 0
+    H, W, spp = 36, 64, 3
+    ia = ref.render(H, W, spp, post=0)
+    ib, _ = o.render_reference(H, W, spp, 0, quirks=1, post=0)
+    assert (ia.view(np.uint32) == ib.view(np.uint32)).all()

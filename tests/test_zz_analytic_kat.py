@@ -181,3 +181,30 @@ def test_render_defocus_camera_bit_exact_vs_oracle():
             assert (st.samples, st.rays, st.rays_ref_equiv) == tuple(int(x) for x in cnt)
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+def test_textured_mesh_bit_exact_vs_oracle():
+    """Face<true> meshes through the CUDA path: texcoords interpolated from the per-record uv table (tree order and
+    list order), raw-memory point/wrap texture fetch.  Hits (u, v included) and image equal the oracle's."""
+    ctx = rt.Context(0)
+    try:
+        s, spec = ck.textured_mesh_scene()
+        cam = rt.core.camera_look_at(spec)
+        ctx.commit(s)
+        ctx.set_camera(cam)
+        o = ck.OracleScene(s, cam)
+        rays = ck.random_rays(30000, 5, -4, 4, toward=(0, 0, 0), spread=1.5)
+        want = o.trace(rays, quirks=0)
+        assert (want["obj"] == 0).mean() > 0.1
+        for mode in (0, 1):  # tree traversal, sequential scan
+            bad = ck.hits_equal(ctx.trace_closest(rays, mode=mode), want)
+            assert len(bad) == 0, (mode, len(bad))
+        H, W, spp = 54, 96, 4
+        img, cnt = o.render_product(H, W, 0, spp, 99)
+        for flags in (abi.RT_RENDER_FUSED, abi.RT_RENDER_WAVEFRONT):
+            got, _, st = ctx.render_host(H, W, spp, seed=99, flags=flags)
+            assert np.array_equal(got.view(np.uint32), img.view(np.uint32)), flags
+            assert (st.samples, st.rays, st.rays_ref_equiv) == tuple(int(x) for x in cnt)
+    finally:
+        ctx.close()
