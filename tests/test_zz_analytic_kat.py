@@ -5,7 +5,11 @@ and the same table is then asked of the reference's own sources (when built) and
 
 Sphere, centre 0, radius 1, ray (0,0,-3) -> +z:  a = 1, b = -6, c = 8, disc = 4, roots t = 2 and t = 4.
 Triangle (0,0,0) (1,0,0) (0,1,0), ray (x,y,-1) -> +z:  pvec = (-1,0,0), det = -1, u = x, v = y, t = 1,
-geometric normal (0,0,1) flipped against the ray to (0,0,-1)."""
+geometric normal (0,0,1) flipped against the ray to (0,0,-1).
+
+The -m gpu tests at the end of this file (known answers, RT_RENDER_ORDERED, thin-lens render, textured mesh) were written
+after the round-1 GPU budget was spent: their oracle halves are verified on the CPU, their CUDA halves have not run yet.
+The file name sorts last on purpose."""
 import math
 
 import numpy as np
