@@ -9,6 +9,7 @@
 //   ref_cuda <spheres|cornell_box|bunny|birthday|mesh> H W spp reps [--faces f.bin] [--tex f.bin h w]
 //            [--camera px py pz lx ly lz fov aspect] [--image out.bin] [--rays rays.bin hits.bin]
 //            [--seed s] [--post 0|1]
+//   ref_cuda powkat 0 0 0 0     (known-answer test of pow(x, 2) / pow(x, 0.5) against x * x / sqrt(x))
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -106,6 +107,36 @@ __global__ void TraceRays(HitableList *world, const float *rays, long n, double 
   out[i] = h;
 }
 
+// Known-answer test of the two pow() calls that decide a sphere hit (sphere.cu:13-21: pow(len, 2), pow(disc, 0.5);
+// SURVEY 7.3-1): is CUDA's pow(x, 2) bitwise x * x and pow(x, 0.5) bitwise sqrt(x) on the operand ranges of the
+// scenes?  Operands: lengths in [1e-3, 4e3] as float -> double (what length() returns), discriminants in [0, 1e9]
+// as doubles with full mantissas, log-uniform, from a 64-bit LCG.  counts = {n, pow2 != x*x, pow.5 != sqrt, max ulp
+// distance of each}.
+__global__ void PowKat(unsigned long long n, unsigned long long *counts) {
+  unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  unsigned long long bad2 = 0, badh = 0, ulp2 = 0, ulph = 0;
+  for (; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+    unsigned long long z = i * 6364136223846793005ULL + 1442695040888963407ULL;
+    z ^= z >> 29;
+    z *= 0xbf58476d1ce4e5b9ULL;
+    z ^= z >> 32;
+    double u = (double)(z >> 11) * (1.0 / 9007199254740992.0);  // [0, 1)
+    double len = (double)(float)exp(log(1e-3) + u * (log(4e3) - log(1e-3)));
+    double disc = exp(log(1e-12) + u * (log(1e9) - log(1e-12)));
+    double a = pow(len, 2), b = len * len;
+    double c = pow(disc, 0.5), d = sqrt(disc);
+    long long da = __double_as_longlong(a) - __double_as_longlong(b), dc = __double_as_longlong(c) - __double_as_longlong(d);
+    if (da) bad2++;
+    if (dc) badh++;
+    ulp2 = max(ulp2, (unsigned long long)(da < 0 ? -da : da));
+    ulph = max(ulph, (unsigned long long)(dc < 0 ? -dc : dc));
+  }
+  if (bad2) atomicAdd(counts + 1, bad2);
+  if (badh) atomicAdd(counts + 2, badh);
+  atomicMax(counts + 3, ulp2);
+  atomicMax(counts + 4, ulph);
+}
+
 static std::vector<char> read_file(const char *path) {
   std::ifstream f(path, std::ios::binary);
   if (!f) {
@@ -121,6 +152,17 @@ int main(int argc, char **argv) {
     return 2;
   }
   std::string scene = argv[1];
+  if (scene == "powkat") {  // ref_cuda powkat _ _ _ _ : prints the KAT counts
+    unsigned long long n = 1ull << 26, h[5] = {0, 0, 0, 0, 0}, *d;
+    CK(cudaMalloc(&d, sizeof(h)));
+    CK(cudaMemset(d, 0, sizeof(h)));
+    PowKat<<<148 * 8, 256>>>(n, d);
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost));
+    printf("{\"powkat_operands\": %llu, \"pow2_ne_mul\": %llu, \"powhalf_ne_sqrt\": %llu, \"pow2_max_ulp\": %llu, "
+           "\"powhalf_max_ulp\": %llu}\n", n, h[1], h[2], h[3], h[4]);
+    return 0;
+  }
   int H = atoi(argv[2]), W = atoi(argv[3]), spp = atoi(argv[4]), reps = atoi(argv[5]);
   const char *faces_path = nullptr, *tex_path = nullptr, *image_path = nullptr, *rays_path = nullptr, *hits_path = nullptr;
   int tex_h = 0, tex_w = 0, post = 0;

@@ -272,10 +272,6 @@ def main():
         rdist.bind_nccl(ctx)
     count, begin = rdist.partition(spp, rank, world)
     flags = {"auto": 0, "fused": rt.abi.RT_RENDER_FUSED, "wavefront": rt.abi.RT_RENDER_WAVEFRONT}[args.strategy]
-    if not args.no_split:  # what Main / DistributedMain pass: small images render as concurrent sample slices
-        flags |= rt.abi.RT_RENDER_SPLIT
-    if args.ordered:
-        flags |= rt.abi.RT_RENDER_ORDERED
     stream = torch.cuda.current_stream()
     sp = stream.cuda_stream
     accum = torch.zeros(H, W, 3, device=dev)
@@ -355,8 +351,8 @@ def main():
     h2d = int(scene.hitables.nbytes + scene.materials.nbytes + sum(m.nbytes for m in scene.meshes) +
               sum(t.nbytes for t in scene.textures) + 96)
     kern_ms = st.render_ms
-    fused_run = st.kernel_launches == 1 or st.kernel_launches == st.iterations + 1  # S slices + k_slice_sum
-    kernel = "k_render_fused" if fused_run else "k_wf_extend"
+    fused_run = st.iterations == 0
+    kernel = "k_render" if fused_run else "k_wf_extend"
     sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
     props = torch.cuda.get_device_properties(local)
     # Roofline of the dominant kernel.  The scene (nodes + records) is L1/L2 resident, so the bound is SM
@@ -408,7 +404,7 @@ def main():
            "config": {"workload": label, "partition": f"spp/{world}",
                       "l2": "flushed between timed steps (256 MiB write)", "strategy": args.strategy,
                       "prims": build.n_prims, "nodes": build.n_nodes,
-                      "sample_slices": int(st.iterations) if fused_run else 1, "ordered_tiles": bool(args.ordered)},
+                      "chunk_samples": int(st.chunk_samples), "work_items": int(st.work_items)},
            "mrays_per_s": float(rays[0].item()) / ms / 1e3, "mrays_ref_equiv_per_s": float(rays[1].item()) / ms / 1e3,
            "rays_per_sample": float(rays[0].item()) / samples,
            "e2e": {"value": samples / ms_e2e / 1e3, "unit": "Msamples/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,

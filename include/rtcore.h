@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 2
+#define RT_ABI_VERSION 3
 
 enum {
   RT_OK = 0,
@@ -143,15 +143,14 @@ typedef struct rt_render_stats {
   uint64_t samples;       /* camera samples started */
   uint64_t rays;          /* closest-hit queries executed by this core */
   uint64_t rays_ref_equiv;/* queries the reference loop would issue for the same paths (ray_tracing.cu:22) */
-  uint64_t node_visits;   /* only when built with RT_STATS=1, else 0 */
-  uint64_t prim_tests;
-  uint32_t iterations;    /* wavefront iterations */
+  uint64_t node_visits;   /* box tests; only with RT_RENDER_PROFILE, else 0 */
+  uint64_t prim_tests;    /* record tests; only with RT_RENDER_PROFILE, else 0 */
+  uint32_t iterations;    /* wavefront iterations (0: the persistent path kernel) */
   uint32_t kernel_launches;
   float render_ms;        /* device time, CUDA events on `stream` */
-  float extend_ms, shade_ms; /* per-stage device time when profiling is enabled, else 0 */
-  float reserved_;
-  uint64_t sched_iters;   /* vote kernel, RT_RENDER_PROFILE only: warp scheduling iterations ...      */
-  uint64_t sched_lanes;   /* ... and lanes that executed in them (sched_lanes / (32*sched_iters) = SIMT use) */
+  uint32_t chunk_samples; /* path kernel: samples per (pixel, chunk) sub-unit of the work distribution */
+  uint32_t work_items;    /* path kernel: (tile, chunk group) items drawn from the global counter */
+  uint32_t reserved_;
 } rt_render_stats;
 
 /* ---- entry points -------------------------------------------------------------------------- */
@@ -180,9 +179,10 @@ int rt_camera_look_at(const float position[3], const float look_at[3], const flo
 /* Parity hook: replaces HitableList::Hit (hitable_list.cu:7-25) on explicit rays.
  * rays = n x 6 floats (position xyz, direction xyz); the direction is used as stored (callers
  * pass Ray::direction_, i.e. already normalized by Ray::Ray, ray.cu:8-11).
- * mode 0: unified-BVH traversal (product path); mode 1: sequential scan over every primitive in
- * list order; modes 2..7: the traversal variants 0..5 of the render kernels (diagnostics: all modes
- * must return identical hits). */
+ * mode 0: the traversal the committed scene renders with (product path); mode 1: sequential scan over every
+ * primitive in list order, as HitableList::Hit executes it; modes 2..5: one specific traversal of the render kernel
+ * (2 binary tree if-if, 3 binary tree while-while, 4 8-wide tree, 5 box list — scenes of at most 32 primitives only).
+ * All modes must return identical hits. */
 int rt_trace_closest_host(rt_ctx *ctx, const float *h_rays, int64_t n, double t_from, double t_to,
                           int mode, rt_hit *h_hits);
 int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t n, double t_from, double t_to,
@@ -203,37 +203,49 @@ typedef struct rt_render_params {
 enum {
   RT_RENDER_DEFAULT = 0,
   RT_RENDER_CLEAR = 1,     /* zero the accumulation buffer first */
-  RT_RENDER_PROFILE = 2,   /* per-stage event timing (serialises stages) */
-  RT_RENDER_FUSED = 4,     /* force the fused persistent-path kernel (paths regenerated in registers) */
+  RT_RENDER_PROFILE = 2,   /* count box / record tests (rt_render_stats.node_visits, prim_tests); slower */
+  RT_RENDER_FUSED = 4,     /* force the persistent path kernel (paths regenerated in registers; the default) */
   RT_RENDER_SORT = 8,      /* wavefront: material-sorted shade queues (one Scatter/Emit body per warp) instead of one queue;
                               same sums, measured 6-9 % slower (profiles/r01_t_wavefront_sorted_queues.txt) */
-  RT_RENDER_WAVEFRONT = 16, /* force the wavefront pipeline (logic/shade -> extend over compacted queues) */
-  RT_RENDER_SPLIT = 32,     /* fused kernel: render the sample range as S <= 32 concurrent slices of
-                               chunk = ceil(spp_count/S) samples (side streams) and add the slice sums in slice order.
-                               Used for images of fewer than 8 waves of thread blocks (e.g. 400x225: S chosen for
-                               about 16 waves) and for meshes behind a tree (4 k - 500 k records: S = min(32, spp_count);
-                               the frame otherwise ends in a long tail of the blocks that cover the mesh).  The image
-                               equals S consecutive rt_render calls over [spp_begin + z*chunk, ...);
-                               rt_render_stats.iterations reports S (1: not split).  Holds (S-1) frames of scratch. */
-  RT_RENDER_ORDERED = 64    /* fused kernel over the 8-wide tree (meshes): thread blocks are issued heaviest tile
-                               first — a 1-ray-per-pixel probe counts the node steps of every 16x8 tile, the tiles are
-                               sorted by that cost and the render kernel maps blockIdx through the sorted list, so the
-                               frame does not end on the few blocks that cover the mesh.  Same image bit for bit.
-                               EXPERIMENTAL, off by default: added after the round-1 GPU budget was spent, unmeasured
-                               (composes with RT_RENDER_SPLIT; ignored for other traversals). */
+  RT_RENDER_WAVEFRONT = 16 /* force the wavefront pipeline (logic/shade -> extend over compacted queues) */
+  /* 32, 64: RT_RENDER_SPLIT / RT_RENDER_ORDERED of ABI 2 (sample slices on side streams, heaviest tile first) are gone:
+     the path kernel now draws (tile, sample chunk) work items from a global counter; the bits are ignored. */
 };
 
+/* Sampling contract (what makes an image reproducible): Philox4x32-10 keyed by `seed`; word w of the random stream
+ * of (pixel, global sample index) is word (w & 3) of block counter (pixel, sample, w >> 2, 0).  Words 0,1: pixel
+ * jitter (ray_tracing.cu:68-71); 2,3: lens sample (thin-lens cameras only, camera.cu:62-65); B+2k, B+2k+1 with B = 4
+ * (lens) or 2 (pinhole): the direction sample of the scatter at depth k — a uniform direction drawn without a
+ * rejection loop (same distribution as lambertian.cu:19-31 / metal.cu:27-36); Metal fuzz takes its radius from word 0
+ * of block (pixel, sample, 0x40000000 + k, 0).  uint32 -> (0, 1] as curand_uniform.
+ *
+ * Summation contract: the radiance of a sample is rounded once to a multiple of 2^-30 (|component| clamped to 2^32,
+ * NaN = 0) and the samples of a pixel are added as 64-bit integers.  Integer addition is exact, so a pixel's sum does
+ * not depend on the order or grouping of its samples: any split of the sample range over rt_render_fixed calls,
+ * work chunks or GPUs (rt_reduce_fixed) gives the same bits. */
+
 /* Replaces the PathTracing<<<>>> launch with post_processing=false (ray_tracing.cu:56-85,
- * utils.cu:220-221): adds the radiance SUM of the requested samples into d_accum_rgb
- * (height*width*3 floats, the reference's glm::vec3 image layout). */
+ * utils.cu:220-221): adds the radiance SUM of the requested samples (the fixed-point sum of this call, rounded to
+ * float once) into d_accum_rgb (height*width*3 floats, the reference's glm::vec3 image layout). */
 int rt_render(rt_ctx *ctx, const rt_render_params *params, float *d_accum_rgb,
               rt_render_stats *stats /*nullable*/, void *stream);
+
+/* The same launch accumulating into caller-owned exact sums: d_accum_fixed = height*width*3 int64, units of 2^-30
+ * (RT_RENDER_CLEAR zeroes it first).  This is the accumulation buffer Main / DistributedMain keep (utils.cu:140). */
+int rt_render_fixed(rt_ctx *ctx, const rt_render_params *params, int64_t *d_accum_fixed,
+                    rt_render_stats *stats /*nullable*/, void *stream);
 
 /* Replaces the post-processing tail of PathTracing (ray_tracing.cu:78-83) and the host loops in
  * GatherImageData / WriteImage (utils.cu:126-129, 87-96): out = sqrt(clamp(accum/spp_total,0,1));
  * either output may be NULL.  d_rgb8 gets trunc(out*255) like WriteImage. */
 int rt_resolve(rt_ctx *ctx, const float *d_accum_rgb, int height, int width, int spp_total,
                float *d_rgb /*nullable*/, uint8_t *d_rgb8 /*nullable*/, void *stream);
+
+/* The same from the exact sums; additionally writes the float sums (the reference's pre-post-processing image)
+ * when d_accum_rgb is not NULL. */
+int rt_resolve_fixed(rt_ctx *ctx, const int64_t *d_accum_fixed, int height, int width, int spp_total,
+                     float *d_accum_rgb /*nullable*/, float *d_rgb /*nullable*/, uint8_t *d_rgb8 /*nullable*/,
+                     void *stream);
 
 /* End-to-end convenience through host buffers: commit-independent render + resolve + D2H.
  * h_accum_rgb (nullable) receives the raw sums, h_rgb (nullable) the post-processed floats. */
@@ -248,6 +260,10 @@ int rt_get_workload(int rank, int world_size, int spp, int *spp_begin /*nullable
  * `nccl_comm` is an ncclComm_t passed as void*. */
 int rt_reduce(rt_ctx *ctx, void *nccl_comm, float *d_accum_rgb, int64_t n_floats, int root,
               void *stream);
+
+/* The same reduce on the exact sums (ncclInt64, SUM): the image of N ranks equals the image of one, bit for bit. */
+int rt_reduce_fixed(rt_ctx *ctx, void *nccl_comm, int64_t *d_accum_fixed, int64_t n_values, int root,
+                    void *stream);
 
 /* Communicator helpers for callers that have no ncclComm_t of their own (the reference ranks talk
  * through MPI_COMM_WORLD, utils.cu:118-125): rank 0 creates a 128-byte ncclUniqueId, the caller

@@ -15,8 +15,9 @@ RT_RENDER_PROFILE = 2
 RT_RENDER_FUSED = 4
 RT_RENDER_SORT = 8
 RT_RENDER_WAVEFRONT = 16
-RT_RENDER_SPLIT = 32
-RT_RENDER_ORDERED = 64
+# rt_trace_closest modes: the scene's render traversal, HitableList::Hit as a sequential scan, and each traversal by name
+TRACE_DEFAULT, TRACE_SEQUENTIAL, TRACE_IFIF, TRACE_WHILE_WHILE, TRACE_WIDE8, TRACE_BOX_LIST = range(6)
+FIXED_ONE = 1 << 30  # units of the exact radiance sums (rt_render_fixed)
 
 material_dtype = np.dtype(
     {
@@ -99,11 +100,9 @@ class RtRenderStats(C.Structure):
         ("iterations", C.c_uint32),
         ("kernel_launches", C.c_uint32),
         ("render_ms", C.c_float),
-        ("extend_ms", C.c_float),
-        ("shade_ms", C.c_float),
-        ("reserved_", C.c_float),
-        ("sched_iters", C.c_uint64),
-        ("sched_lanes", C.c_uint64),
+        ("chunk_samples", C.c_uint32),
+        ("work_items", C.c_uint32),
+        ("reserved_", C.c_uint32),
     ]
 
     def as_dict(self):

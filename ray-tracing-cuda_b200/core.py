@@ -43,7 +43,10 @@ def lib():
     L.rt_trace_closest_device.argtypes = [vp, vp, i64, f64, f64, C.c_int, vp, vp]
     L.rt_primary_rays_host.argtypes = [vp, C.c_int, C.c_int, vp]
     L.rt_render.argtypes = [vp, C.POINTER(abi.RtRenderParams), vp, C.POINTER(abi.RtRenderStats), vp]
+    L.rt_render_fixed.argtypes = [vp, C.POINTER(abi.RtRenderParams), vp, C.POINTER(abi.RtRenderStats), vp]
     L.rt_resolve.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp]
+    L.rt_resolve_fixed.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp]
+    L.rt_reduce_fixed.argtypes = [vp, vp, vp, i64, C.c_int, vp]
     L.rt_render_host.argtypes = [vp, C.POINTER(abi.RtRenderParams), vp, vp, C.POINTER(abi.RtRenderStats)]
     L.rt_get_workload.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]
     L.rt_reduce.argtypes = [vp, vp, vp, i64, C.c_int, vp]
@@ -53,7 +56,7 @@ def lib():
     L.rt_write_jpeg.argtypes = [C.c_char_p, C.c_int, C.c_int, vp, C.c_int]
     L.rt_write_ppm.argtypes = [C.c_char_p, C.c_int, C.c_int, vp]
     L.rt_write_pfm.argtypes = [C.c_char_p, C.c_int, C.c_int, vp]
-    if L.rt_abi_version() != 2:
+    if L.rt_abi_version() != 3:
         raise RtError("librtcore.so ABI version mismatch")
     _lib = L
     return L
@@ -140,6 +143,22 @@ class Context:
         st = abi.RtRenderStats()
         _check(lib().rt_render(self._h, C.byref(p), d_accum_ptr, C.byref(st), stream))
         return st
+
+    def render_fixed_device(self, d_fixed_ptr, height, width, spp_count, spp_begin=0, max_depth=10, seed=0, flags=0,
+                            stream=None):
+        """rt_render_fixed into caller-owned exact sums (int64 [H, W, 3] on the device, units of 2^-30)."""
+        p = self.params(height, width, spp_count, spp_begin, max_depth, seed, flags)
+        st = abi.RtRenderStats()
+        _check(lib().rt_render_fixed(self._h, C.byref(p), d_fixed_ptr, C.byref(st), stream))
+        return st
+
+    def resolve_fixed_device(self, d_fixed_ptr, height, width, spp_total, d_accum_ptr=None, d_rgb_ptr=None,
+                             d_rgb8_ptr=None, stream=None):
+        _check(lib().rt_resolve_fixed(self._h, d_fixed_ptr, height, width, spp_total, d_accum_ptr, d_rgb_ptr, d_rgb8_ptr,
+                                      stream))
+
+    def reduce_fixed(self, nccl_comm, d_fixed_ptr, n_values, root=0, stream=None):
+        _check(lib().rt_reduce_fixed(self._h, nccl_comm, d_fixed_ptr, n_values, root, stream))
 
     def resolve_device(self, d_accum_ptr, height, width, spp_total, d_rgb_ptr=None, d_rgb8_ptr=None, stream=None):
         _check(lib().rt_resolve(self._h, d_accum_ptr, height, width, spp_total, d_rgb_ptr, d_rgb8_ptr, stream))

@@ -22,6 +22,9 @@ using namespace rtc;
 extern "C" int rt_abi_version(void) { return RT_ABI_VERSION; }
 extern "C" const char *rt_last_error_string(void) { return g_err.c_str(); }
 
+extern "C" int rt_ctx_destroy(rt_ctx *c);
+extern "C" int rt_nccl_destroy(rt_ctx *ctx);
+
 extern "C" int rt_ctx_create(int device, rt_ctx **out) {
   if (!out) {
     set_error("rt_ctx_create: null out pointer");
@@ -43,9 +46,14 @@ extern "C" int rt_ctx_create(int device, rt_ctx **out) {
   RT_CUDA(cudaSetDevice(device));
   rt_ctx *c = new rt_ctx();
   c->device = device;
-  RT_CUDA(cudaEventCreate(&c->ev0));
-  RT_CUDA(cudaEventCreate(&c->ev1));
-  RT_CUDA(cudaEventCreate(&c->ev2));
+  cudaError_t ee = cudaEventCreate(&c->ev0);
+  if (ee == cudaSuccess) ee = cudaEventCreate(&c->ev1);
+  if (ee == cudaSuccess) ee = cudaEventCreate(&c->ev2);
+  if (ee == cudaSuccess) ee = cudaDeviceGetAttribute(&c->n_sm, cudaDevAttrMultiProcessorCount, device);
+  if (ee != cudaSuccess) {  // nothing half-built survives a failed create
+    rt_ctx_destroy(c);
+    return cuda_fail(ee, "rt_ctx_create");
+  }
   *out = c;
   return RT_OK;
 }
@@ -54,13 +62,11 @@ extern "C" int rt_ctx_destroy(rt_ctx *c) {
   if (!c) return RT_OK;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
-  DevBuf *bufs[] = {&c->nodes, &c->wnodes, &c->wnodes4, &c->cnodes8, &c->cnodes4, &c->recs, &c->recs_seq, &c->face_uv, &c->face_uv_seq, &c->mats, &c->textures,
-                    &c->tex_pixels, &c->counters, &c->accum_tmp, &c->rgb_tmp, &c->rgb8_tmp, &c->rays_tmp, &c->hits_tmp, &c->slice_sums, &c->tile_cost, &c->tile_order};
+  rt_nccl_destroy(c);  // a caller that forgot it does not leak the communicator
+  DevBuf *bufs[] = {&c->nodes, &c->wnodes, &c->recs, &c->recs_seq, &c->face_uv, &c->face_uv_seq, &c->mats, &c->textures,
+                    &c->tex_pixels, &c->counters, &c->accum_tmp, &c->fixed_tmp, &c->rgb_tmp, &c->rgb8_tmp, &c->rays_tmp,
+                    &c->hits_tmp};
   for (DevBuf *b : bufs) b->release();
-  for (cudaStream_t s : c->slice_st)
-    if (s) cudaStreamDestroy(s);
-  for (cudaEvent_t e : c->slice_ev)
-    if (e) cudaEventDestroy(e);
   for (DevBuf &b : c->scratch) b.release();
   for (DevBuf &b : c->wf) b.release();
   for (void *p : c->tex_allocs) cudaFree(p);
@@ -244,6 +250,28 @@ extern "C" int rt_reduce(rt_ctx *ctx, void *nccl_comm, float *d_accum_rgb, int64
   if (rc) return rc;
   RT_CUDA(cudaSetDevice(ctx->device));
   int r = g_nccl.Reduce(d_accum_rgb, d_accum_rgb, (size_t)n_floats, /*ncclFloat*/ 7, /*ncclSum*/ 0, root, comm,
+                        (cudaStream_t)stream);
+  if (r) return nccl_fail(r, "ncclReduce");
+  return RT_OK;
+}
+
+// The same reduce on the fixed-point sums (ncclInt64): integer addition is exact, so the image of N ranks is the
+// image one rank would have rendered, bit for bit, whatever the partition.
+extern "C" int rt_reduce_fixed(rt_ctx *ctx, void *nccl_comm, int64_t *d_accum_fixed, int64_t n_values, int root,
+                               void *stream) {
+  if (!ctx || !d_accum_fixed || n_values < 0) {
+    set_error("rt_reduce_fixed: bad argument");
+    return RT_ERR_INVALID;
+  }
+  void *comm = nccl_comm ? nccl_comm : ctx->nccl_comm;
+  if (!comm) {
+    set_error("rt_reduce_fixed: no NCCL communicator (pass one or call rt_nccl_init)");
+    return RT_ERR_INVALID;
+  }
+  int rc = nccl_load();
+  if (rc) return rc;
+  RT_CUDA(cudaSetDevice(ctx->device));
+  int r = g_nccl.Reduce(d_accum_fixed, d_accum_fixed, (size_t)n_values, /*ncclInt64*/ 4, /*ncclSum*/ 0, root, comm,
                         (cudaStream_t)stream);
   if (r) return nccl_fail(r, "ncclReduce");
   return RT_OK;

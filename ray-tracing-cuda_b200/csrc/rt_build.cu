@@ -334,63 +334,6 @@ __global__ void k_wide_expand(const float4 *__restrict__ nodes, const uint2 *__r
 }
 
 
-// Compact form of the wide nodes (rt_cwide.cuh; layout: CWideLayout in rt_device.cuh).  One thread per wide node.
-// origin = componentwise minimum of the child boxes; step per axis = the power of two 2^k with
-// 1.001 * extent <= 255 * 2^k; lo planes are rounded down and hi planes up to the grid with at least 1/1024 of a
-// step of slack (a plane exactly at the origin keeps q = 0: there the decoded plane IS the float it came from), so the
-// decoded box contains the float box with a margin far above the rounding of the traversal's two-FMA plane distance.
-// All grid arithmetic in double (exact: differences of floats divided by a power of two).
-template <int W>
-__global__ void k_wide_compress(const float4 *__restrict__ wnodes, int n_w, uint4 *__restrict__ cnodes) {
-  int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n_w) return;
-  using L = WideLayout<W>;
-  using C = CWideLayout<W>;
-  const float *f = reinterpret_cast<const float *>(wnodes + (size_t)L::F4 * t);
-  const uint32_t *u = reinterpret_cast<const uint32_t *>(f);
-  const uint32_t valid = u[7 * W];
-  uint32_t out[C::WORDS];
-  for (int i = 0; i < C::WORDS; i++) out[i] = 0u;
-  uint32_t ebits = 0;
-  for (int a = 0; a < 3; a++) {
-    float org = CUDART_INF_F, top = -CUDART_INF_F;
-    for (int i = 0; i < W; i++)
-      if (valid >> i & 1u) {
-        org = fminf(org, f[a * W + i]);
-        top = fmaxf(top, f[(3 + a) * W + i]);
-      }
-    if (!(org <= top)) org = top = 0.f;  // no valid child (never emitted) or NaN
-    const double ext = ((double)top - (double)org) * 1.001;
-    int k = -126;
-    if (ext > 0.0) {
-      frexp(ext / 255.0, &k);  // ext / 255 = m * 2^k, m in [0.5, 1)  =>  2^k >= ext / 255
-      if (k < -126) k = -126;
-    }
-    const double step = ldexp(1.0, k);
-    ebits |= (uint32_t)(k + 127) << (8 * a);
-    out[a] = __float_as_uint(org);
-    for (int i = 0; i < W; i++) {
-      uint32_t qlo = 255u, qhi = 0u;  // empty slot: inverted box
-      if (valid >> i & 1u) {
-        const double xl = ((double)f[a * W + i] - (double)org) / step;
-        const double xh = ((double)f[(3 + a) * W + i] - (double)org) / step;
-        double l = xl > 0.0 ? floor(xl - 1.0 / 1024) : 0.0;
-        double h = ceil(xh + 1.0 / 1024);
-        l = l < 0.0 ? 0.0 : (l > 255.0 ? 255.0 : l);
-        h = h < 0.0 ? 0.0 : (h > 255.0 ? 255.0 : h);
-        qlo = (uint32_t)l;
-        qhi = (uint32_t)h;
-      }
-      out[4 + (a * C::G) + (i >> 2)] |= qlo << (8 * (i & 3));
-      out[4 + ((3 + a) * C::G) + (i >> 2)] |= qhi << (8 * (i & 3));
-    }
-  }
-  out[3] = ebits | (valid << 24);
-  for (int i = 0; i < W; i++) out[C::REFW + i] = u[6 * W + i];
-  uint4 *o = cnodes + (size_t)C::U4 * t;
-  for (int q = 0; q < C::U4; q++) o[q] = make_uint4(out[4 * q], out[4 * q + 1], out[4 * q + 2], out[4 * q + 3]);
-}
-
 }  // namespace rtc
 
 // =================================================================================================
@@ -429,86 +372,56 @@ inline HostRec tri_rec(const float p0[3], const float p1[3], const float p2[3], 
 
 }  // namespace
 
-// Wide / compact trees are derived from the binary tree ON DEMAND: rt_scene_commit asks for the tree of the scene's
-// default traversal (none for the box list, the binary loops and the soups), rt_render / rt_trace_closest for the
-// tree of an explicitly selected variant.  The collapse runs level by level; its two queues live in scratch[6] / [7]
-// (bp_lo / bp_hi of the build, dead after k_emit and sized for one entry per build primitive).
-int rtc::ensure_trees(rt_ctx *ctx, unsigned need, cudaStream_t st) {
-  if (need & RT_TREE_C8) need |= RT_TREE_W8;
-  if (need & RT_TREE_C4) need |= RT_TREE_W4;
-  need &= ~ctx->trees;
-  if (!need || ctx->scene.n_recs <= 0) return RT_OK;
+// The 8-wide tree is derived from the binary tree ON DEMAND: rt_scene_commit builds it when the scene renders with it
+// (4 k - 500 k records), rt_trace_closest when mode 4 asks for it.  The collapse runs level by level; its two queues
+// live in scratch[6] / [7] (bp_lo / bp_hi of the build, dead after k_emit and sized for one entry per build primitive).
+int rtc::ensure_wide_tree(rt_ctx *ctx, cudaStream_t st) {
+  if (ctx->has_wide || ctx->scene.n_recs <= 0) return RT_OK;
   if ((size_t)ctx->scene.n_recs > (size_t)WLEAF_FIRST_MASK) {
-    set_error("wide trees: too many records for the wide-node leaf encoding");
+    set_error("wide tree: too many records for the wide-node leaf encoding");
     return RT_ERR_LIMIT;
   }
   DevBuf *S = ctx->scratch;
   RT_CUDA(S[10].reserve(32));
   uint32_t *cnt = S[10].as<uint32_t>();
-  for (int width = 8; width >= 4; width -= 4) {
-    const unsigned wbit = width == 8 ? RT_TREE_W8 : RT_TREE_W4, cbit = width == 8 ? RT_TREE_C8 : RT_TREE_C4;
-    DevBuf &wbuf = width == 8 ? ctx->wnodes : ctx->wnodes4;
-    if (need & wbit) {
-      const int f4 = width == 8 ? WideLayout<8>::F4 : WideLayout<4>::F4;
-      int n_w = 0;
-      for (int pass = 0; pass < 2; pass++) {
-        uint2 *in = S[6].as<uint2>(), *out = S[7].as<uint2>();
-        uint2 seed = make_uint2(0u, 0u);
-        uint32_t c[2] = {0u, 1u};
-        RT_CUDA(cudaMemcpyAsync(in, &seed, sizeof(seed), cudaMemcpyHostToDevice, st));
-        RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
-        int n_in = 1, levels = 0;
-        while (n_in > 0) {
-          const float4 *bn = ctx->nodes.as<float4>();
-          float4 *wn = pass ? wbuf.as<float4>() : nullptr;
-          if (width == 8) {
-            if (pass == 0) k_wide_expand<false, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
-            else k_wide_expand<true, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
-          } else {
-            if (pass == 0) k_wide_expand<false, 4><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
-            else k_wide_expand<true, 4><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
-          }
-          RT_CUDA(cudaMemcpyAsync(c, cnt, sizeof(c), cudaMemcpyDeviceToHost, st));
-          RT_CUDA(cudaStreamSynchronize(st));
-          n_in = (int)c[0];
-          c[0] = 0;
-          RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
-          std::swap(in, out);
-          levels++;
-        }
-        if (pass == 0) {
-          n_w = (int)c[1];
-          RT_CUDA(wbuf.reserve((size_t)n_w * f4 * 16));
-        } else if ((int)c[1] != n_w) {
-          set_error("wide trees: collapse passes disagree");
-          return RT_ERR_CUDA;
-        }
-        if (width == 8) ctx->build_stats.wide_depth = levels;
-      }
-      ctx->n_wide[width == 8 ? 0 : 1] = n_w;
-      if (width == 8) {
-        ctx->scene.wnodes = wbuf.as<float4>();
-        ctx->scene.n_wnodes = n_w;
-        ctx->build_stats.n_wide_nodes = n_w;
-      } else {
-        ctx->scene.wnodes4 = wbuf.as<float4>();
-      }
-      ctx->trees |= wbit;
+  const int f4 = WideLayout<8>::F4;
+  int n_w = 0;
+  for (int pass = 0; pass < 2; pass++) {
+    uint2 *in = S[6].as<uint2>(), *out = S[7].as<uint2>();
+    uint2 seed = make_uint2(0u, 0u);
+    uint32_t c[2] = {0u, 1u};
+    RT_CUDA(cudaMemcpyAsync(in, &seed, sizeof(seed), cudaMemcpyHostToDevice, st));
+    RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
+    int n_in = 1, levels = 0;
+    while (n_in > 0) {
+      const float4 *bn = ctx->nodes.as<float4>();
+      float4 *wn = pass ? ctx->wnodes.as<float4>() : nullptr;
+      if (pass == 0)
+        k_wide_expand<false, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
+      else
+        k_wide_expand<true, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
+      RT_CUDA(cudaMemcpyAsync(c, cnt, sizeof(c), cudaMemcpyDeviceToHost, st));
+      RT_CUDA(cudaStreamSynchronize(st));
+      n_in = (int)c[0];
+      c[0] = 0;
+      RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
+      std::swap(in, out);
+      levels++;
     }
-    if (need & cbit) {  // compact copy of the same tree (same node indices): RT_TRAV=21 / 22
-      const int n_w = ctx->n_wide[width == 8 ? 0 : 1];
-      DevBuf &cbuf = width == 8 ? ctx->cnodes8 : ctx->cnodes4;
-      RT_CUDA(cbuf.reserve((size_t)n_w * (width == 8 ? CWideLayout<8>::U4 : CWideLayout<4>::U4) * 16));
-      if (width == 8) {
-        k_wide_compress<8><<<nblk(n_w), 256, 0, st>>>(wbuf.as<float4>(), n_w, cbuf.as<uint4>());
-        ctx->scene.cnodes8 = cbuf.as<uint4>();
-      } else {
-        k_wide_compress<4><<<nblk(n_w), 256, 0, st>>>(wbuf.as<float4>(), n_w, cbuf.as<uint4>());
-        ctx->scene.cnodes4 = cbuf.as<uint4>();
-      }
-      ctx->trees |= cbit;
+    if (pass == 0) {
+      n_w = (int)c[1];
+      RT_CUDA(ctx->wnodes.reserve((size_t)n_w * f4 * 16));
+    } else if ((int)c[1] != n_w) {
+      set_error("wide tree: collapse passes disagree");
+      return RT_ERR_CUDA;
     }
+    ctx->build_stats.wide_depth = levels;
   }
+  ctx->n_wide = n_w;
+  ctx->scene.wnodes = ctx->wnodes.as<float4>();
+  ctx->scene.n_wnodes = n_w;
+  ctx->build_stats.n_wide_nodes = n_w;
+  ctx->has_wide = true;
   RT_CUDA(cudaGetLastError());
   return RT_OK;
 }
@@ -793,11 +706,10 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   }
   DScene &s = ctx->scene;
   s.nodes = ctx->nodes.as<float4>();
-  s.wnodes = s.wnodes4 = nullptr;  // derived trees: built on demand (ensure_trees)
-  s.cnodes8 = s.cnodes4 = nullptr;
+  s.wnodes = nullptr;  // derived tree: built on demand (ensure_wide_tree)
   s.n_wnodes = 0;
-  ctx->trees = 0;
-  ctx->n_wide[0] = ctx->n_wide[1] = 0;
+  ctx->has_wide = false;
+  ctx->n_wide = 0;
   s.recs = ctx->recs.as<float4>();
   s.recs_seq = recs_seq;
   s.face_uv = any_uv ? ctx->face_uv.as<float>() : nullptr;
@@ -838,9 +750,15 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   rt_build_stats &bs = ctx->build_stats;
   bs.n_wide_nodes = 0;
   bs.wide_depth = 0;
-  // the tree of the traversal this scene renders with by default (RT_TRAV honoured); part of the build time
+  // the traversal this scene renders with (RT_TRAV / RT_STRATEGY are read here, once per commit) and its tree;
+  // part of the build time
+  ctx->trav = default_trav(ctx);
   {
-    int rc = ensure_trees(ctx, trees_for_trav(trav_variant(ctx)), st);
+    const char *env = getenv("RT_STRATEGY");
+    ctx->opt_wavefront = env && strcmp(env, "wavefront") == 0;
+  }
+  if (ctx->trav == 17) {
+    int rc = ensure_wide_tree(ctx, st);
     if (rc) {
       ctx->has_scene = false;
       return rc;

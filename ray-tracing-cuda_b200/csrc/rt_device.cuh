@@ -71,19 +71,9 @@ constexpr int STACK_SIZE = 64;
 // empty slot = WREF_EMPTY with an inverted box.
 // ------------------------------------------------------------------------------------------------
 constexpr int WIDE = 8, WNODE_F4 = 16;
-// Same layout at width W = 4 (128-byte nodes, one cache line): W/4 float4 per component array.
-//   float4 index of lo.{x,y,z}: axis * W/4;  hi: (3 + axis) * W/4;  ref: 6 * W/4;  meta: 7 * W/4
 template <int W>
 struct WideLayout {
   static constexpr int G = W / 4, F4 = 8 * G, HI = 3 * G, REF = 6 * G, META = 7 * G;
-};
-// Compact wide node (rt_cwide.cuh): child boxes quantised to 8 bits per plane against the node's own origin and a
-// power-of-two step per axis.  uint32 words: [0..2] origin xyz (float), [3] ex | ey<<8 | ez<<16 | valid<<24 (step =
-// 2^(e-127)), then 6 plane arrays of W bytes (lo.x lo.y lo.z hi.x hi.y hi.z; byte i = child i), then W refs (same
-// encoding as the wide node).  W = 4: 64 B (4 uint4, refs in uint4 #3); W = 8: 96 B (6 uint4, refs in #4, #5).
-template <int W>
-struct CWideLayout {
-  static constexpr int G = W / 4, U4 = W == 4 ? 4 : 6, REFW = 4 * (U4 - G), WORDS = 4 * U4;
 };
 constexpr uint32_t WLEAF = 0x80000000u, WREF_EMPTY = 0xffffffffu;
 constexpr int WLEAF_COUNT_SHIFT = 28, WLEAF_MAX_COUNT = 7;
@@ -106,9 +96,6 @@ struct DTexture {
 struct DScene {
   const float4 *nodes;     // 32-byte nodes: {lo.xyz, a}, {hi.xyz, b}
   const float4 *wnodes;    // 256-byte wide nodes (8 children), node 0 = root; null when n_recs == 0
-  const float4 *wnodes4;   // 128-byte wide nodes (4 children)
-  const uint4 *cnodes8;    // 96-byte compact wide nodes (8 children, 8-bit planes), same indices as wnodes
-  const uint4 *cnodes4;    // 64-byte compact wide nodes (4 children), same indices as wnodes4
   const float4 *recs;      // records in BVH (Morton) order, 3 float4 each
   const float4 *recs_seq;  // records in list order (Append order; faces in post-sort order; incl. SKY)
   const float *face_uv;    // per BVH-order record: 6 floats (Face<true> texcoords), or null
@@ -188,24 +175,25 @@ static_assert((double)DET_EPS_F >= 1e-7, "DET_EPS_F must round up");
 
 // utils.cu:49-85 TriangleHit, decision part.  Returns true when u, v pass and t >= tf_f; the
 // caller applies the upper bound.  a = v0, e1 = v1 - v0, e2 = v2 - v0.
+// Straight-line form: det, u, v, t are always computed (the same IEEE operations on the same operands as the
+// reference's early-exit form, so the same bits) and the five rejections are ANDed.  Each rejection is written as
+// the negation of the reference's `if (...) return false`, which keeps its NaN behaviour.  In the per-lane loops the
+// early exits only pay when every lane of the warp leaves (profiles/r01_x_cornell_boxlist_ncu_summary.txt: 11.5 -> 6.7
+// lanes across the function, i.e. the warp almost always runs to the end anyway) and cost four divergent branches.
 __device__ __forceinline__ bool tri_test(V3 a, V3 e1, V3 e2, const RayQ &r, float tf_f, float *out_t, float *out_u,
                                          float *out_v) {
   V3 pvec = cross(r.d, e2);
   float det = dot(e1, pvec);
-  if (fabsf(det) < DET_EPS_F) return false;
   float invDet = 1 / det;
   V3 tvec = r.o - a;
   float u = dot(tvec, pvec) * invDet;
-  if (u < 0 || u > 1) return false;
   V3 qvec = cross(tvec, e1);
   float v = dot(r.d, qvec) * invDet;
-  if (v < 0 || u + v > 1) return false;
   float t = dot(e2, qvec) * invDet;
-  if (!(t >= tf_f)) return false;
   *out_t = t;
   *out_u = u;
   *out_v = v;
-  return true;
+  return !(fabsf(det) < DET_EPS_F) & !(u < 0 || u > 1) & !(v < 0 || u + v > 1) & (t >= tf_f);
 }
 
 __device__ __forceinline__ double rec_radius(float4 r1) {
@@ -260,16 +248,17 @@ __device__ __forceinline__ void best_init(Best &b, double t_to) {
   b.obj = 0x7fffffff;
   b.sub = -1;
 }
-__device__ __forceinline__ bool best_offer(Best &b, double t, int32_t rec, int32_t obj, int32_t sub) {
-  // precondition: t <= b.t
-  if (t == b.t && b.rec != REC_NONE) {
-    if (!(obj < b.obj || (obj == b.obj && sub > b.sub))) return false;
-  }
-  b.t = t;
-  b.rec = rec;
-  b.obj = obj;
-  b.sub = sub;
-  return true;
+// `cond`: the candidate passed its own test and t <= the current bound.  Predicated selects, no branches.
+__device__ __forceinline__ bool best_offer(Best &b, bool cond, double t, int32_t rec, int32_t obj, int32_t sub) {
+  // precondition when cond: t <= b.t
+  const bool tie = (t == b.t) & (b.rec != REC_NONE);
+  const bool win = !tie | (obj < b.obj) | ((obj == b.obj) & (sub > b.sub));
+  const bool take = cond & win;
+  b.t = take ? t : b.t;
+  b.rec = take ? rec : b.rec;
+  b.obj = take ? obj : b.obj;
+  b.sub = take ? sub : b.sub;
+  return take;
 }
 
 // One record against the ray.  Returns the number of records consumed (2 for a quad).
@@ -280,33 +269,29 @@ __device__ __forceinline__ int rec_test(const float4 *__restrict__ recs, int k, 
                                         bool &ambiguous) {
   float4 r0 = __ldg(recs + 3 * (size_t)k), r1 = __ldg(recs + 3 * (size_t)k + 1), r2 = __ldg(recs + 3 * (size_t)k + 2);
   uint32_t kind = __float_as_uint(r2.w) & KIND_MASK;
-  if (kind == K_TRI) {
-    float t, u, v;
-    if (tri_test(xyz(r0), xyz(r1), xyz(r2), r, rg.tf_f, &t, &u, &v) && t <= b.t_f) {
-      if (best_offer(b, (double)t, k, __float_as_int(r0.w), __float_as_int(r1.w))) b.t_f = t;
-    }
-    return 1;
-  }
-  if (kind == K_QUAD0) {
+  if (kind == K_QUAD0) {  // both triangles of the parallelogram in one straight-line block
     float t0, t1, u, v;
-    bool h0 = tri_test(xyz(r0), xyz(r1), xyz(r2), r, rg.tf_f, &t0, &u, &v);
     float4 s0 = __ldg(recs + 3 * (size_t)k + 3), s1 = __ldg(recs + 3 * (size_t)k + 4), s2 = __ldg(recs + 3 * (size_t)k + 5);
-    bool h1 = tri_test(xyz(s0), xyz(s1), xyz(s2), r, rg.tf_f, &t1, &u, &v);
-    if (h0) {
-      if (h1 && t1 < t0) ambiguous = true;
-      if (t0 <= b.t_f) {
-        if (best_offer(b, (double)t0, k, __float_as_int(r0.w), 0)) b.t_f = t0;
-      }
-    } else if (h1 && t1 <= b.t_f) {
-      if (best_offer(b, (double)t1, k + 1, __float_as_int(s0.w), 1)) b.t_f = t1;
-    }
+    const bool h0 = tri_test(xyz(r0), xyz(r1), xyz(r2), r, rg.tf_f, &t0, &u, &v);
+    const bool h1 = tri_test(xyz(s0), xyz(s1), xyz(s2), r, rg.tf_f, &t1, &u, &v);
+    ambiguous |= h0 & h1 & (t1 < t0);
+    // parallelogram.cu:25-41: the first triangle that hits wins; the second is only looked at when the first misses
+    const bool first = h0;
+    const float t = first ? t0 : t1;
+    const bool cond = (h0 | h1) & (t <= b.t_f);
+    if (best_offer(b, cond, (double)t, first ? k : k + 1, __float_as_int(r0.w), first ? 0 : 1)) b.t_f = t;
     return 2;
   }
+  if (kind == K_TRI) {
+    float t, u, v;
+    const bool h = tri_test(xyz(r0), xyz(r1), xyz(r2), r, rg.tf_f, &t, &u, &v);
+    if (best_offer(b, h & (t <= b.t_f), (double)t, k, __float_as_int(r0.w), __float_as_int(r1.w))) b.t_f = t;
+    return 1;
+  }
   if (kind == K_SPHERE) {
-    double t;
-    if (sphere_test(xyz(r0), rec_radius(r1), r, rg.t_from, &t) && t <= b.t) {
-      if (best_offer(b, t, k, __float_as_int(r0.w), 0)) b.t_f = float_le(t);
-    }
+    double t = 0;
+    const bool h = sphere_test(xyz(r0), rec_radius(r1), r, rg.t_from, &t);
+    if (best_offer(b, h && t <= b.t, t, k, __float_as_int(r0.w), 0)) b.t_f = float_le(t);
     return 1;
   }
   return 1;  // K_QUAD1 reached on its own never happens (leaves keep pairs together); K_SKY is not in the BVH
@@ -521,10 +506,9 @@ __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r
 
 // "while-while" form of the same traversal (Aila & Laine 2009): every lane first walks inner nodes
 // until it holds a leaf, then the warp tests leaf records together, so node steps and record tests
-// are not interleaved across lanes.  SPEC: a lane that holds a leaf keeps walking (postponing the
-// leaf) until every lane of the warp holds one.  CULL: the far child is pushed with its entry
-// distance and dropped at pop time when the closest hit has moved in front of it.
-template <bool STATS, bool SPEC, bool CULL>
+// are not interleaved across lanes.  (Round 1 also measured speculative leaf postponement and pop-time culling:
+// both slower; removed.)
+template <bool STATS>
 __device__ __forceinline__ Hit world_hit_bvh_ww(const DScene &s, const RayQ &r, double t_from, double t_to,
                                                 TravStats *st) {
   Range rg;
@@ -549,73 +533,56 @@ __device__ __forceinline__ Hit world_hit_bvh_ww(const DScene &s, const RayQ &r, 
     const float nox = -(r.o.x * idx), noy = -(r.o.y * idy), noz = -(r.o.z * idz);
     const float t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
     uint2 stack[STACK_SIZE];
-    float stack_t[CULL ? STACK_SIZE : 1];
     int sp = 0;
     uint32_t ca = s.root_a, cb = s.root_b;
     const float4 *__restrict__ nodes = s.nodes;
     bool done = false;
-    // pops the next node to visit into (ca, cb); false when the stack is exhausted
-    auto pop = [&]() -> bool {
-      while (sp > 0) {
-        --sp;
-        if (CULL) {
-          float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
-          if (stack_t[sp] > t_hi + fabsf(t_hi) * 1e-5f) continue;
-        }
-        uint2 e = stack[sp];
-        ca = e.x;
-        cb = e.y;
-        return true;
-      }
-      return false;
-    };
     while (!done) {
       uint32_t leaf_a = 0, leaf_b = 0;  // leaf_b == 0: no leaf held
       for (;;) {
         if (cb & LEAF_FLAG) {
-          if (leaf_b) break;  // SPEC: second leaf; (ca, cb) keeps it for the next round
           leaf_a = ca;
           leaf_b = cb;
-          if (!pop()) {
+          if (sp == 0) {
             done = true;
-            break;
+          } else {
+            uint2 e = stack[--sp];
+            ca = e.x;
+            cb = e.y;
           }
-          if (!SPEC) break;
-        } else {
-          if (STATS) st->nodes += 2;
-          float4 l0 = __ldg(nodes + 2 * (size_t)ca), l1 = __ldg(nodes + 2 * (size_t)ca + 1);
-          float4 r0 = __ldg(nodes + 2 * (size_t)cb), r1 = __ldg(nodes + 2 * (size_t)cb + 1);
-          float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
-          float ln, lf, rn, rf;
-          slab2(l0, l1, r0, r1, idx, idy, idz, nox, noy, noz, t_lo, t_hi, ln, lf, rn, rf);
-          bool hl = ln <= lf * 1.00001f, hr = rn <= rf * 1.00001f;
-          uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
-          uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
-          if (hl && hr) {
-            bool left_first = ln <= rn;
-            if (sp < STACK_SIZE) {
-              stack[sp] = left_first ? make_uint2(ra, rb) : make_uint2(la, lb);
-              if (CULL) stack_t[sp] = left_first ? rn : ln;
-              sp++;
-            } else {
-              overflow = true;
-            }
-            ca = left_first ? la : ra;
-            cb = left_first ? lb : rb;
-          } else if (hl) {
-            ca = la;
-            cb = lb;
-          } else if (hr) {
-            ca = ra;
-            cb = rb;
-          } else if (!pop()) {
-            done = true;
-            break;
-          }
+          break;
         }
-        if (SPEC) {
-          // stop walking once every lane of the warp holds a leaf (or is finished)
-          if (!__any_sync(__activemask(), leaf_b == 0)) break;
+        if (STATS) st->nodes += 2;
+        float4 l0 = __ldg(nodes + 2 * (size_t)ca), l1 = __ldg(nodes + 2 * (size_t)ca + 1);
+        float4 r0 = __ldg(nodes + 2 * (size_t)cb), r1 = __ldg(nodes + 2 * (size_t)cb + 1);
+        float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
+        float ln, lf, rn, rf;
+        slab2(l0, l1, r0, r1, idx, idy, idz, nox, noy, noz, t_lo, t_hi, ln, lf, rn, rf);
+        bool hl = ln <= lf * 1.00001f, hr = rn <= rf * 1.00001f;
+        uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
+        uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
+        if (hl && hr) {
+          bool left_first = ln <= rn;
+          if (sp < STACK_SIZE) {
+            stack[sp++] = left_first ? make_uint2(ra, rb) : make_uint2(la, lb);
+          } else {
+            overflow = true;
+          }
+          ca = left_first ? la : ra;
+          cb = left_first ? lb : rb;
+        } else if (hl) {
+          ca = la;
+          cb = lb;
+        } else if (hr) {
+          ca = ra;
+          cb = rb;
+        } else if (sp == 0) {
+          done = true;
+          break;
+        } else {
+          uint2 e = stack[--sp];
+          ca = e.x;
+          cb = e.y;
         }
       }
       if (leaf_b) {
@@ -636,143 +603,12 @@ __device__ __forceinline__ Hit world_hit_bvh_ww(const DScene &s, const RayQ &r, 
   return h;
 }
 
-// ------------------------------------------------------------------------------------------------
-// Resumable form of the same traversal: one call = one node step or one record test.  The render
-// kernel k_render_vote keeps a Trav per lane and lets the WARP decide each iteration which kind of
-// step to execute (the kind most lanes are waiting for), so that node steps, record tests and
-// shading are never interleaved lane by lane.  Visit order, culling and tie rules are those of
-// world_hit_bvh_ifif: identical hits.
-// ------------------------------------------------------------------------------------------------
-enum : int { ST_GEN = 0, ST_NODE = 1, ST_LEAF = 2, ST_SHADE = 3, ST_DONE = 4 };
-
-struct Trav {
-  RayQ r;
-  float idx, idy, idz, nox, noy, noz, t_lo;
-  Best b;
-  uint32_t ca, cb;  // ST_NODE: the (a, b) words of an inner node; ST_LEAF: next record, end record
-  int sp;
-  bool ambiguous, overflow;
-};
-
-__device__ __forceinline__ int trav_set(Trav &tv, uint32_t a, uint32_t b) {
-  if (b & LEAF_FLAG) {
-    tv.ca = a;
-    tv.cb = a + (b & ~LEAF_FLAG);
-    return ST_LEAF;
-  }
-  tv.ca = a;
-  tv.cb = b;
-  return ST_NODE;
-}
-__device__ __forceinline__ int trav_pop(Trav &tv, const uint2 *stack) {
-  if (tv.sp == 0) return ST_SHADE;
-  uint2 e = stack[--tv.sp];
-  return trav_set(tv, e.x, e.y);
-}
-// Starts a query on tv.r; returns the first state.
-__device__ __forceinline__ int trav_begin(const DScene &s, Trav &tv, const Range &rg) {
-  best_init(tv.b, rg.t_to);
-  if (s.sky_obj >= 0) {  // sky.cu:18-27
-    double t = 1e9;
-    if (rg.t_from <= t && t <= rg.t_to) {
-      tv.b.t = t;
-      tv.b.t_f = 1e9f;
-      tv.b.rec = REC_SKY;
-      tv.b.obj = s.sky_obj;
-      tv.b.sub = 0;
-    }
-  }
-  tv.ambiguous = tv.overflow = false;
-  tv.sp = 0;
-  if (s.n_recs <= 0) return ST_SHADE;
-  tv.idx = slab_rcp(tv.r.d.x);
-  tv.idy = slab_rcp(tv.r.d.y);
-  tv.idz = slab_rcp(tv.r.d.z);
-  tv.nox = -(tv.r.o.x * tv.idx);
-  tv.noy = -(tv.r.o.y * tv.idy);
-  tv.noz = -(tv.r.o.z * tv.idz);
-  tv.t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
-  return trav_set(tv, s.root_a, s.root_b);
-}
-__device__ __forceinline__ int trav_node_step(const DScene &s, Trav &tv, uint2 *stack) {
-  const float4 *__restrict__ nodes = s.nodes;
-  float4 l0 = __ldg(nodes + 2 * (size_t)tv.ca), l1 = __ldg(nodes + 2 * (size_t)tv.ca + 1);
-  float4 r0 = __ldg(nodes + 2 * (size_t)tv.cb), r1 = __ldg(nodes + 2 * (size_t)tv.cb + 1);
-  float t_hi = tv.b.t_f + fabsf(tv.b.t_f) * 1e-5f;
-  float ln, lf, rn, rf;
-  slab2(l0, l1, r0, r1, tv.idx, tv.idy, tv.idz, tv.nox, tv.noy, tv.noz, tv.t_lo, t_hi, ln, lf, rn, rf);
-  bool hl = ln <= lf * 1.00001f, hr = rn <= rf * 1.00001f;
-  uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
-  uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
-  if (hl && hr) {
-    bool left_first = ln <= rn;
-    if (tv.sp < STACK_SIZE) {
-      stack[tv.sp++] = left_first ? make_uint2(ra, rb) : make_uint2(la, lb);
-    } else {
-      tv.overflow = true;
-    }
-    return trav_set(tv, left_first ? la : ra, left_first ? lb : rb);
-  }
-  if (hl) return trav_set(tv, la, lb);
-  if (hr) return trav_set(tv, ra, rb);
-  return trav_pop(tv, stack);
-}
-__device__ __forceinline__ int trav_leaf_step(const DScene &s, Trav &tv, const Range &rg, const uint2 *stack) {
-  int k = (int)tv.ca;
-  k += rec_test(s.recs, k, tv.r, rg, tv.b, tv.ambiguous);
-  tv.ca = (uint32_t)k;
-  if (k >= (int)tv.cb) return trav_pop(tv, stack);
-  return ST_LEAF;
-}
-__device__ __forceinline__ Hit trav_finish(const DScene &s, const Trav &tv, const Range &rg) {
-  if (tv.ambiguous || tv.overflow) return world_hit_seq(s, tv.r, rg.t_from, rg.t_to);
-  Hit h;
-  h.t = tv.b.rec == REC_NONE ? 0.0 : tv.b.t;
-  h.rec = tv.b.rec;
-  h.seq = 0;
-  return h;
-}
-// Per-lane driver of the step functions (parity hook / reference for the voting kernel).
-template <bool STATS>
-__device__ __forceinline__ Hit world_hit_bvh_steps(const DScene &s, const RayQ &r, double t_from, double t_to,
-                                                   TravStats *st) {
-  Range rg;
-  rg.t_from = t_from;
-  rg.t_to = t_to;
-  rg.tf_f = float_ge(t_from);
-  Trav tv;
-  tv.r = r;
-  uint2 stack[STACK_SIZE];
-  int state = trav_begin(s, tv, rg);
-  while (state != ST_SHADE) {
-    if (state == ST_NODE) {
-      if (STATS) st->nodes += 2;
-      state = trav_node_step(s, tv, stack);
-    } else {
-      if (STATS) {
-        uint32_t before = tv.ca;
-        state = trav_leaf_step(s, tv, rg, stack);
-        st->prims += state == ST_LEAF ? tv.ca - before : 1;
-        continue;
-      }
-      state = trav_leaf_step(s, tv, rg, stack);
-    }
-  }
-  return trav_finish(s, tv, rg);
-}
-
-// Traversal variants (selected per launch; all return identical hits):
-//   0 if-if (round-1 first kernel)   1 while-while   2 while-while + speculative leaf postponement
-//   3 = 1 + pop-time culling         4 = 2 + pop-time culling         5 = resumable steps (vote kernel)
+// Binary-tree traversal loops of the render kernels (identical hits): 0 if-if, 1 while-while.
 template <bool STATS, int TRAV>
 __device__ __forceinline__ Hit world_hit_bvh(const DScene &s, const RayQ &r, double t_from, double t_to,
                                              TravStats *st) {
-  if (TRAV == 0) return world_hit_bvh_ifif<STATS>(s, r, t_from, t_to, st);
-  if (TRAV == 1) return world_hit_bvh_ww<STATS, false, false>(s, r, t_from, t_to, st);
-  if (TRAV == 2) return world_hit_bvh_ww<STATS, true, false>(s, r, t_from, t_to, st);
-  if (TRAV == 3) return world_hit_bvh_ww<STATS, false, true>(s, r, t_from, t_to, st);
-  if (TRAV == 5) return world_hit_bvh_steps<STATS>(s, r, t_from, t_to, st);
-  return world_hit_bvh_ww<STATS, true, true>(s, r, t_from, t_to, st);
+  if (TRAV == 1) return world_hit_bvh_ww<STATS>(s, r, t_from, t_to, st);
+  return world_hit_bvh_ifif<STATS>(s, r, t_from, t_to, st);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -876,44 +712,116 @@ __device__ __forceinline__ V3 texture_value(const DScene &s, const DMaterial &m,
 struct PathKey {
   uint32_t pixel, sample, k0, k1;
 };
-constexpr int MAX_REJECT_ITER = 64;
 
-// lambertian.cu:19-31 SphericalRand / metal.cu:27-36 RandomInUnitSphere on the keyed Philox
-// stream: dimension 1 + depth, one block per rejection iteration, at most MAX_REJECT_ITER.
-__device__ __forceinline__ V3 ball_rejection(const PathKey &pk, int depth, float *out_l) {
-  float x = 0, y = 0, z = 0, l = 0;
-  for (int it = 0; it < MAX_REJECT_ITER; it++) {
-    uint32_t o[4];
-    philox4x32_10(pk.pixel, pk.sample, (uint32_t)(1 + depth), (uint32_t)it, pk.k0, pk.k1, o);
-    x = u01(o[0]) * 2.0f + -1.0f;
-    y = u01(o[1]) * 2.0f + -1.0f;
-    z = u01(o[2]) * 2.0f + -1.0f;
-    l = sqrtf(x * x + y * y + z * z);
-    if (!(l > 1)) break;
+// ------------------------------------------------------------------------------------------------
+// Sampling.  The random words of a path are a counter-based stream: word w of (pixel, sample) is word w & 3 of
+// the Philox block (pixel, sample, w >> 2, 0).  Layout (rtcore.h, "sampling contract"):
+//   words 0, 1        pixel jitter                           (ray_tracing.cu:68-71)
+//   words 2, 3        lens sample, thin-lens cameras only    (camera.cu:62-65)
+//   words B+2k, B+2k+1   the direction sample of the scatter at depth k, B = 4 with a lens, else 2
+// so one block serves two bounces (and the camera block serves bounce 0 of a pinhole camera); Metal with fuzz
+// takes its radius from word 0 of block (pixel, sample, 0x40000000 + k, 0).
+//
+// Lambertian::Scatter normalises a rejection-sampled ball point (lambertian.cu:19-31), i.e. it draws a uniform
+// DIRECTION; Metal::Scatter uses the ball point itself (metal.cu:27-36).  Both are drawn here without a loop:
+// direction = (sqrt(1 - z^2) cos phi, sqrt(1 - z^2) sin phi, z), z = 1 - 2 u0, phi = 2 pi u1 (Archimedes), ball
+// point = direction * cbrt(u2).  Same distributions as the reference's rejection loops, one Philox block instead
+// of 1.91 on average — and no warp waiting for the longest of its lanes' trip counts (round 1: philox + rejection
+// = 17 % of all warp instructions at 8 of 32 lanes).  sin / cos / cbrt are written out in IEEE operations (explicit
+// fmaf, correctly rounded division) so that the CPU oracle reproduces them bit for bit; libdevice's would not be.
+// ------------------------------------------------------------------------------------------------
+struct PhiloxCache {  // words 2, 3 of the block generated last (the second bounce of a block costs nothing)
+  uint32_t block, w2, w3;
+};
+constexpr uint32_t PHILOX_NO_BLOCK = 0xffffffffu;
+
+__device__ __forceinline__ void path_words(const PathKey &pk, uint32_t w, PhiloxCache *pc, uint32_t *a, uint32_t *b) {
+  const uint32_t block = w >> 2;
+  if ((w & 2u) && pc && pc->block == block) {
+    *a = pc->w2;
+    *b = pc->w3;
+    return;
   }
-  *out_l = l;
-  return mk(x, y, z);
+  uint32_t o[4];
+  philox4x32_10(pk.pixel, pk.sample, block, 0u, pk.k0, pk.k1, o);
+  if (pc) {
+    pc->block = block;
+    pc->w2 = o[2];
+    pc->w3 = o[3];
+  }
+  *a = (w & 2u) ? o[2] : o[0];
+  *b = (w & 2u) ? o[3] : o[1];
+}
+
+// (cos, sin)(2 pi u) * sqrt(1/2), u in (0, 1].  Quadrant k = floor(4u), x = (pi/2)(4u - k - 1/2) in [-pi/4, pi/4):
+// Taylor polynomials of degree 9 / 8 (|error| < 3e-8), then the rotation by (k + 1/2) pi/2, whose sine and cosine
+// are +-sqrt(1/2) — left to the caller's radius.
+__host__ __device__ __forceinline__ void sincos_2pi_scaled(float u, float *c, float *s) {
+  const float q = u * 4.0f;
+  const float kf = floorf(q);
+  const float x = ((q - kf) - 0.5f) * 1.57079637050628662109375f;
+  const float x2 = x * x;
+  float ps = fmaf(x2, 2.75573192e-6f, -1.98412698e-4f);
+  ps = fmaf(x2, ps, 8.33333333e-3f);
+  ps = fmaf(x2, ps, -1.66666667e-1f);
+  const float sn = fmaf(x * x2, ps, x);
+  float pc = fmaf(x2, 2.48015873e-5f, -1.38888889e-3f);
+  pc = fmaf(x2, pc, 4.16666667e-2f);
+  pc = fmaf(x2, pc, -0.5f);
+  const float cs = fmaf(x2, pc, 1.0f);
+  const float p = cs - sn, qq = cs + sn;
+  const int k = (int)kf;
+  const float cv = (k & 1) ? qq : p, sv = (k & 1) ? p : qq;
+  *c = ((k + 1) & 2) ? -cv : cv;
+  *s = (k & 2) ? -sv : sv;
+}
+
+// Uniform direction on the unit sphere from two words.
+__host__ __device__ __forceinline__ V3 sphere_direction(float u0, float u1) {
+  const float z = 1.0f - 2.0f * u0;
+  const float r = sqrtf(fmaxf(1.0f - z * z, 0.0f)) * 0.707106769084930419921875f;
+  float c, s;
+  sincos_2pi_scaled(u1, &c, &s);
+  return mk(r * c, r * s, z);
+}
+
+// Cube root of x in (0, 1]: exponent / 3 by integer division, three Newton steps (relative error < 2e-7).
+__host__ __device__ __forceinline__ float cbrt_unit(float x) {
+  uint32_t i;
+#ifdef __CUDA_ARCH__
+  i = __float_as_uint(x);
+#else
+  memcpy(&i, &x, 4);
+#endif
+  i = i / 3u + 709921077u;
+  float y;
+#ifdef __CUDA_ARCH__
+  y = __uint_as_float(i);
+#else
+  memcpy(&y, &i, 4);
+#endif
+  y = y - (y * y * y - x) / (3.0f * (y * y));
+  y = y - (y * y * y - x) / (3.0f * (y * y));
+  y = y - (y * y * y - x) / (3.0f * (y * y));
+  return y;
 }
 
 __device__ __forceinline__ bool material_needs_uv(const DMaterial &m) { return m.texture >= 0; }
 
 // Material::Scatter (lambertian.cu:33-43, metal.cu:12-25, dielectric.cu:16-44, diffuse_light.cu:5-9,
 // sky.cu:3-7).  Returns false when the path ends here.  The scattered ray goes through Ray::Ray,
-// which normalizes (ray.cu:8-11).
-// BALL: float* -> V3, the ball sample of this bounce (ball_rejection, or a sample drawn ahead by ball_rejection_coop).
-template <typename BALL>
-__device__ __forceinline__ bool scatter_with(const DScene &s, const DMaterial &m, const RayQ &ray, float t,
-                                             const Surface &sf, BALL ball, V3 *att, RayQ *out) {
+// which normalizes (ray.cu:8-11).  word0 = index of the first stream word of this bounce.
+__device__ __forceinline__ bool scatter(const DScene &s, const DMaterial &m, const RayQ &ray, float t, const Surface &sf,
+                                        const PathKey &pk, int depth, uint32_t word0, PhiloxCache *pc, V3 *att,
+                                        RayQ *out) {
   switch (m.type) {
     case RT_MAT_LAMBERTIAN: {
       if (dot(ray.d, sf.normal) >= 0) return false;
       V3 p = ray.o + t * ray.d;
       V3 albedo = texture_value(s, m, sf.u, sf.v);
-      float l;
-      V3 r = ball(&l);
-      r.x /= l;
-      r.y /= l;
-      r.z /= l;
+      uint32_t a, b;
+      path_words(pk, word0, pc, &a, &b);
+      V3 r = sphere_direction(u01(a), u01(b));
       V3 next_dir = normalize(r + sf.normal);
       *att = albedo;
       out->o = p;
@@ -928,8 +836,10 @@ __device__ __forceinline__ bool scatter_with(const DScene &s, const DMaterial &m
       float fuzz = m.color_fuzz.w;
       out->o = p;
       if (fuzz > 0) {
-        float l;
-        V3 r = ball(&l);
+        uint32_t a, b, o[4];
+        path_words(pk, word0, pc, &a, &b);
+        philox4x32_10(pk.pixel, pk.sample, 0x40000000u + (uint32_t)depth, 0u, pk.k0, pk.k1, o);
+        V3 r = sphere_direction(u01(a), u01(b)) * cbrt_unit(u01(o[0]));
         out->d = normalize(reflected + fuzz * r);
       } else {
         out->d = normalize(reflected);
@@ -955,74 +865,21 @@ __device__ __forceinline__ bool scatter_with(const DScene &s, const DMaterial &m
   }
 }
 
-__device__ __forceinline__ bool scatter(const DScene &s, const DMaterial &m, const RayQ &ray, float t, const Surface &sf,
-                                        const PathKey &pk, int depth, V3 *att, RayQ *out) {
-  return scatter_with(s, m, ray, t, sf, [&](float *l) { return ball_rejection(pk, depth, l); }, att, out);
+// ------------------------------------------------------------------------------------------------
+// Fixed-point radiance sums.  A sample's radiance is rounded once to a multiple of 2^-30 and the samples of a pixel
+// are summed as 64-bit integers: exact, hence independent of the order in which warps, sample chunks, rt_render
+// calls or GPUs contribute them — any schedule and any partition gives the same bits.  |component| is clamped
+// to 2^32 (a sum holds 2^31 such samples), NaN counts as 0.
+// ------------------------------------------------------------------------------------------------
+constexpr float FIXED_SCALE = 1073741824.0f, FIXED_CLAMP = 4294967296.0f;
+constexpr double FIXED_INV = 1.0 / 1073741824.0;
+__device__ __forceinline__ long long to_fixed(float c) {
+  if (c != c) c = 0.0f;
+  c = c > FIXED_CLAMP ? FIXED_CLAMP : c;
+  c = c < -FIXED_CLAMP ? -FIXED_CLAMP : c;
+  return __float2ll_rn(c * FIXED_SCALE);
 }
-
-// Does Scatter draw a ball sample for this hit?  (lambertian.cu:36, metal.cu:15,20: front face only; Metal only with fuzz)
-__device__ __forceinline__ bool scatter_needs_ball(const DMaterial &m, const RayQ &ray, const Surface &sf) {
-  if (m.type == RT_MAT_LAMBERTIAN) return !(dot(ray.d, sf.normal) >= 0);
-  if (m.type == RT_MAT_METAL) return !(dot(ray.d, sf.normal) >= 0) && m.color_fuzz.w > 0;
-  return false;
-}
-
-// ball_rejection for the lanes of a (partly) converged warp: the same Philox blocks, the same first accepted
-// iteration, so the same sample — but the iterations of the lanes that still `need` one are spread over ALL calling
-// lanes.  In the per-lane loop a warp runs max(trip count) rounds (5.2 for 19 Lambertian lanes, acceptance 0.52) with
-// 8 of 32 lanes busy (profiles/r01_x_cornell_boxlist_ncu_summary.txt: philox + ball_rejection = 17 % of all warp
-// instructions at 8 lanes).  Here every lane that needs no sample (light / sky / dielectric hit, finished pixel, or a
-// lane already served) tries a LATER iteration of the first needy lane above it: lane L's run = the calling lanes
-// between the previous needy lane and L; L itself tries iteration base, the run below it base + 1, base + 2, ...
-// (by decreasing lane); L takes the accepted candidate of lowest iteration, or moves base past the run.
-// Every lane that is converged at the call must call (need = false to help only).
-__device__ __forceinline__ V3 ball_rejection_coop(bool need, const PathKey &pk, int depth, float *out_l) {
-  const unsigned act = __activemask();
-  const int lane = threadIdx.x & 31;
-  const unsigned le = (2u << lane) - 1u;  // lanes <= this one
-  float x = 0, y = 0, z = 0, l = 0;
-  uint32_t base = 0;
-  bool exhausted = false;
-  unsigned needy = __ballot_sync(act, need);
-  while (needy) {
-    const bool self = (needy >> lane) & 1u;
-    const unsigned above = needy & ~le;
-    const int tgt = self ? lane : (above ? __ffs(above) - 1 : -1);
-    const uint32_t off = self ? 0u : 1u + (uint32_t)__popc(act & ~le & ((1u << (tgt & 31)) - 1u));
-    const int src = tgt < 0 ? lane : tgt;
-    const uint32_t c0 = __shfl_sync(act, pk.pixel, src), c1 = __shfl_sync(act, pk.sample, src);
-    const uint32_t c2 = __shfl_sync(act, (uint32_t)(1 + depth), src), c3 = __shfl_sync(act, base, src) + off;
-    float cx = 0, cy = 0, cz = 0, cl = 2.f;
-    if (tgt >= 0 && c3 < (uint32_t)MAX_REJECT_ITER) {
-      uint32_t o[4];
-      philox4x32_10(c0, c1, c2, c3, pk.k0, pk.k1, o);
-      cx = u01(o[0]) * 2.0f + -1.0f;
-      cy = u01(o[1]) * 2.0f + -1.0f;
-      cz = u01(o[2]) * 2.0f + -1.0f;
-      cl = sqrtf(cx * cx + cy * cy + cz * cz);
-    }
-    const unsigned okm = __ballot_sync(act, !(cl > 1));
-    const unsigned below = needy & (le >> 1);  // needy lanes < this one
-    const unsigned run = act & le & ~(below ? (2u << (31 - __clz(below))) - 1u : 0u);
-    const unsigned sel = okm & run;
-    const int from = sel ? 31 - __clz(sel) : lane;  // highest lane of the run = lowest iteration
-    const float gx = __shfl_sync(act, cx, from), gy = __shfl_sync(act, cy, from);
-    const float gz = __shfl_sync(act, cz, from), gl = __shfl_sync(act, cl, from);
-    if (self) {
-      if (sel) {
-        x = gx, y = gy, z = gz, l = gl;
-        need = false;
-      } else {
-        base += (uint32_t)__popc(run);
-        if (base >= (uint32_t)MAX_REJECT_ITER) exhausted = true, need = false;
-      }
-    }
-    needy = __ballot_sync(act, need);
-  }
-  if (exhausted) return ball_rejection(pk, depth, out_l);  // 0.48^64: the serial loop's own answer
-  *out_l = l;
-  return mk(x, y, z);
-}
+__device__ __forceinline__ float from_fixed(long long q) { return __double2float_rn(__ll2double_rn(q) * FIXED_INV); }
 
 // Material::Emit (diffuse_light.cu:11-13, sky.cu:9-14, material.cu:3-6)
 __device__ __forceinline__ V3 emit(const DScene &s, const DMaterial &m, float u, float v, V3 p) {
@@ -1056,11 +913,16 @@ __device__ __forceinline__ RayQ camera_ray_at(const DCamera &c, double x, double
   return r;
 }
 
-// ray_tracing.cu:68-74: camera sample `sample` of pixel (i, j) from Philox block (pixel, sample, 0, 0)
+// ray_tracing.cu:68-74: camera sample `sample` of pixel (i, j) from stream words 0..3 (block 0)
 __device__ __forceinline__ RayQ camera_sample(const DCamera &cam, int i, int j, int height, int width,
-                                              const PathKey &pk) {
+                                              const PathKey &pk, PhiloxCache *pc) {
   uint32_t o[4];
   philox4x32_10(pk.pixel, pk.sample, 0u, 0u, pk.k0, pk.k1, o);
+  if (pc) {
+    pc->block = 0u;
+    pc->w2 = o[2];
+    pc->w3 = o[3];
+  }
   double x = ((double)u01(o[0]) + double(j)) / double(width);
   double y = ((double)u01(o[1]) + double(height - i)) / double(height);
   x = 2 * x - 1;
@@ -1071,6 +933,10 @@ __device__ __forceinline__ RayQ camera_sample(const DCamera &cam, int i, int j, 
     lv = u01(o[3]) * cam.lens_radius;
   }
   return camera_ray_at(cam, x, y, lu, lv);
+}
+// first stream word of the scatter at `depth`
+__device__ __forceinline__ uint32_t scatter_word(const DCamera &cam, int depth) {
+  return (cam.is_defocus ? 4u : 2u) + 2u * (uint32_t)depth;
 }
 
 }  // namespace rtc

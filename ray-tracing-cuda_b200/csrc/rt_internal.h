@@ -43,21 +43,16 @@ struct DevBuf {
   }
 };
 
-// derived trees (rt_ctx::trees): built on demand by ensure_trees
-enum : unsigned { RT_TREE_W8 = 1u, RT_TREE_W4 = 2u, RT_TREE_C8 = 4u, RT_TREE_C4 = 8u };
-
 struct RenderCounters {  // device-side counters of one rt_render call
-  unsigned long long samples, rays, rays_ref, nodes, prims, seq_fallbacks, sched_iters, sched_lanes;
+  unsigned long long samples, rays, rays_ref, nodes, prims, reserved[3];
 };
 
 }  // namespace rtc
 
 struct rt_ctx;
 namespace rtc {
-int trav_variant(const rt_ctx *ctx);                  // rt_render.cu: RT_TRAV or the scene's default
-unsigned trees_for_trav(int trav);                    // which derived trees a render variant walks
-unsigned trees_for_mode(int mode);                    // ... and a rt_trace_closest mode
-int ensure_trees(rt_ctx *ctx, unsigned need, cudaStream_t st);  // rt_build.cu
+int default_trav(const rt_ctx *ctx);                  // rt_render.cu: the scene's traversal (RT_TRAV overrides), read at commit
+int ensure_wide_tree(rt_ctx *ctx, cudaStream_t st);   // rt_build.cu: the 8-wide tree, derived from the binary tree on demand
 }  // namespace rtc
 
 struct rt_ctx {
@@ -65,27 +60,24 @@ struct rt_ctx {
   bool has_scene = false, has_camera = false;
   rtc::DScene scene{};
   rtc::DCamera camera{};
-  unsigned trees = 0;  // RT_TREE_* present for the committed scene
-  int n_wide[2] = {0, 0};  // 8-wide / 4-wide node counts
+  int n_sm = 148;
+  int trav = 0;               // traversal of the render kernel for the committed scene (default_trav)
+  bool opt_wavefront = false; // RT_STRATEGY=wavefront at commit: the default strategy of rt_render
+  bool has_wide = false;      // the 8-wide tree exists for the committed scene
+  int n_wide = 0;
   rtc::FlatItems flat{};  // box list of scenes with <= FLAT_MAX primitives (flat.n = 0: none)
   rt_camera camera_host{};
   // scene storage
-  rtc::DevBuf nodes, wnodes, wnodes4, cnodes8, cnodes4, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;
+  rtc::DevBuf nodes, wnodes, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;
   std::vector<void *> tex_allocs;
   // build scratch
   rtc::DevBuf scratch[12];
   // render scratch
-  rtc::DevBuf counters, accum_tmp, rgb_tmp, rgb8_tmp, rays_tmp, hits_tmp;
+  rtc::DevBuf counters, accum_tmp, fixed_tmp, rgb_tmp, rgb8_tmp, rays_tmp, hits_tmp;
   rtc::DevBuf wf[16];  // wavefront path state
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
-  // RT_RENDER_SPLIT: side streams of the sample slices, fork / join events, per-slice sums (created on first use)
-  static constexpr int kMaxSlices = 32;
-  cudaStream_t slice_st[kMaxSlices - 1] = {};
-  cudaEvent_t slice_ev[kMaxSlices] = {};
-  rtc::DevBuf slice_sums;
-  // RT_RENDER_ORDERED: per-tile probe cost and the tile list sorted by it
-  rtc::DevBuf tile_cost, tile_order;
-  std::vector<uint32_t> tile_cost_host, tile_order_host;
+  uint32_t last_iterations = 0, last_launches = 0, last_items = 0;
+  int last_chunk = 0;
   rt_build_stats build_stats{};
   // nccl (loaded lazily)
   void *nccl_comm = nullptr;

@@ -5,9 +5,13 @@
 // All rendering goes through librtcore.so (include/rtcore.h); nothing here traces a ray.
 #include "rt_scene_api.cuh"
 
+#include <fcntl.h>
 #include <unistd.h>
 
 #include <algorithm>
+#include <cctype>
+#include <cerrno>
+#include <sstream>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -405,47 +409,90 @@ void WriteStats(const Options &o, int rank, int world_size, const rt_build_stats
 }
 
 // NCCL rendezvous between the ranks of one box: rank 0 publishes the ncclUniqueId in /dev/shm.
+// The file name carries a per-run nonce, so that a file left behind by a run that died can never be taken for this
+// run's: RT_JOB_ID (rtrun: its pid + start time), else the launcher's pid (the ranks' common parent: torchrun,
+// mpirun) + that process's start time from /proc (a reused pid has another start time) + MASTER_PORT if set.
+// The record is {magic, world size, id}; readers check all of it.
+struct RendezvousRecord {
+  char magic[8];
+  int32_t world_size, reserved;
+  char id[128];
+};
 std::string RendezvousPath() {
   const char *job = getenv("RT_JOB_ID");
-  if (!job || !*job) job = getenv("MASTER_PORT");
-  std::string key = job && *job ? std::string(job) : "ppid" + std::to_string((long)getppid());
-  return "/dev/shm/rtcore_nccl_" + key;
+  std::string key;
+  if (job && *job) {
+    key = job;
+  } else {
+    const long ppid = (long)getppid();
+    key = "p" + std::to_string(ppid);
+    std::ifstream st("/proc/" + std::to_string(ppid) + "/stat");
+    std::string line;
+    if (std::getline(st, line)) {  // field 22 (starttime) counted after the ")" that ends the command name
+      size_t k = line.rfind(')');
+      std::istringstream is(k == std::string::npos ? std::string() : line.substr(k + 1));
+      std::string f;
+      for (int i = 0; i < 20 && (is >> f); i++) {}
+      if (!f.empty()) key += "-" + f;
+    }
+    const char *port = getenv("MASTER_PORT");
+    if (port && *port) key += "-" + std::string(port);
+  }
+  for (char &c : key)
+    if (!(isalnum((unsigned char)c) || c == '-' || c == '_')) c = '_';
+  return "/dev/shm/rtcore_nccl_" + std::to_string((long)getuid()) + "_" + key;
 }
 
 void BindNccl(rt_ctx *ctx, int rank, int world_size) {
-  char id[128];
-  std::string path = RendezvousPath();
+  RendezvousRecord rec;
+  memset(&rec, 0, sizeof(rec));
+  const std::string path = RendezvousPath();
   if (rank == 0) {
-    RTAPI_RT(rt_nccl_unique_id(id));
-    std::string tmp = path + ".tmp";
-    {
-      std::ofstream f(tmp, std::ios::binary);
-      f.write(id, sizeof(id));
-    }
+    memcpy(rec.magic, "RTNCCL01", 8);
+    rec.world_size = world_size;
+    RTAPI_RT(rt_nccl_unique_id(rec.id));
+    const std::string tmp = path + ".tmp";
+    unlink(path.c_str());  // nothing of an earlier run survives under this name
+    unlink(tmp.c_str());
+    int fd = open(tmp.c_str(), O_CREAT | O_EXCL | O_WRONLY, 0600);
+    CHECK(fd >= 0) << "cannot create " << tmp << ": " << strerror(errno);
+    CHECK(write(fd, &rec, sizeof(rec)) == (ssize_t)sizeof(rec)) << "short write to " << tmp;
+    close(fd);
     CHECK(rename(tmp.c_str(), path.c_str()) == 0) << "cannot publish " << path;
   } else {
     bool ok = false;
     for (int tries = 0; tries < 6000 && !ok; tries++) {
-      std::ifstream f(path, std::ios::binary);
-      if (f.good() && f.read(id, sizeof(id)) && f.gcount() == (std::streamsize)sizeof(id)) ok = true;
-      else std::this_thread::sleep_for(std::chrono::milliseconds(10));
+      int fd = open(path.c_str(), O_RDONLY);
+      if (fd >= 0) {
+        ok = read(fd, &rec, sizeof(rec)) == (ssize_t)sizeof(rec) && memcmp(rec.magic, "RTNCCL01", 8) == 0 &&
+             rec.world_size == world_size;
+        close(fd);
+      }
+      if (!ok) std::this_thread::sleep_for(std::chrono::milliseconds(10));
     }
-    CHECK(ok) << "rank " << rank << ": no ncclUniqueId at " << path << " after 60 s";
+    CHECK(ok) << "rank " << rank << ": no ncclUniqueId for " << world_size << " ranks at " << path << " after 60 s";
   }
-  RTAPI_RT(rt_nccl_init(ctx, id, world_size, rank));
+  RTAPI_RT(rt_nccl_init(ctx, rec.id, world_size, rank));
   if (rank == 0) unlink(path.c_str());  // every rank has joined once ncclCommInitRank returns
 }
 
 // The part of Main / DistributedMain after init_world: flatten, build, render, (reduce), resolve, write.
+// Both drivers honour the launcher (rtrun -n N, torchrun, mpirun): with N ranks each renders its GetWorkload share of
+// the samples (utils.cu:111-113), the exact sums are reduced to rank 0 (one ncclReduce) and rank 0 writes the image —
+// the same bits as one rank renders alone.  The reference's Main is single-GPU only (utils.cu:132-179); `mpi` tells
+// whether the scene itself initialised MPI and bound its device (spheres.cu:83-98) or Main has to.
 void RenderWorld(curandState **d_states, Camera **d_camera, HitableList **d_world, glm::vec3 **d_image,
                  nvstd::function<void(HitableList *, Camera *)> init_world, int height, int width, int spp,
                  uint64_t curand_seed, bool distributed) {
   auto t_start = std::chrono::steady_clock::now();
   Options o = ReadOptions(height, width, spp);
   int rank = 0, world_size = 1;
-  if (distributed) {
-    MPI_Comm_size(MPI_COMM_WORLD, &world_size);
-    MPI_Comm_rank(MPI_COMM_WORLD, &rank);
+  MPI_Comm_size(MPI_COMM_WORLD, &world_size);
+  MPI_Comm_rank(MPI_COMM_WORLD, &rank);
+  if (!distributed && world_size > 1) {  // Main under a launcher: bind rank -> device as spheres.cu:90-93 does
+    int count = 1;
+    RTAPI_CUDA(cudaGetDeviceCount(&count));
+    RTAPI_CUDA(cudaSetDevice(rank % count));
   }
   int device = 0;
   RTAPI_CUDA(cudaGetDevice(&device));
@@ -472,32 +519,38 @@ void RenderWorld(curandState **d_states, Camera **d_camera, HitableList **d_worl
 
   int spp_begin = 0;
   int local_spp = rt_get_workload(rank, world_size, o.spp, &spp_begin);
-  if (distributed) LOG(INFO) << "[" << rank << " / " << world_size << "] workload: " << local_spp;
+  if (distributed || world_size > 1) LOG(INFO) << "[" << rank << " / " << world_size << "] workload: " << local_spp;
   if (world_size > 1) BindNccl(ctx, rank, world_size);
 
+  // the accumulation buffer: exact 64-bit sums (rtcore.h, summation contract)
+  int64_t *d_sums = nullptr;
+  RTAPI_CUDA(cudaMalloc(&d_sums, n * 3 * sizeof(int64_t)));
   rt_render_params p;
   p.height = o.height;
   p.width = o.width;
   p.spp_begin = spp_begin;
   p.spp_count = local_spp;
   p.max_depth = o.max_depth;
-  p.flags = RT_RENDER_CLEAR | RT_RENDER_SPLIT;  // small images: concurrent sample slices (rtcore.h)
+  p.flags = RT_RENDER_CLEAR;
   p.seed = o.seed;
   rt_render_stats rs;
-  float *accum = reinterpret_cast<float *>(*d_image);
-  RTAPI_RT(rt_render(ctx, &p, accum, &rs, nullptr));
-  if (distributed)
+  RTAPI_RT(rt_render_fixed(ctx, &p, d_sums, &rs, nullptr));
+  if (distributed || world_size > 1)
     LOG(INFO) << "[" << rank << " / " << world_size << "] Ray tracing finished in " << rs.render_ms << "ms.";
   else
     LOG(INFO) << "Ray tracing finished in " << rs.render_ms << "ms.";
 
   // utils.cu:124 (MPI_Reduce of host copies) -> one ncclReduce of the device buffer
-  if (world_size > 1) RTAPI_RT(rt_reduce(ctx, nullptr, accum, (int64_t)n * 3, 0, nullptr));
+  if (world_size > 1) RTAPI_RT(rt_reduce_fixed(ctx, nullptr, d_sums, (int64_t)n * 3, 0, nullptr));
+  float *image = reinterpret_cast<float *>(*d_image);
   if (rank == 0) {
-    // ray_tracing.cu:78-83 / utils.cu:126-129 on the device, then WriteImage's *255 truncation
+    // ray_tracing.cu:78-83 / utils.cu:126-129 on the device, then WriteImage's *255 truncation.  *d_image is left as
+    // the reference leaves it: post-processed by Main (post_processing = true, utils.cu:162), raw sums by
+    // DistributedMain (utils.cu:220)
     uint8_t *d_rgb8 = nullptr;
     RTAPI_CUDA(cudaMalloc(&d_rgb8, n * 3));
-    RTAPI_RT(rt_resolve(ctx, accum, o.height, o.width, std::max(o.spp, 1), distributed ? nullptr : accum, d_rgb8, nullptr));
+    RTAPI_RT(rt_resolve_fixed(ctx, d_sums, o.height, o.width, std::max(o.spp, 1), distributed ? image : nullptr,
+                              distributed ? nullptr : image, d_rgb8, nullptr));
     std::vector<uint8_t> rgb8(n * 3);
     RTAPI_CUDA(cudaMemcpy(rgb8.data(), d_rgb8, n * 3, cudaMemcpyDeviceToHost));
     RTAPI_CUDA(cudaFree(d_rgb8));
@@ -505,8 +558,11 @@ void RenderWorld(curandState **d_states, Camera **d_camera, HitableList **d_worl
     bool ppm = o.out.size() > 4 && o.out.compare(o.out.size() - 4, 4, ".ppm") == 0;
     RTAPI_RT(ppm ? rt_write_ppm(o.out.c_str(), o.width, o.height, rgb8.data())
                  : rt_write_jpeg(o.out.c_str(), o.width, o.height, rgb8.data(), 100));
+  } else {
+    RTAPI_RT(rt_resolve_fixed(ctx, d_sums, o.height, o.width, std::max(o.spp, 1), image, nullptr, nullptr, nullptr));
   }
   RTAPI_CUDA(cudaDeviceSynchronize());
+  RTAPI_CUDA(cudaFree(d_sums));
   double total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
   WriteStats(o, rank, world_size, bs, rs, local_spp, total_ms);
   if (world_size > 1) rt_nccl_destroy(ctx);

@@ -6,6 +6,8 @@
 #include <sys/wait.h>
 #include <unistd.h>
 
+#include <ctime>
+
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -22,7 +24,10 @@ int main(int argc, char **argv) {
     fprintf(stderr, "usage: rtrun -n N program [args...]\n");
     return 2;
   }
-  std::string job = std::to_string((long)getpid());
+  // per-run nonce of the rendezvous file: pid + wall-clock start in ns (a reused pid has another start time)
+  struct timespec ts;
+  clock_gettime(CLOCK_REALTIME, &ts);
+  std::string job = std::to_string((long)getpid()) + "-" + std::to_string((long long)ts.tv_sec * 1000000000LL + ts.tv_nsec);
   std::vector<pid_t> pids;
   for (int r = 0; r < n; r++) {
     pid_t pid = fork();

@@ -36,6 +36,11 @@ def oracle_lib():
                                         C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
     lib.ro_render_product.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64,
                                       C.c_void_p, C.c_void_p, C.c_int]
+    lib.ro_render_product_fixed.argtypes = lib.ro_render_product.argtypes
+    lib.ro_fixed_to_float.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+    lib.ro_sphere_direction.argtypes = [C.c_float, C.c_float, C.c_void_p]
+    lib.ro_cbrt_unit.restype = C.c_float
+    lib.ro_cbrt_unit.argtypes = [C.c_float]
     lib.ro_philox4x32_10.argtypes = [C.c_void_p] * 3
     lib.ro_curand_uniform_seq.argtypes = [C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]
     return lib
@@ -125,6 +130,15 @@ class OracleScene:
         cnt = np.zeros(3, np.uint64)
         self.lib.ro_render_product(self.h, self.camera.ctypes.data, height, width, spp_begin, spp_count, depth_limit,
                                    seed, accum.ctypes.data, cnt.ctypes.data, nthreads)
+        return accum, cnt
+
+    def render_product_fixed(self, height, width, spp_begin, spp_count, seed, depth_limit=10, accum=None, nthreads=0):
+        """The exact sums (int64, 2^-30 units) rt_render_fixed accumulates."""
+        if accum is None:
+            accum = np.zeros((height, width, 3), np.int64)
+        cnt = np.zeros(3, np.uint64)
+        self.lib.ro_render_product_fixed(self.h, self.camera.ctypes.data, height, width, spp_begin, spp_count,
+                                         depth_limit, seed, accum.ctypes.data, cnt.ctypes.data, nthreads)
         return accum, cnt
 
     def __del__(self):

@@ -102,12 +102,12 @@ def test_sequential_scan_mode_bit_exact(ctx, name):
 def test_degenerate_directions(ctx, name):
     """Rays with direction components exactly +-0 / denormal / 1e-30 and origins exactly on box planes: the
     slab tests (FFMA form, clamped reciprocal) must never cull a record the reference accepts.  Every
-    traversal (binary, 8-wide, cooperative) against the oracle's exhaustive scan."""
+    traversal (the scene's default, binary if-if / while-while, 8-wide) against the oracle's exhaustive scan."""
     s, cam, o = _setup(ctx, name)
     lo, hi = _BOX[name]
     rr = ck.degenerate_rays(40000, 33, lo, hi)
     want = o.trace(rr, quirks=0)
-    for mode in (0, 2, 3, 8, 9, 10, 11, 13, 14):
+    for mode in (0, 2, 3, 4):
         got = ctx.trace_closest(rr, mode=mode)
         bad = ck.hits_equal(got, want, _fields(name))
         assert len(bad) == 0, (mode, len(bad), rr[bad[:3]], got[bad[:3]], want[bad[:3]])
@@ -115,14 +115,13 @@ def test_degenerate_directions(ctx, name):
 
 @pytest.mark.parametrize("name", ["cornell_box", "spheres", "bunny9k", "soup100k"])
 def test_traversal_variants_identical(ctx, name):
-    """Every traversal variant of the render kernels (modes 2..7 per-lane binary loops, 8 = 8-wide tree,
-    9 = 8-wide tree + warp-cooperative record tests, 10 = binary tree + cooperative, 11 = 4-wide tree,
-    13 / 14 = compact 4-/8-wide tree with 8-bit quantised child boxes, rt_cwide.cuh) returns the oracle's hits."""
+    """Every traversal of the render kernel (mode 2 binary if-if, 3 binary while-while, 4 8-wide tree; the box list
+    has its own test) returns the oracle's hits."""
     s, cam, o = _setup(ctx, name)
     lo, hi = _BOX[name]
     rr = np.concatenate([ctx.primary_rays(54, 96), ck.random_rays(30000, 21, lo, hi)])
     want = o.trace(rr, quirks=0)
-    for mode in (2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 14):
+    for mode in (2, 3, 4):
         got = ctx.trace_closest(rr, mode=mode)
         bad = ck.hits_equal(got, want, _fields(name))
         assert len(bad) == 0, (mode, len(bad), got[bad[:3]], want[bad[:3]])
@@ -130,7 +129,7 @@ def test_traversal_variants_identical(ctx, name):
 
 @pytest.mark.parametrize("name", ["cornell_box", "birthday", "mixed30"])
 def test_box_list_traversal(ctx, name):
-    """Mode 12: the box-list traversal of scenes with at most 32 primitives (every box tested by every lane, nearest
+    """Mode 5: the box-list traversal of scenes with at most 32 primitives (every box tested by every lane, nearest
     box first, the rest re-tested against the closest hit) returns the oracle's hits on random, primary and
     degenerate rays; larger scenes refuse the mode."""
     if name == "mixed30":
@@ -159,17 +158,17 @@ def test_box_list_traversal(ctx, name):
         rr = np.concatenate([ctx.primary_rays(54, 96), ck.random_rays(40000, 5, lo, hi)])
     rr = np.concatenate([rr, ck.degenerate_rays(20000, 34, lo, hi)])
     want = o.trace(rr, quirks=0)
-    got = ctx.trace_closest(rr, mode=12)
+    got = ctx.trace_closest(rr, mode=5)
     bad = ck.hits_equal(got, want, fields)
     assert len(bad) == 0, (len(bad), rr[bad[:3]], got[bad[:3]], want[bad[:3]])
     # ranges other than the render default
     for rng_ in ((0.0, 1e9), (1e-3, 300.0)):
-        got = ctx.trace_closest(rr[:20000], *rng_, mode=12)
+        got = ctx.trace_closest(rr[:20000], *rng_, mode=5)
         assert len(ck.hits_equal(got, o.trace(rr[:20000], *rng_, quirks=0), fields)) == 0, rng_
     # a scene with more than 32 primitives has no box list
     _setup(ctx, "spheres")
     with pytest.raises(Exception):
-        ctx.trace_closest(rr[:10], mode=12)
+        ctx.trace_closest(rr[:10], mode=5)
 
 
 def test_mixed_scene_all_primitive_types(ctx):
@@ -229,6 +228,7 @@ def test_degenerate_inputs(ctx):
 
 @pytest.mark.parametrize("name,hw,spp", [("cornell_box", (72, 128), 16), ("spheres", (54, 96), 8), ("bunny9k", (54, 96), 4)])
 def test_render_bit_exact_vs_oracle(ctx, name, hw, spp):
+    import torch
     s, cam, o = _setup(ctx, name)
     H, W = hw
     want, cnt = o.render_product(H, W, 0, spp, 1234)
@@ -238,69 +238,69 @@ def test_render_bit_exact_vs_oracle(ctx, name, hw, spp):
         diff = np.nonzero((got.view(np.uint32) != want.view(np.uint32)).any(axis=2))
         assert len(diff[0]) == 0, (flags, len(diff[0]), got[diff][:3], want[diff][:3])
         assert (st.samples, st.rays, st.rays_ref_equiv) == tuple(int(x) for x in cnt)
-    # a split sample range accumulates to the same sums as the oracle run the same way
+    # the float interface adds the (rounded) sum of each call: the oracle run the same way
     a, _ = o.render_product(H, W, 0, spp // 2, 1234)
     a, _ = o.render_product(H, W, spp // 2, spp - spp // 2, 1234, accum=a)
-    import torch
     d = torch.zeros(H, W, 3, device="cuda")
     ctx.render_device(d.data_ptr(), H, W, spp // 2, 0, seed=1234)
     ctx.render_device(d.data_ptr(), H, W, spp - spp // 2, spp // 2, seed=1234)
     torch.cuda.synchronize()
     assert (d.cpu().numpy().view(np.uint32) == a.view(np.uint32)).all()
+    # the exact sums: any split of the sample range, either strategy, equals the oracle's one-shot sums
+    fx, _ = o.render_product_fixed(H, W, 0, spp, 1234)
+    q = torch.zeros(H, W, 3, device="cuda", dtype=torch.int64)
+    ctx.render_fixed_device(q.data_ptr(), H, W, spp // 3, 0, seed=1234, flags=abi.RT_RENDER_CLEAR)
+    ctx.render_fixed_device(q.data_ptr(), H, W, spp - spp // 3, spp // 3, seed=1234, flags=abi.RT_RENDER_WAVEFRONT)
+    torch.cuda.synchronize()
+    assert np.array_equal(q.cpu().numpy(), fx)
+    acc = torch.zeros(H, W, 3, device="cuda")
+    ctx.resolve_fixed_device(q.data_ptr(), H, W, spp, d_accum_ptr=acc.data_ptr())
+    torch.cuda.synchronize()
+    assert np.array_equal(acc.cpu().numpy().view(np.uint32), want.view(np.uint32))
 
 
 @pytest.mark.parametrize("name,hw,spp", [("cornell_box", (72, 128), 8), ("spheres", (54, 96), 8), ("bunny9k", (54, 96), 4)])
 def test_render_kernel_variants_bit_exact(ctx, name, hw, spp, monkeypatch):
-    """Every fused-kernel variant (RT_TRAV 0..22; 5 = warp-scheduled vote kernel, 6..8 = pool kernel with 2..4 slots
-    per lane, 9..11 = warp-synchronous kernel: binary + cooperative record tests, 8-wide tree, 8-wide + cooperative, 12..13 = persistent kernel
-    without reconvergence at the query boundary over the binary / 8-wide tree, 14 = streaming kernel: single steps with deferred record tests and shading, 15 = 4-wide tree, 16/17 = fused kernel with the if-if loop over the 4-/8-wide tree, 18/19 = the same with the while-while loop, 20 = box list for scenes of at most 32 primitives,
-    21/22 = if-if loop over the compact 4-/8-wide tree with 8-bit quantised boxes)
-    renders the oracle's image."""
-    s, cam, o = _setup(ctx, name)
+    """Every traversal the render kernel is compiled for (RT_TRAV, read at commit: 0 binary if-if at 64 registers,
+    1 binary while-while, 17 8-wide tree, 20 box list where the scene has one) renders the oracle's image."""
+    s, cam = _named(name)
+    camera = rt.core.camera_look_at(cam)
+    o = ck.OracleScene(s, camera)
     H, W = hw
     want, cnt = o.render_product(H, W, 0, spp, 99)
-    for trav in range(24):
+    for trav in (0, 1, 17, 20):
         monkeypatch.setenv("RT_TRAV", str(trav))
+        ctx.commit(s)
+        ctx.set_camera(camera)
         got, _, st = ctx.render_host(H, W, spp, seed=99, flags=abi.RT_RENDER_FUSED)
         assert (got.view(np.uint32) == want.view(np.uint32)).all(), trav
         assert (st.samples, st.rays, st.rays_ref_equiv) == tuple(int(x) for x in cnt), trav
+    monkeypatch.delenv("RT_TRAV")
+    ctx.commit(s)
 
 
-@pytest.mark.parametrize("name,hw,spp", [("spheres", (54, 96), 8), ("cornell_box", (72, 128), 7), ("bunny9k", (54, 96), 5)])
-def test_render_split_sample_slices(ctx, name, hw, spp):
-    """RT_RENDER_SPLIT (what Main / DistributedMain pass): a small image is rendered as S concurrent sample slices on S
-    streams and the slice sums are added in slice order, so the image is bit-identical to S consecutive calls over
-    the sub-ranges (oracle run the same way), with the counters of the whole range.  Large images are not split."""
+@pytest.mark.parametrize("name,hw,spp", [("spheres", (54, 96), 8), ("cornell_box", (67, 125), 7), ("bunny9k", (54, 96), 37)])
+def test_work_distribution_does_not_change_the_image(ctx, name, hw, spp, monkeypatch):
+    """The path kernel hands out (pixel, sample chunk) sub-units from (tile, chunk group) items drawn from a global
+    counter; which warp renders what is a race by design.  The exact sums do not depend on it: forced chunk sizes of
+    1, 3 (ragged against 7, 8 and 37 samples) and 16, items of 1 and 5 chunks, an image whose last tile row / column
+    is ragged — always the oracle's sums and counters."""
+    import torch
     s, cam, o = _setup(ctx, name)
     H, W = hw
-    _, cnt = o.render_product(H, W, 0, spp, 77)
-    # scene default (box list on Cornell) and the binary while-while loop with the automatic slice count (one sample per
-    # slice at these sizes), then a forced count of 3 (ragged last slice for 7 and 8 samples)
-    for trav, forced in ((None, None), ("1", None), (None, "3")):
-        env = {"RT_TRAV": trav, "RT_SPLIT": forced}
-        for k, v in env.items():
-            if v is not None:
-                os.environ[k] = v
-        try:
-            got, _, st = ctx.render_host(H, W, spp, seed=77, flags=abi.RT_RENDER_FUSED | abi.RT_RENDER_SPLIT)
-        finally:
-            for k in env:
-                os.environ.pop(k, None)
-        S = st.iterations
-        assert 1 < S <= 32 and st.kernel_launches == S + 1, (S, st.kernel_launches)
-        assert forced is None or S == int(forced)
-        chunk = -(-spp // S)
-        want = None
-        for z in range(S):
-            n = min(chunk, spp - z * chunk)
-            want, _ = o.render_product(H, W, z * chunk, n, 77, accum=want)
-        assert (got.view(np.uint32) == want.view(np.uint32)).all(), (trav, S)
+    want, cnt = o.render_product_fixed(H, W, 0, spp, 77)
+    q = torch.zeros(H, W, 3, device="cuda", dtype=torch.int64)
+    for chunk, item in ((None, None), ("1", "1"), ("3", "5"), ("16", "1"), ("2", "16")):
+        if chunk:
+            monkeypatch.setenv("RT_CHUNK", chunk)
+            monkeypatch.setenv("RT_ITEM_CHUNKS", item)
+        st = ctx.render_fixed_device(q.data_ptr(), H, W, spp, 0, seed=77, flags=abi.RT_RENDER_CLEAR)
+        torch.cuda.synchronize()
+        assert np.array_equal(q.cpu().numpy(), want), (chunk, item)
         assert (st.samples, st.rays, st.rays_ref_equiv) == tuple(int(x) for x in cnt)
-    # one sample per pixel stays whole; so do full-size frames, except over a mesh (as many slices as samples, <= 32)
-    _, _, st = ctx.render_host(H, W, 1, seed=77, flags=abi.RT_RENDER_SPLIT)
-    assert st.iterations == 1 and st.kernel_launches == 1
-    _, _, st = ctx.render_host(1080, 1920, 4, seed=77, flags=abi.RT_RENDER_SPLIT)
-    assert st.iterations == (4 if name == "bunny9k" else 1)
+        assert st.kernel_launches == 1 and st.work_items > 0
+        if chunk:
+            assert st.chunk_samples == min(int(chunk), spp)
 
 
 def test_render_textured_sphere_close(ctx):
@@ -325,10 +325,10 @@ def test_max_depth_and_resolve(ctx):
         assert np.abs(rgb - ref_rgb).max() <= 1e-6
 
 
-def test_compact_wide_tree_full_size(ctx):
-    """Quantised boxes must only ever be LARGER than the float boxes: on a 1 M-triangle soup (the size class the compact
-    tree is built for; the oracle would need minutes) modes 13 / 14 return exactly the hits of the binary tree (mode 2)
-    on 400 k primary and random rays, and on rays scaled far away from / shrunk towards the origin."""
+def test_wide_tree_full_size(ctx):
+    """A 1 M-triangle soup (the oracle would need minutes): the 8-wide tree and the binary while-while loop return
+    exactly the hits of the binary if-if loop on 400 k primary and random rays, and on rays scaled far away from the
+    scene box."""
     s, cam = scenes.soup(1000000)
     ctx.commit(s)
     ctx.set_camera(rt.core.camera_look_at(cam))
@@ -338,7 +338,7 @@ def test_compact_wide_tree_full_size(ctx):
     rr = np.concatenate([rr, far])
     want = ctx.trace_closest(rr, mode=2)
     assert (want["obj"] >= 0).mean() > 0.3
-    for mode in (13, 14):
+    for mode in (3, 4):
         got = ctx.trace_closest(rr, mode=mode)
         bad = ck.hits_equal(got, want)
         assert len(bad) == 0, (mode, len(bad), rr[bad[:3]], got[bad[:3]], want[bad[:3]])
@@ -346,20 +346,18 @@ def test_compact_wide_tree_full_size(ctx):
 
 def test_full_size_properties(ctx):
     """BASELINE sizes through size-independent properties: additivity over sample ranges and
-    strategy independence (fused == wavefront) at 1920x1080 on the full bunny."""
+    strategy independence (path kernel == wavefront) of the exact sums at 1920x1080 on the full bunny."""
     import torch
     s, cam, o = _setup(ctx, "bunny")
     H, W = 1080, 1920
-    a = torch.zeros(H, W, 3, device="cuda")
-    b = torch.zeros(H, W, 3, device="cuda")
-    ctx.render_device(a.data_ptr(), H, W, 2, 0, seed=11, flags=abi.RT_RENDER_FUSED)
-    ctx.render_device(b.data_ptr(), H, W, 2, 0, seed=11, flags=abi.RT_RENDER_WAVEFRONT)
+    a = torch.zeros(H, W, 3, device="cuda", dtype=torch.int64)
+    b = torch.zeros(H, W, 3, device="cuda", dtype=torch.int64)
+    ctx.render_fixed_device(a.data_ptr(), H, W, 2, 0, seed=11, flags=abi.RT_RENDER_FUSED)
+    ctx.render_fixed_device(b.data_ptr(), H, W, 2, 0, seed=11, flags=abi.RT_RENDER_WAVEFRONT)
     torch.cuda.synchronize()
-    assert torch.equal(a.view(torch.int32), b.view(torch.int32))
-    # rows of the full frame equal the oracle on a sampled band
-    c = torch.zeros(H, W, 3, device="cuda")
-    ctx.render_device(c.data_ptr(), H, W, 1, 0, seed=11)
-    ctx.render_device(c.data_ptr(), H, W, 1, 1, seed=11)
+    assert torch.equal(a, b)
+    c = torch.zeros(H, W, 3, device="cuda", dtype=torch.int64)
+    ctx.render_fixed_device(c.data_ptr(), H, W, 1, 1, seed=11)
+    ctx.render_fixed_device(c.data_ptr(), H, W, 1, 0, seed=11)
     torch.cuda.synchronize()
-    # (x0) + x1 == x0 + x1 for two samples: identical float sums
-    assert torch.equal(a.view(torch.int32), c.view(torch.int32))
+    assert torch.equal(a, c)

@@ -41,12 +41,12 @@ def main():
         for ex in extra:
             if ex:
                 os.environ[ex[0]] = ex[1]
-            bs = ctx.commit(scene)
             for tv in a.trav.split(","):
-                os.environ["RT_TRAV"] = tv
+                os.environ["RT_TRAV"] = tv  # read at commit
+                bs = ctx.commit(scene)
                 st = ctx.render_device(acc.data_ptr(), H, W, 1, 0, seed=1, flags=flags | rt.abi.RT_RENDER_CLEAR | rt.abi.RT_RENDER_PROFILE)
                 nodes, prims, rays1 = st.node_visits, st.prim_tests, st.rays
-                simt = st.sched_lanes / max(32 * st.sched_iters, 1)
+                simt = 0.0
                 best = 1e30
                 for _ in range(a.reps):
                     st = ctx.render_device(acc.data_ptr(), H, W, spp, 0, seed=1, flags=flags | rt.abi.RT_RENDER_CLEAR)
