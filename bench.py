@@ -1,14 +1,20 @@
-"""bench.py — the reference's headline metric (path Msamples/s) on BASELINE.json configs[1]:
-scenes/cornell_box.cu at 1024x1024, 1024 spp, max depth 10, on N B200s of one node.
+"""bench.py — the reference's headline metric (path Msamples/s) on every BASELINE.json config, on N B200s of one node.
 
-A step = one full frame: every rank renders its GetWorkload share of the 1024 samples per pixel
-(sample partition, utils.cu:111-113) and the float accumulation buffers are summed at rank 0 with
-one ncclReduce (replaces D2H + MPI_Reduce, utils.cu:115-125).  `value` = H*W*spp / step time with
-the scene resident in HBM; `e2e` = the same frame through host buffers (scene description H2D +
-BVH build + render + reduce + resolve + image D2H), i.e. what Main()/DistributedMain() do per run.
+Top level of the JSON line: BASELINE.json configs[1], scenes/cornell_box.cu at 1024x1024, 1024 spp, max depth 10.
+`workloads` carries the other configs with the same keys (spheres 400x225x16 at depth 10 and 50, bunny 1080p x256,
+birthday 1080p x512, triangle soups 1 M / 10 M at 4K x64), `hit_bit_exact` the primary-ray (t, hit) mismatch counts of
+the metric's last clause: against the CPU oracle, against the reference's CUDA code built --fmad=false, and against its
+default build (all on full-resolution pixel-centre rays).
 
-`--impl reference` times the reference's own sources compiled for the host (oracle/_ref, built from
-/root/reference by oracle/Makefile) on all host threads, on a bounded sample of the same frame.
+A step = one full frame: every rank renders its GetWorkload share of the samples of every pixel (sample partition,
+utils.cu:111-113) into exact 64-bit sums and the sums are added at rank 0 with one ncclReduce (replaces D2H +
+MPI_Reduce, utils.cu:115-125).  `value` = H*W*spp / step time with the scene resident in HBM; `e2e` = the same frame
+through host buffers (scene description H2D + BVH build + render + reduce + resolve + image D2H), i.e. what
+Main()/DistributedMain() do per run.
+
+`--impl reference` times the reference's own sources compiled for the host (oracle/_ref, built from /root/reference by
+oracle/Makefile) on all host threads, on a bounded sample of the same frame.
+`--workload X` benches one config alone (top level = that config); `--only-headline` skips the other configs.
 """
 import argparse
 import importlib
@@ -16,6 +22,7 @@ import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -26,20 +33,25 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 WORKLOADS = {
-    # name: (scene, H, W, spp)
-    "cornell_box": ("cornell_box", 1024, 1024, 1024),
-    "spheres": ("spheres", 225, 400, 16),
-    "bunny": ("bunny", 1080, 1920, 256),
-    "birthday": ("birthday", 1080, 1920, 512),
+    # name: (scene, H, W, spp, max depth)
+    "cornell_box": ("cornell_box", 1024, 1024, 1024, 10),
+    "spheres_d10": ("spheres", 225, 400, 16, 10),
+    "spheres_d50": ("spheres", 225, 400, 16, 50),
+    "bunny": ("bunny", 1080, 1920, 256, 10),
+    "birthday": ("birthday", 1080, 1920, 512, 10),
     # BASELINE.json configs[4]: procedural triangle soup, scene data >> L2: HBM-bound roofline
-    "soup1m": ("soup1000000", 2160, 3840, 64),
-    "soup10m": ("soup10000000", 2160, 3840, 64),
+    "soup1m": ("soup1000000", 2160, 3840, 64, 10),
+    "soup10m": ("soup10000000", 2160, 3840, 64, 10),
 }
-MAX_DEPTH = 10
+WORKLOADS["spheres"] = WORKLOADS["spheres_d10"]
+HEADLINE = "cornell_box"
+# the other configs in the default run: (timed steps, warm-up steps)
+OTHERS = {"spheres_d10": (5, 3), "spheres_d50": (5, 3), "bunny": (3, 3), "birthday": (3, 3), "soup1m": (2, 1), "soup10m": (2, 1)}
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clocks / throttle reasons sampled for the whole run (B200_PROFILING.md); a timed region reads the
+    samples that arrived between its start and its end."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -49,7 +61,7 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
                                           "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -58,18 +70,16 @@ class ClockSampler:
 
     def _read(self):
         for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+            self.lines.append((time.perf_counter(), ln.strip()))
 
-    def stop(self):
+    def region(self, t0, t1):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
+        lines = [ln for (t, ln) in list(self.lines) if t0 <= t <= t1 + 0.15]
+        if not lines:  # a region shorter than the sampling period: the nearest samples
+            lines = [ln for (t, ln) in list(self.lines) if t0 - 0.3 <= t <= t1 + 0.3]
         sm, mx, reasons, power = [], [], set(), []
-        for ln in self.lines:
+        for ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -85,6 +95,14 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
 
 def load_peaks():
     try:
@@ -95,12 +113,16 @@ def load_peaks():
 
 
 def load_profile_constants():
-    """Per-sample figures measured with ncu (profiles/): warp instructions per sample of the dominant kernel."""
+    """Per-launch figures measured with ncu (profiles/): DRAM bytes, lanes per instruction of the dominant kernel."""
     try:
         with open(os.path.join(ROOT, "profiles", "constants.json")) as f:
             return json.load(f)
     except OSError:
         return {}
+
+
+def scene_of(rt, name):
+    return rt.scenes.by_name(name)
 
 
 def ref_scene_named(ck, name):
@@ -123,7 +145,7 @@ def reference_arm(args, workload):
         return
     import checkers as ck
 
-    name, H, W, spp = WORKLOADS[workload]
+    name, H, W, spp, depth = WORKLOADS[workload]
     if name.startswith("soup"):
         print(json.dumps({"impl": "reference", "unavailable": "no bounded sample of a 1M+ triangle frame finishes on the host "
                           "reference build (2048-triangle leaves, bvh.cuh:71-98)"}))
@@ -131,7 +153,7 @@ def reference_arm(args, workload):
     base = {"impl": "reference", "metric": "path Msamples/s", "unit": "Msamples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"scenes/{name}.cu {W}x{H} {spp}spp depth{MAX_DEPTH}"}}
+            "config": {"workload": f"scenes/{name}.cu {W}x{H} {spp}spp depth10"}}
     kind = "reference" if ck.have_ref() else "port"
     threads = os.cpu_count() or 1
     if kind == "reference":
@@ -143,11 +165,9 @@ def reference_arm(args, workload):
         o = ck.OracleScene(scene)
         o.camera_look_at(cam)
         run = lambda rows, s: o.render_reference(rows, W, s, 10086, nthreads=threads)  # noqa: E731
-    # bounded sample: the top `rows` rows of the frame at 1 spp, sized from a probe to ~6 s per step
-    # (the host harness renders rows [0, rows) of a rows x W image: same camera rays per row only if
-    #  rows == H, so the sample keeps rows == H and bounds spp instead)
+    # bounded sample: the full frame at spp_s samples per pixel, sized from a probe to ~6 s per step
     t0 = time.perf_counter()
-    run(H // 16, 1) if kind == "port" else ref.render(H // 16, W, 1, post=0, nthreads=threads)
+    run(H // 16, 1)
     probe = time.perf_counter() - t0
     full_1spp = probe * 16
     spp_s = max(1, min(spp, int(6.0 / max(full_1spp, 1e-6))))
@@ -168,7 +188,7 @@ def reference_arm(args, workload):
     print(json.dumps(base))
 
 
-def cpu_baseline(name, H, W, spp, budget_s=12.0):
+def cpu_baseline(name, H, W, spp, budget_s=10.0):
     import checkers as ck
 
     threads = os.cpu_count() or 1
@@ -201,31 +221,293 @@ def cpu_baseline(name, H, W, spp, budget_s=12.0):
             "sample": f"{label} at {spp_s} spp (of {spp}), {t:.1f} s"}
 
 
-def ref_cuda_baseline(name, H, W, scene, spp=16):
-    """The reference's own CUDA build on this GPU (baseline/_ref/ref_cuda, built from /root/reference by
-    baseline/Makefile): its PathTracing kernel timed its own way at `spp` samples (the kernel is linear in spp)."""
-    import tempfile
-    exe = os.path.join(ROOT, "baseline", "_ref", "ref_cuda")
-    if not os.path.exists(exe):
-        return {"unavailable": "baseline/_ref/ref_cuda not built"}
-    extra = []
-    tmp = tempfile.mkdtemp()
+def _ref_cuda_args(name, scene, tmp):
+    """Command-line extras that hand the reference CUDA harness the same synthetic mesh / texture."""
+    extra, ref_scene = [], name
     if name == "bunny":
         fp = os.path.join(tmp, "faces.bin")
         scene.meshes[0].astype(np.float32).tofile(fp)
         extra = ["--faces", fp]
-        spp = 2
     if name == "birthday":
         fp = os.path.join(tmp, "tex.bin")
         np.ascontiguousarray(scene.textures[0]).tofile(fp)
         extra = ["--tex", fp, str(scene.textures[0].shape[0]), str(scene.textures[0].shape[1])]
+    return ref_scene, extra
+
+
+def ref_cuda_baseline(name, H, W, scene, spp=16):
+    """The reference's own CUDA build on this GPU (baseline/_ref/ref_cuda, built from /root/reference by
+    baseline/Makefile): its PathTracing kernel timed its own way at `spp` samples (the kernel is linear in spp)."""
+    exe = os.path.join(ROOT, "baseline", "_ref", "ref_cuda")
+    if not os.path.exists(exe):
+        return {"unavailable": "baseline/_ref/ref_cuda not built"}
+    tmp = tempfile.mkdtemp()
+    ref_scene, extra = _ref_cuda_args(name, scene, tmp)
+    if name == "bunny":
+        spp = 2
     try:
-        p = subprocess.run([exe, name, str(H), str(W), str(spp), "3"] + extra, capture_output=True, text=True, timeout=240)
+        p = subprocess.run([exe, ref_scene, str(H), str(W), str(spp), "3"] + extra, capture_output=True, text=True, timeout=240)
         r = json.loads(p.stdout.strip().splitlines()[-1])
         return {"value": r["msamples_per_s"], "unit": "Msamples/s", "kind": "reference CUDA build, sm_100a, --fmad default",
                 "sample": f"full {W}x{H} frame at {spp} spp, best of 3, kernel-only (cudaEvents) as utils.cu:155-170", "ms": r["ms_best"]}
     except Exception as e:  # noqa: BLE001
         return {"unavailable": repr(e)[:200]}
+
+
+REF_HIT = np.dtype([("t", "<f8"), ("u", "<f8"), ("v", "<f8"), ("normal", "<f4", 3), ("hit", "<i4")])
+
+
+def hit_bit_exact(rt, ctx, name, H, W, scene, camspec, oracle_budget_s=8.0):
+    """BASELINE.json's `hit bit-exactness`: closest hits of full-resolution pixel-centre primary rays through
+    rt_trace_closest against (a) the CPU oracle (t bits, object / face ids, normal), (b) world->Hit of the reference's
+    own CUDA code built --fmad=false and (c) its default build (t bits, hit flag, normal; the reference has no ids)."""
+    import checkers as ck
+
+    out = {"rays": H * W}
+    scene_b, cam_b = scene, camspec
+    if name == "spheres":
+        # the layout is drawn inside user code (spheres.cu:54-80): nvcc's device front end evaluates the draws of one
+        # argument list left to right, g++ (the host build the oracle is pinned to) right to left; the GPU reference
+        # therefore renders the "ltr" scene, and so do we here
+        scene_b, cam_b, _ = rt.scenes.spheres(arg_order="ltr")
+    ctx.commit(scene_b)
+    camera = rt.core.camera_look_at(cam_b)
+    ctx.set_camera(camera)
+    rays = ctx.primary_rays(H, W)
+    mine = ctx.trace_closest(rays)
+    # (a) oracle: the reference's semantics on the host (its own BVH, AABB::Hit included); a stride keeps it in budget
+    o = ck.OracleScene(scene_b, camera)
+    stride = 1
+    t0 = time.perf_counter()
+    probe = o.trace(rays[::64], quirks=1)
+    dt = (time.perf_counter() - t0) * 64
+    while dt / stride > oracle_budget_s:
+        stride *= 2
+    want = o.trace(rays[::stride], quirks=1) if stride > 1 else o.trace(rays, quirks=1)
+    got = mine[::stride]
+    fields = ("t", "obj", "sub", "normal", "material")
+    bad = ck.hits_equal(got, want, fields)
+    out["mismatch_vs_oracle"] = int(len(bad))
+    out["oracle_rays"] = int(len(want))
+    del probe
+    # (b), (c) the reference's CUDA code
+    tmp = tempfile.mkdtemp()
+    ref_scene, extra = _ref_cuda_args(name, scene_b, tmp)
+    rp = os.path.join(tmp, "rays.bin")
+    rays.tofile(rp)
+    hit_m = mine["obj"] >= 0
+    for key, exe in (("ref_cuda_nofmad", "ref_cuda_nofmad"), ("ref_cuda_default", "ref_cuda")):
+        path = os.path.join(ROOT, "baseline", "_ref", exe)
+        if not os.path.exists(path):
+            out[f"mismatch_vs_{key}"] = None
+            continue
+        hp = os.path.join(tmp, key + "_hits.bin")
+        try:
+            subprocess.run([path, ref_scene, str(H), str(W), "1", "0"] + extra + ["--rays", rp, hp], capture_output=True,
+                           text=True, timeout=240, check=True)
+            rh = np.fromfile(hp, dtype=REF_HIT)
+            ref_hit = rh["hit"] != 0
+            both = ref_hit & hit_m
+            tb = (rh["t"].view(np.uint64) != mine["t"].view(np.uint64)) & both
+            nb = (rh["normal"].view(np.uint32) != mine["normal"].view(np.uint32)).any(axis=1) & both & (mine["t"] < 1e9)
+            flag = ref_hit != hit_m
+            rel = np.abs(rh["t"][both] - mine["t"][both]) / np.maximum(np.abs(mine["t"][both]), 1e-30)
+            out[f"mismatch_vs_{key}"] = int((tb | nb | flag).sum())
+            out[f"{key}_detail"] = {"t_bits": int(tb.sum()), "normal_bits": int(nb.sum()), "hit_flag": int(flag.sum()),
+                                    "max_rel_t": float(rel.max() if len(rel) else 0.0)}
+        except Exception as e:  # noqa: BLE001
+            out[f"mismatch_vs_{key}"] = None
+            out[f"{key}_detail"] = {"error": repr(e)[:160]}
+    d = out.get("ref_cuda_nofmad_detail", {})
+    out["max_rel_t"] = d.get("max_rel_t")
+    return out
+
+
+def pow_kat():
+    exe = os.path.join(ROOT, "baseline", "_ref", "ref_cuda_nofmad")
+    if not os.path.exists(exe):
+        return None
+    try:
+        p = subprocess.run([exe, "powkat", "0", "0", "0", "0"], capture_output=True, text=True, timeout=120)
+        return json.loads(p.stdout.strip().splitlines()[-1])
+    except Exception as e:  # noqa: BLE001
+        return {"error": repr(e)[:160]}
+
+
+class Runner:
+    """One context per process; benches one workload at a time."""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+
+        self.torch, self.dist, self.args = torch, dist, args
+        self.rt = importlib.import_module("ray-tracing-cuda_b200")
+        self.rdist = importlib.import_module("ray-tracing-cuda_b200.distributed")
+        self.rank, self.world, self.local = self.rdist.init_process_group()
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.ctx = self.rt.Context(self.local)
+        if self.world > 1:
+            self.rdist.bind_nccl(self.ctx)
+        self.stream = torch.cuda.current_stream()
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)  # > 126 MB L2
+        self.peaks, self.peak_kind = load_peaks()
+        self.consts = load_profile_constants()
+        self.props = torch.cuda.get_device_properties(self.local)
+        self.sampler = ClockSampler(self.local)
+        if self.rank == 0:
+            self.sampler.start()
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def timed(self, fn, steps, warmup):
+        torch = self.torch
+        for _ in range(warmup):
+            fn()
+            self.flush.fill_(1)
+        times = []
+        self.barrier()
+        for _ in range(steps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            self.barrier()
+            e0.record(self.stream)
+            fn()
+            e1.record(self.stream)
+            self.barrier()
+            times.append(e0.elapsed_time(e1))
+            self.flush.fill_(1)  # L2 flush between timed iterations
+        self.barrier()
+        t = torch.tensor([float(np.sum(times))], device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item()) / steps
+
+    def bench(self, workload, steps, warmup, baselines):
+        torch, rt, ctx, args = self.torch, self.rt, self.ctx, self.args
+        rank, world = self.rank, self.world
+        name, H, W, spp, depth = WORKLOADS[workload]
+        if args.spp:
+            spp = args.spp
+        if args.depth > 0:
+            depth = args.depth
+        scene, camspec = scene_of(rt, name)
+        camera = rt.core.camera_look_at(camspec)
+        build = ctx.commit(scene)
+        ctx.set_camera(camera)
+        count, begin = self.rdist.partition(spp, rank, world)
+        flags = {"auto": 0, "fused": rt.abi.RT_RENDER_FUSED, "wavefront": rt.abi.RT_RENDER_WAVEFRONT}[args.strategy]
+        sp = self.stream.cuda_stream
+        sums = torch.zeros(H, W, 3, device=self.dev, dtype=torch.int64)
+        rgb = torch.zeros(H, W, 3, device=self.dev)
+        rgb_host = torch.zeros(H, W, 3).pin_memory()
+        CLEAR = rt.abi.RT_RENDER_CLEAR
+
+        def step_device():
+            ctx.render_fixed_device(sums.data_ptr(), H, W, count, begin, depth, seed=1, flags=flags | CLEAR, stream=sp)
+            if world > 1:
+                ctx.reduce_fixed(None, sums.data_ptr(), H * W * 3, 0, sp)
+
+        def step_e2e():
+            ctx.commit(scene)  # host description -> device records + BVH (H2D inside)
+            ctx.set_camera(camera)
+            ctx.render_fixed_device(sums.data_ptr(), H, W, count, begin, depth, seed=1, flags=flags | CLEAR, stream=sp)
+            if world > 1:
+                ctx.reduce_fixed(None, sums.data_ptr(), H * W * 3, 0, sp)
+            if rank == 0:
+                ctx.resolve_fixed_device(sums.data_ptr(), H, W, spp, None, rgb.data_ptr(), None, sp)
+                rgb_host.copy_(rgb, non_blocking=True)
+            self.stream.synchronize()
+
+        t0 = time.perf_counter()
+        ms = self.timed(step_device, steps, warmup)
+        t1 = time.perf_counter()
+        clocks = self.sampler.region(t0, t1) if rank == 0 else None
+        # one more step for ray counts and the kernel-only time, then a stats launch (counters of the same frame at
+        # reduced spp: per-ray figures are spp independent)
+        st = ctx.render_fixed_device(sums.data_ptr(), H, W, count, begin, depth, seed=1, flags=flags | CLEAR, stream=sp)
+        prof_spp = max(1, min(count, 4))
+        st_prof = ctx.render_fixed_device(sums.data_ptr(), H, W, prof_spp, begin, depth, seed=1,
+                                          flags=flags | CLEAR | rt.abi.RT_RENDER_PROFILE, stream=sp)
+        ms_e2e = self.timed(step_e2e, max(1, min(steps, 3)), 1)
+        rays = torch.tensor([float(st.rays), float(st.rays_ref_equiv)], device=self.dev, dtype=torch.float64)
+        if world > 1:
+            self.dist.all_reduce(rays)
+        if rank != 0:
+            return None
+        peaks, consts = self.peaks, self.consts
+        samples = H * W * spp
+        h2d = int(scene.hitables.nbytes + scene.materials.nbytes + sum(m.nbytes for m in scene.meshes) +
+                  sum(t.nbytes for t in scene.textures) + 96)
+        kern_ms = st.render_ms
+        fused_run = st.iterations == 0
+        sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
+        # Roofline of the dominant kernel.  Cache-resident scenes (C1-C4): the bound is SM instruction issue (SURVEY 8d,
+        # DESIGN 3): peak = SMs x 4 schedulers x f_clk warp-instructions/s at the clock sampled DURING the run.
+        # Algorithmic work per launch (SURVEY 8d figures x the counters of a stats launch of the same frame): 23 flops
+        # per box test, 52 per ray-triangle record test, 23 per accepted hit, /1.3 (FMA-fused instruction count) + 12
+        # control instructions per box test; one warp instruction = 32 lanes.
+        boxes, recs_tested = float(st_prof.node_visits), float(st_prof.prim_tests)
+        scale = float(count) / max(prof_spp, 1)
+        thread_inst = ((23.0 * boxes + 52.0 * recs_tested + 23.0 * float(st_prof.rays)) / 1.3 + 12.0 * boxes) * scale
+        issue_peak = self.props.multi_processor_count * 4 * sm_mhz * 1e6
+        achieved = thread_inst / 32.0 / (kern_ms * 1e-3)
+        is_soup = name.startswith("soup")
+        base_name = "spheres" if name == "spheres" else workload
+        traffic = consts.get("dram_bytes_per_launch", {}).get(base_name)
+        if traffic is not None and is_soup:  # soups: node / record misses scale with the samples of the launch
+            traffic = int(traffic * float(count) / consts.get("dram_bytes_capture_spp", {}).get(base_name, count))
+        roofline = {"bound": "issue", "achieved": achieved / 1e9, "peak": issue_peak / 1e9, "unit": "Gwarp-inst/s",
+                    "frac": achieved / issue_peak, "traffic": traffic,
+                    "traffic_source": "dram bytes of the committed ncu capture of this workload (profiles/constants.json), "
+                                      "not measured in this run",
+                    "kernel": "k_render" if fused_run else "k_wf_extend", "kernel_ms": kern_ms, "sm_mhz": sm_mhz,
+                    "peak_source": "148 SMs x 4 issue slots x sampled SM clock (B200_PROFILING.md / SURVEY 8d); not a tensor or HBM bound",
+                    "algorithmic": {"box_tests_per_ray": boxes / max(float(st_prof.rays), 1.0),
+                                    "record_tests_per_ray": recs_tested / max(float(st_prof.rays), 1.0),
+                                    "thread_inst_per_ray": thread_inst / max(float(st.rays), 1.0)},
+                    "measured_ncu": consts.get("ncu", {}).get(base_name)}
+        if is_soup:
+            # Scene data (48 B records + 32 B nodes) is far larger than L2 and bounce rays are incoherent: the bound is
+            # HBM.  Algorithmic bytes per launch = every box test reads its 32-byte node, every record test its 48-byte
+            # record (SURVEY 8d), plus the sums read + written once.  `frac` rises with the box tests of a worse tree,
+            # so the line also carries `dram_frac`: the DRAM bytes ncu measured for this workload / kernel time / peak.
+            alg = (32.0 * boxes + 48.0 * recs_tested) * scale + H * W * 48
+            a_gbs = alg / (kern_ms * 1e-3) / 1e9
+            roofline.update({"bound": "hbm", "achieved": a_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                             "frac": a_gbs / peaks["hbm_gbs"], "peak_source": f"{self.peak_kind} MEASURED_PEAKS.json hbm_gbs",
+                             "dram_frac": (traffic / (kern_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]) if traffic else None,
+                             "issue": {"achieved": achieved / 1e9, "peak": issue_peak / 1e9, "frac": achieved / issue_peak}})
+        label = (f"synthetic triangle soup {build.n_tris} tris {W}x{H} {spp}spp depth{depth}" if is_soup
+                 else f"scenes/{name}.cu {W}x{H} {spp}spp depth{depth}")
+        out = {"metric": "path Msamples/s", "value": samples / ms / 1e3, "unit": "Msamples/s", "n_gpus": world, "steps": steps,
+               "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+               "dtype": "f32", "data": "synthetic",
+               "config": {"workload": label, "partition": f"spp/{world}",
+                          "l2": "flushed between timed steps (256 MiB write)", "strategy": args.strategy,
+                          "prims": build.n_prims, "nodes": build.n_nodes,
+                          "chunk_samples": int(st.chunk_samples), "work_items": int(st.work_items)},
+               "mrays_per_s": float(rays[0].item()) / ms / 1e3, "mrays_ref_equiv_per_s": float(rays[1].item()) / ms / 1e3,
+               "rays_per_sample": float(rays[0].item()) / samples, "frame_ms": ms,
+               "e2e": {"value": samples / ms_e2e / 1e3, "unit": "Msamples/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
+                       "d2h_bytes_per_step": H * W * 12},
+               "gpu_launches": int(st.kernel_launches * steps),
+               "roofline": roofline, "clocks": clocks,
+               "build": {"ms": build.build_ms, "max_depth": build.max_depth, "sah": build.sah_cost,
+                         "wide_nodes": build.n_wide_nodes, "wide_depth": build.wide_depth}}
+        if baselines and is_soup:
+            out["cpu_baseline"] = {"unavailable": "the host reference build scans meshes with 2048-triangle leaves (bvh.cuh:71-98): "
+                                                  "no bounded sample of a 1M+ triangle frame finishes in the bench budget"}
+        elif baselines:
+            if workload != "spheres_d50":  # the reference hard-codes depth 10 (ray_tracing.cu:10)
+                out["cpu_baseline"] = cpu_baseline(name, H, W, spp, 10.0 if workload == HEADLINE else 4.0)
+                out["ref_cuda_baseline"] = ref_cuda_baseline(name, H, W, scene)
+            if workload != "spheres_d10" and workload != "spheres_d50" or workload == "spheres_d10":
+                pass
+        return out
 
 
 def main():
@@ -234,194 +516,45 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="cornell_box", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS), help="bench this config alone")
+    ap.add_argument("--only-headline", action="store_true", help="skip the other BASELINE configs and hit_bit_exact")
     ap.add_argument("--spp", type=int, default=0, help="override spp (diagnostic; the headline uses the config's)")
-    ap.add_argument("--depth", type=int, default=0,
-                    help="bounce limit (default 10 = the reference's TRACE_DEPTH_LIMIT, ray_tracing.cu:10; BASELINE config 1 "
-                         "also names depth 50: --workload spheres --depth 50)")
+    ap.add_argument("--depth", type=int, default=0, help="override the bounce limit (diagnostic)")
     ap.add_argument("--strategy", default="auto", choices=["auto", "fused", "wavefront"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-split", action="store_true", help="do not pass RT_RENDER_SPLIT (diagnostic)")
-    ap.add_argument("--ordered", action="store_true",
-                    help="pass RT_RENDER_ORDERED (experimental: heaviest tile first on meshes; off by default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
-        return reference_arm(args, args.workload)
+        return reference_arm(args, args.workload or HEADLINE)
 
-    import torch
-    import torch.distributed as dist
-
-    rt = importlib.import_module("ray-tracing-cuda_b200")
-    from importlib import import_module
-    rdist = import_module("ray-tracing-cuda_b200.distributed")
-
-    rank, world, local = rdist.init_process_group()
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    name, H, W, spp = WORKLOADS[args.workload]
-    if args.spp:
-        spp = args.spp
-    MAX_DEPTH = args.depth if args.depth > 0 else globals()["MAX_DEPTH"]
-    scene, camspec = rt.scenes.by_name(name)
-    ctx = rt.Context(local)
-    camera = rt.core.camera_look_at(camspec)
-    build = ctx.commit(scene)
-    ctx.set_camera(camera)
-    if world > 1:
-        rdist.bind_nccl(ctx)
-    count, begin = rdist.partition(spp, rank, world)
-    flags = {"auto": 0, "fused": rt.abi.RT_RENDER_FUSED, "wavefront": rt.abi.RT_RENDER_WAVEFRONT}[args.strategy]
-    stream = torch.cuda.current_stream()
-    sp = stream.cuda_stream
-    accum = torch.zeros(H, W, 3, device=dev)
-    rgb = torch.zeros(H, W, 3, device=dev)
-    rgb_host = torch.zeros(H, W, 3).pin_memory()
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def step_device():
-        ctx.render_device(accum.data_ptr(), H, W, count, begin, MAX_DEPTH, seed=1, flags=flags | rt.abi.RT_RENDER_CLEAR,
-                          stream=sp)
-        if world > 1:
-            ctx.reduce(None, accum.data_ptr(), H * W * 3, 0, sp)
-
-    def step_e2e():
-        ctx.commit(scene)  # host description -> device records + BVH (H2D inside)
-        ctx.set_camera(camera)
-        ctx.render_device(accum.data_ptr(), H, W, count, begin, MAX_DEPTH, seed=1, flags=flags | rt.abi.RT_RENDER_CLEAR,
-                          stream=sp)
-        if world > 1:
-            ctx.reduce(None, accum.data_ptr(), H * W * 3, 0, sp)
-        if rank == 0:
-            ctx.resolve_device(accum.data_ptr(), H, W, spp, rgb.data_ptr(), None, sp)
-            rgb_host.copy_(rgb, non_blocking=True)
-        stream.synchronize()
-
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
-            fn()
-            flush.fill_(1)
-        times = []
-        barrier()
-        for _ in range(steps):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            barrier()
-            e0.record(stream)
-            fn()
-            e1.record(stream)
-            barrier()
-            times.append(e0.elapsed_time(e1))
-            flush.fill_(1)  # L2 flush between timed iterations
-        barrier()
-        t = torch.tensor([float(np.sum(times))], device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()) / steps
-
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    ms = timed(step_device, args.steps, args.warmup)
-    clocks = sampler.stop() if rank == 0 else None
-    # one more step with stats for ray counts and the kernel-only time
-    st = ctx.render_device(accum.data_ptr(), H, W, count, begin, MAX_DEPTH, seed=1, flags=flags | rt.abi.RT_RENDER_CLEAR,
-                           stream=sp)
-    # stats launch (counters of the same frame at reduced spp: per-ray figures are spp independent)
-    prof_spp = max(1, min(count, 4))
-    st_prof = ctx.render_device(accum.data_ptr(), H, W, prof_spp, begin, MAX_DEPTH, seed=1,
-                                flags=flags | rt.abi.RT_RENDER_CLEAR | rt.abi.RT_RENDER_PROFILE, stream=sp)
-    ms_e2e = timed(step_e2e, max(1, min(args.steps, 3)), 1)
-
-    rays = torch.tensor([float(st.rays), float(st.rays_ref_equiv)], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(rays)
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-    peaks, peak_kind = load_peaks()
-    consts = load_profile_constants()
-    samples = H * W * spp
-    value = samples / ms / 1e3
-    h2d = int(scene.hitables.nbytes + scene.materials.nbytes + sum(m.nbytes for m in scene.meshes) +
-              sum(t.nbytes for t in scene.textures) + 96)
-    kern_ms = st.render_ms
-    fused_run = st.iterations == 0
-    kernel = "k_render" if fused_run else "k_wf_extend"
-    sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
-    props = torch.cuda.get_device_properties(local)
-    # Roofline of the dominant kernel.  The scene (nodes + records) is L1/L2 resident, so the bound is SM
-    # instruction issue: peak = SMs x 4 schedulers x f_clk warp-instructions/s at the
-    # clock sampled DURING the run.  Algorithmic work per launch (SURVEY §8d figures x the counters of a stats
-    # launch of the same frame): 23 flops per box test, 52 per ray-triangle record test, 23 per accepted hit,
-    # /1.3 (FMA-fused instruction count) + 12 control instructions per box test; one warp instruction = 32 lanes.
-    boxes, recs_tested = float(st_prof.node_visits), float(st_prof.prim_tests)
-    scale = float(count) / max(prof_spp, 1)  # the stats launch renders prof_spp samples per pixel
-    thread_inst = ((23.0 * boxes + 52.0 * recs_tested + 23.0 * float(st_prof.rays)) / 1.3 + 12.0 * boxes) * scale
-    issue_peak = props.multi_processor_count * 4 * sm_mhz * 1e6
-    achieved = thread_inst / 32.0 / (kern_ms * 1e-3)
-    alg_bytes = H * W * 24 + build.n_prims * 48 + build.n_nodes * 32  # accumulation r+w, scene read once
-    hbm_achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
-    is_soup = name.startswith("soup")
-    # DRAM bytes per launch from the committed ncu capture of the same workload (profiles/constants.json).  Cache-
-    # resident scenes: the traffic is the accumulation buffer + one read of the scene, independent of spp.  Soups:
-    # node/record misses dominate and scale with the samples of the launch (capture spp -> this launch's spp).
-    traffic = consts.get("dram_bytes_per_launch", {}).get(args.workload)
-    if traffic is not None and is_soup:
-        traffic = int(traffic * float(count) / consts.get("dram_bytes_capture_spp", {}).get(args.workload, count))
-    roofline = {"bound": "issue", "achieved": achieved / 1e9, "peak": issue_peak / 1e9, "unit": "Gwarp-inst/s",
-                "frac": achieved / issue_peak, "traffic": traffic,
-                "kernel": kernel, "kernel_ms": kern_ms, "sm_mhz": sm_mhz,
-                "peak_source": "148 SMs x 4 issue slots x sampled SM clock (B200_PROFILING.md / SURVEY 8d); not a tensor or HBM bound",
-                "algorithmic": {"box_tests_per_ray": boxes / max(float(st_prof.rays), 1.0),
-                                "record_tests_per_ray": recs_tested / max(float(st_prof.rays), 1.0),
-                                "thread_inst_per_ray": thread_inst / max(float(st.rays), 1.0)},
-                "hbm": {"bound": "hbm", "achieved": hbm_achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                        "frac": hbm_achieved / peaks["hbm_gbs"], "peak_source": f"{peak_kind} MEASURED_PEAKS.json hbm_gbs",
-                        "note": "scene is cache resident: HBM is not the binding resource"},
-                "measured_ncu": consts.get("ncu", {}).get(args.workload)}
-    if is_soup:
-        # Scene data (48 B records + 32 B nodes) is far larger than L2 and bounce rays are incoherent: the bound is
-        # HBM.  Algorithmic bytes per launch = every node visit reads its 32-byte node, every record test its 48-byte
-        # record, plus the accumulation buffer read + written once; cache hits make the measured DRAM
-        # traffic (profiles/, `traffic`) smaller than this.
-        alg = (32.0 * boxes + 48.0 * recs_tested) * scale + H * W * 24
-        a_gbs = alg / (kern_ms * 1e-3) / 1e9
-        roofline.update({"bound": "hbm", "achieved": a_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": a_gbs / peaks["hbm_gbs"], "peak_source": f"{peak_kind} MEASURED_PEAKS.json hbm_gbs",
-                         "issue": {"achieved": achieved / 1e9, "peak": issue_peak / 1e9, "frac": achieved / issue_peak}})
-        roofline.pop("hbm", None)
-    label = (f"synthetic triangle soup {build.n_tris} tris {W}x{H} {spp}spp depth{MAX_DEPTH}" if is_soup
-             else f"scenes/{name}.cu {W}x{H} {spp}spp depth{MAX_DEPTH}")
-    out = {"metric": "path Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
-           "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-           "dtype": "f32", "data": "synthetic",
-           "config": {"workload": label, "partition": f"spp/{world}",
-                      "l2": "flushed between timed steps (256 MiB write)", "strategy": args.strategy,
-                      "prims": build.n_prims, "nodes": build.n_nodes,
-                      "chunk_samples": int(st.chunk_samples), "work_items": int(st.work_items)},
-           "mrays_per_s": float(rays[0].item()) / ms / 1e3, "mrays_ref_equiv_per_s": float(rays[1].item()) / ms / 1e3,
-           "rays_per_sample": float(rays[0].item()) / samples,
-           "e2e": {"value": samples / ms_e2e / 1e3, "unit": "Msamples/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
-                   "d2h_bytes_per_step": H * W * 12},
-           "gpu_launches": int((st.kernel_launches + (1 if world > 1 else 0)) * args.steps),
-           "roofline": roofline, "clocks": clocks,
-           "build": {"ms": build.build_ms, "max_depth": build.max_depth, "sah": build.sah_cost,
-                     "wide_nodes": build.n_wide_nodes, "wide_depth": build.wide_depth}}
-    if not args.no_cpu_baseline and world == 1 and is_soup:
-        out["cpu_baseline"] = {"unavailable": "the host reference build scans meshes with 2048-triangle leaves (bvh.cuh:71-98): "
-                                              "no bounded sample of a 1M+ triangle frame finishes in the bench budget"}
-    elif not args.no_cpu_baseline and world == 1:
-        out["cpu_baseline"] = cpu_baseline(name, H, W, spp)
-        out["ref_cuda_baseline"] = ref_cuda_baseline(name, H, W, scene)
-    print(json.dumps(out))
-    if world > 1:
-        dist.destroy_process_group()
+    r = Runner(args)
+    single = args.workload is not None
+    head = args.workload or HEADLINE
+    baselines = (not args.no_cpu_baseline) and r.world == 1
+    out = r.bench(head, args.steps, args.warmup, baselines)
+    if not single and not args.only_headline and not args.spp and not args.depth:
+        others = {}
+        for w, (steps, warm) in OTHERS.items():
+            res = r.bench(w, steps, warm, baselines)
+            if res is not None:
+                for k in ("metric", "unit", "higher_is_better", "scaling", "vs_baseline", "dtype", "data", "n_gpus"):
+                    res.pop(k, None)
+                others[w] = res
+        if r.rank == 0:
+            out["workloads"] = others
+            if baselines:
+                hb = {}
+                for w in ("cornell_box", "spheres_d10", "bunny", "birthday"):
+                    name, H, W, _, _ = WORKLOADS[w]
+                    scene, camspec = scene_of(r.rt, name)
+                    hb[name] = hit_bit_exact(r.rt, r.ctx, name, H, W, scene, camspec)
+                hb["pow_kat_device"] = pow_kat()
+                out["hit_bit_exact"] = hb
+    if r.rank == 0:
+        r.sampler.stop()
+        print(json.dumps(out))
+    if r.world > 1:
+        r.dist.destroy_process_group()
 
 
 if __name__ == "__main__":

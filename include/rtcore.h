@@ -97,7 +97,9 @@ typedef struct rt_texture {
 /* Camera frame: the seven vectors + lens fields the reference Camera holds (camera.cuh:12-14). */
 typedef struct rt_camera {
   float position[3], lower_left_corner[3], horizontal[3], vertical[3], u[3], v[3], w[3];
-  int32_t is_defocus;
+  int32_t is_defocus; /* 0 pinhole; 1 thin lens sampled as the reference does (DiskRand, camera.cu:74-77: a SQUARE
+                         (0, lens_radius]^2 in the positive quadrant); 2 thin lens sampled as a uniform disk of radius
+                         lens_radius (what the name promises; scene API: RT_CAMERA_DISK=1) */
   double lens_radius;
 } rt_camera; /* 96 bytes */
 

@@ -12,7 +12,8 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtcore.so")
+# RT_CORE_LIB: an experiment build of the same ABI (csrc/Makefile OUT=...); diagnostics only
+LIB_PATH = os.environ.get("RT_CORE_LIB") or os.path.join(_HERE, "librtcore.so")
 _lib = None
 
 

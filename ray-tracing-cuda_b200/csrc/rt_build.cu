@@ -724,6 +724,10 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   s.sky_obj = sky_obj;
   s.sky_mat = sky_mat;
   s.has_spheres = n_spheres > 0;
+  {  // RT_SPHERE_POW=ieee: Sphere::Hit in plain IEEE arithmetic (the CPU oracle's form); default: CUDA's pow, as the reference
+    const char *env = getenv("RT_SPHERE_POW");
+    s.sphere_pow = (env && strcmp(env, "ieee") == 0) ? 0 : 1;
+  }
   // box list for the flat traversal (rt_flat.cuh): the single-primitive leaf nodes k_emit wrote
   ctx->flat.n = 0;
   if (n_bp > 0 && n_bp <= FLAT_MAX) {

@@ -106,6 +106,7 @@ struct DScene {
   int32_t n_recs, n_recs_seq, n_nodes, n_wnodes;
   int32_t sky_obj, sky_mat;  // first Sky in the list, or -1
   int32_t has_spheres;
+  int32_t sphere_pow;  // 1: Sphere::Hit's pow() calls go to CUDA's pow like the reference's (sphere_test); 0: IEEE x * x / sqrt
 };
 
 struct DCamera {  // camera.cuh:12-14
@@ -119,6 +120,7 @@ struct Hit {
   double t;
   int32_t rec;   // record index (BVH order in mode 0, list order in mode 1), REC_SKY, REC_NONE
   int32_t seq;   // 1: rec indexes recs_seq
+  int32_t box;   // box-list traversal: index of the box whose record was hit (the box a scattered ray starts on), else -1
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -158,6 +160,7 @@ struct RayQ {
 struct Range {
   double t_from, t_to;  // as passed to Hit()
   float tf_f;           // smallest float >= t_from : (double)t >= t_from  <=>  t >= tf_f
+  bool lib_pow;         // DScene::sphere_pow (sphere_test)
 };
 __host__ __device__ __forceinline__ float float_ge(double x) {  // smallest float >= x
 #ifdef __CUDA_ARCH__
@@ -202,10 +205,35 @@ __device__ __forceinline__ double rec_radius(float4 r1) {
 
 // sphere.cu:11-44 Sphere::Hit, decision part: the root the reference would return for an
 // unbounded t_to (near root if >= t_from, else far root), or false.
+//
+// The reference squares and takes roots with pow(x, 2) / pow(x, 0.5) (sphere.cu:13-21), which resolve to CUDA's
+// double pow(double, double).  That function is NOT correctly rounded: on the B200 its result differs from x * x on
+// 6 % and from sqrt(x) on 14 % of the operands of these scenes, by one ulp (bench.py hit_bit_exact.pow_kat_device; the
+// KAT kernel lives in baseline/ref_cuda_harness.cu).  lib_pow = true (the default, DScene::sphere_pow) therefore calls
+// the same pow() on the same operands: primary-ray t equals the reference's own CUDA code (built --fmad=false) bit for
+// bit.  The five pow calls cost ~10x the rest of the test, so they only run for rays the plain IEEE form (x * x, sqrt)
+// cannot rule out: a ray misses for certain when the IEEE discriminant is below -E, E = 1e-14 * (b^2 + 4a(|oc|^2 +
+// r^2)) — a bound ~40x the largest difference one ulp in each pow can make.  lib_pow = false is the IEEE form alone: what the
+// CPU oracle computes (oracle/rt_oracle.cpp, pinned to the reference's HOST build, whose glibc pow is correctly
+// rounded on all but ~1e-5 of the operands), used by the GPU-vs-oracle tests (RT_SPHERE_POW=ieee at commit).
 #ifndef RT_SPHERE_INLINE
 #define RT_SPHERE_INLINE __forceinline__
 #endif
-static __device__ RT_SPHERE_INLINE bool sphere_test(V3 c, double radius, const RayQ &r, double t_from, double *out_t) {
+// The reference's quadratic with CUDA's pow, out of line and by value: its ~1000 instructions must not weigh on the
+// registers of the loops that call sphere_test.  Returns {a, sqrt of the discriminant, or -1 for a miss}.
+struct SphereLibPow {
+  double a, sq;
+};
+static __device__ __noinline__ SphereLibPow sphere_quadratic_libdevice(double len_d, double len_oc, double radius, double b) {
+  SphereLibPow o;
+  o.a = pow(len_d, 2.0);
+  const double cc = pow(len_oc, 2.0) - pow(radius, 2.0);
+  const double disc = pow(b, 2.0) - 4 * o.a * cc;
+  o.sq = disc < 0 ? -1.0 : pow(disc, 0.5);
+  return o;
+}
+static __device__ RT_SPHERE_INLINE bool sphere_test(V3 c, double radius, const RayQ &r, double t_from, bool lib_pow,
+                                                    double *out_t) {
   double len_d = (double)length(r.d);
   double a = len_d * len_d;
   V3 oc = r.o - c;
@@ -213,8 +241,18 @@ static __device__ RT_SPHERE_INLINE bool sphere_test(V3 c, double radius, const R
   double len_oc = (double)length(oc);
   double cc = len_oc * len_oc - radius * radius;
   double disc = b * b - 4 * a * cc;
-  if (disc < 0) return false;
-  double sq = sqrt(disc);
+  double sq;
+  if (lib_pow) {
+    const double guard = 1e-14 * (b * b + 4 * a * (len_oc * len_oc + radius * radius));
+    if (disc < -guard) return false;
+    const SphereLibPow q = sphere_quadratic_libdevice(len_d, len_oc, radius, b);
+    if (q.sq < 0) return false;  // pow(disc, 0.5) of a non-negative disc is never negative
+    a = q.a;
+    sq = q.sq;
+  } else {
+    if (disc < 0) return false;
+    sq = sqrt(disc);
+  }
   double t = (-b - sq) / (2 * a);
   if (t_from <= t) {
     *out_t = t;
@@ -228,6 +266,60 @@ static __device__ RT_SPHERE_INLINE bool sphere_test(V3 c, double radius, const R
   return false;
 }
 
+// Sphere::Hit for the traversal loops when lib_pow is on.  Calling CUDA's pow five times for every sphere a ray MIGHT
+// hit cost 45 % of the spheres frame and 44 % of birthday's (one sphere; profiles/r02_f_*).  A traversal only has to
+// ORDER candidates, and the IEEE form of the test is within a known distance of the pow form: the root t with
+//   dt = guard / (sqrt(disc) * 2a) + 1e-13 |t|,   guard = 1e-14 (b^2 + 4a(|oc|^2 + r^2))
+// (disc differs by < guard / 40, a and the roots by 1 ulp each; measured difference <= 8e-13 |t|).  Every decision that
+// holds over the whole interval [t - dt, t + dt] — in range, nearer or farther than the best so far — is taken on the
+// IEEE value; anything closer than that is UNSURE and sends the query to the sequential scan, which calls pow for
+// every sphere (world_hit_seq; as rare as two surfaces within 1e-12 of each other).  The winner's t is then computed
+// ONCE with pow (finalize_sphere_hit): the same value the reference's CUDA code returns.
+enum : int { SPH_MISS = 0, SPH_HIT = 1, SPH_UNSURE = 2 };
+struct SphereApprox {
+  int state;
+  double t, dt;
+};
+static __device__ RT_SPHERE_INLINE SphereApprox sphere_test_interval(V3 c, double radius, const RayQ &r, double t_from) {
+  SphereApprox o;
+  o.t = o.dt = 0;
+  const double len_d = (double)length(r.d);
+  const double a = len_d * len_d;
+  const V3 oc = r.o - c;
+  const double b = (double)(2 * dot(r.d, oc));
+  const double len_oc = (double)length(oc);
+  const double l2 = len_oc * len_oc, r2 = radius * radius;
+  const double disc = b * b - 4 * a * (l2 - r2);
+  const double guard = 1e-14 * (b * b + 4 * a * (l2 + r2));
+  if (disc < -guard) {
+    o.state = SPH_MISS;
+    return o;
+  }
+  if (!(disc > guard)) {  // tangent within the guard (or NaN)
+    o.state = SPH_UNSURE;
+    return o;
+  }
+  const double sq = sqrt(disc), inv = 1.0 / (2 * a);
+  const double dsq = guard / sq * inv;
+  double t = (-b - sq) * inv, dt = dsq + 1e-13 * fabs(t);
+  if (!(t >= t_from + dt)) {
+    if (t > t_from - dt) {
+      o.state = SPH_UNSURE;
+      return o;
+    }
+    t = (-b + sq) * inv;
+    dt = dsq + 1e-13 * fabs(t);
+    if (!(t >= t_from + dt)) {
+      o.state = t > t_from - dt ? SPH_UNSURE : SPH_MISS;
+      return o;
+    }
+  }
+  o.state = SPH_HIT;
+  o.t = t;
+  o.dt = dt;
+  return o;
+}
+
 // ------------------------------------------------------------------------------------------------
 // Closest-hit bookkeeping with the reference's tie rules made order independent:
 //   smaller t wins; equal t: the lower list index wins (HitableList::Hit replaces only on
@@ -239,6 +331,10 @@ struct Best {
   float t_f;   // largest float <= t: a float candidate passes `t <= t_to` iff t <= t_f
   int32_t rec;
   int32_t obj, sub;
+  double t_err;  // > 0: t is the IEEE stand-in of a sphere hit (sphere_test_interval), exact value within t +- t_err
+  // one parallelogram whose two triangles both hit with the second one closer (resolve_quad_order); amb_rec < 0: none
+  int32_t amb_rec;  // its QUAD1 record
+  float amb_t0, amb_t1;
 };
 
 __device__ __forceinline__ void best_init(Best &b, double t_to) {
@@ -247,6 +343,9 @@ __device__ __forceinline__ void best_init(Best &b, double t_to) {
   b.rec = REC_NONE;
   b.obj = 0x7fffffff;
   b.sub = -1;
+  b.t_err = 0.0;
+  b.amb_rec = -1;
+  b.amb_t0 = b.amb_t1 = 0.f;
 }
 // `cond`: the candidate passed its own test and t <= the current bound.  Predicated selects, no branches.
 __device__ __forceinline__ bool best_offer(Best &b, bool cond, double t, int32_t rec, int32_t obj, int32_t sub) {
@@ -262,9 +361,13 @@ __device__ __forceinline__ bool best_offer(Best &b, bool cond, double t, int32_t
 }
 
 // One record against the ray.  Returns the number of records consumed (2 for a quad).
-// `ambiguous` is raised in the one situation where Parallelogram::Hit's "first triangle that
-// hits wins" (parallelogram.cu:25-41) depends on the t_to it was called with: both triangles
-// hit and the second is closer.  The caller then re-runs the ray through the sequential scan.
+// Parallelogram::Hit's "first triangle that hits wins" (parallelogram.cu:25-41) depends on the t_to it is called
+// with when both triangles hit and the second is closer (a ray through the shared diagonal, within rounding): the
+// traversal reports the first triangle, as the reference does when nothing listed EARLIER is closer, remembers the pair
+// in Best::amb_*, and resolve_quad_order settles the rest once the closest hit of everything else is known.
+// `ambiguous` (the caller re-runs the ray through the sequential scan) is left for what that cannot settle.
+// SPH = false: the scene has no Sphere (DScene::has_spheres) — the FP64 test and its registers are compiled out.
+template <bool SPH = true>
 __device__ __forceinline__ int rec_test(const float4 *__restrict__ recs, int k, const RayQ &r, const Range &rg, Best &b,
                                         bool &ambiguous) {
   float4 r0 = __ldg(recs + 3 * (size_t)k), r1 = __ldg(recs + 3 * (size_t)k + 1), r2 = __ldg(recs + 3 * (size_t)k + 2);
@@ -274,27 +377,117 @@ __device__ __forceinline__ int rec_test(const float4 *__restrict__ recs, int k, 
     float4 s0 = __ldg(recs + 3 * (size_t)k + 3), s1 = __ldg(recs + 3 * (size_t)k + 4), s2 = __ldg(recs + 3 * (size_t)k + 5);
     const bool h0 = tri_test(xyz(r0), xyz(r1), xyz(r2), r, rg.tf_f, &t0, &u, &v);
     const bool h1 = tri_test(xyz(s0), xyz(s1), xyz(s2), r, rg.tf_f, &t1, &u, &v);
-    ambiguous |= h0 & h1 & (t1 < t0);
+    if (h0 & h1 & (t1 < t0)) {
+      ambiguous |= b.amb_rec >= 0;  // a second such pair on one ray: the sequential scan decides
+      b.amb_rec = k + 1;
+      b.amb_t0 = t0;
+      b.amb_t1 = t1;
+    }
     // parallelogram.cu:25-41: the first triangle that hits wins; the second is only looked at when the first misses
     const bool first = h0;
     const float t = first ? t0 : t1;
     const bool cond = (h0 | h1) & (t <= b.t_f);
+    if constexpr (SPH) {  // too close to an approximate sphere hit to call
+      ambiguous |= cond & (b.t_err > 0) & ((double)t >= b.t - b.t_err);
+      b.t_err = cond ? 0.0 : b.t_err;
+    }
     if (best_offer(b, cond, (double)t, first ? k : k + 1, __float_as_int(r0.w), first ? 0 : 1)) b.t_f = t;
     return 2;
   }
   if (kind == K_TRI) {
     float t, u, v;
     const bool h = tri_test(xyz(r0), xyz(r1), xyz(r2), r, rg.tf_f, &t, &u, &v);
-    if (best_offer(b, h & (t <= b.t_f), (double)t, k, __float_as_int(r0.w), __float_as_int(r1.w))) b.t_f = t;
+    const bool cond = h & (t <= b.t_f);
+    if constexpr (SPH) {
+      ambiguous |= cond & (b.t_err > 0) & ((double)t >= b.t - b.t_err);
+      b.t_err = cond ? 0.0 : b.t_err;
+    }
+    if (best_offer(b, cond, (double)t, k, __float_as_int(r0.w), __float_as_int(r1.w))) b.t_f = t;
     return 1;
   }
-  if (kind == K_SPHERE) {
-    double t = 0;
-    const bool h = sphere_test(xyz(r0), rec_radius(r1), r, rg.t_from, &t);
-    if (best_offer(b, h && t <= b.t, t, k, __float_as_int(r0.w), 0)) b.t_f = float_le(t);
-    return 1;
+  if constexpr (SPH) {
+    if (kind == K_SPHERE) {
+      if (rg.lib_pow) {  // decide on the IEEE interval, compute the winner with pow afterwards (finalize_sphere_hit)
+        const SphereApprox q = sphere_test_interval(xyz(r0), rec_radius(r1), r, rg.t_from);
+        const double e = q.dt + b.t_err;
+        if (q.state == SPH_UNSURE) {
+          ambiguous = true;
+        } else if (q.state == SPH_HIT && q.t <= b.t + e) {
+          if (q.t < b.t - e) {
+            b.t = q.t;
+            b.t_err = q.dt;
+            b.t_f = float_ge(q.t + q.dt);  // a triangle at or below this may still win: it is checked against t_err
+            b.rec = k;
+            b.obj = __float_as_int(r0.w);
+            b.sub = 0;
+          } else {
+            ambiguous = true;
+          }
+        }
+        return 1;
+      }
+      double t = 0;
+      const bool h = sphere_test(xyz(r0), rec_radius(r1), r, rg.t_from, false, &t);
+      if (best_offer(b, h && t <= b.t, t, k, __float_as_int(r0.w), 0)) b.t_f = float_le(t);
+      return 1;
+    }
   }
   return 1;  // K_QUAD1 reached on its own never happens (leaves keep pairs together); K_SKY is not in the BVH
+}
+
+// The pending parallelogram of Best::amb_* (triangles at t1 < t0, list index q), given the closest hit b of a traversal
+// that let it report t0.  HitableList::Hit calls it with T = the closest report of the objects listed before it
+// (hitable_list.cu:11-21) and it answers t0 if t0 <= T, else t1 if t1 <= T (parallelogram.cu:25-41):
+//   b.t < t1, or b is the pair itself, or b.t >= t0   -> nothing changes (a closer object wins either way / T >= t0);
+//   t1 <= b.t < t0 and b is listed BEFORE q            -> T = b.t: the pair answers t1, which wins unless t1 == b.t
+//                                                         (HitableList replaces on `<` only);
+//   t1 <= b.t < t0 and b is listed AFTER q             -> depends on whether something listed before q lies in
+//                                                         [b.t, t0), a one-ulp window: the sequential scan decides.
+// The scan used to be the answer to EVERY such ray; on a scene with a mesh it tests every face (bunny: 69 451, 12 ms
+// for one lane, its warp waiting) and the handful of rays per frame that cross the backdrop's diagonal left 39 % of the
+// SM cycles of the launch idle (profiles/r02_i_bunny_two_phase_ncu_summary.txt).
+__device__ __forceinline__ void resolve_quad_order(const DScene &s, Best &b, bool &ambiguous) {
+  if (b.amb_rec < 0) return;
+  const double t0 = (double)b.amb_t0, t1 = (double)b.amb_t1;
+  if (b.t_err > 0 && (fabs(b.t - t0) <= b.t_err || fabs(b.t - t1) <= b.t_err)) {
+    ambiguous = true;
+    return;
+  }
+  if (b.t < t1 || b.t >= t0 || b.rec == b.amb_rec - 1) return;
+  const int q = __float_as_int(__ldg(s.recs + 3 * (size_t)b.amb_rec).w);
+  if (b.rec != REC_NONE && b.obj < q) {
+    if (t1 < b.t) {
+      b.t = t1;
+      b.t_f = b.amb_t1;
+      b.rec = b.amb_rec;
+      b.obj = q;
+      b.sub = 1;
+      b.t_err = 0.0;
+    }
+  } else {
+    ambiguous = true;
+  }
+}
+
+// The winner of a lib_pow traversal, when it is a sphere: its t as the reference computes it (CUDA's pow).
+// EXACT_T = false (render kernels): Trace only ever uses (float)t — hit_point = o + (float)t * d, ray_tracing.cu:32,
+// sphere.cu:23 — so when the whole interval [t - t_err, t + t_err] rounds to ONE float, that float is (float) of the
+// pow value too and pow is not called; it is when the interval straddles a float rounding boundary (~1e-5 of hits).
+template <bool SPH, bool EXACT_T = true>
+__device__ __forceinline__ void finalize_sphere_hit(const DScene &s, const RayQ &r, const Range &rg, Best &b, bool &ambiguous) {
+  if constexpr (SPH) {
+    if (b.t_err > 0 && b.rec >= 0) {
+      if constexpr (!EXACT_T) {
+        if (__double2float_rn(b.t - b.t_err) == __double2float_rn(b.t + b.t_err)) return;
+      }
+      const float4 r0 = __ldg(s.recs + 3 * (size_t)b.rec), r1 = __ldg(s.recs + 3 * (size_t)b.rec + 1);
+      double t = 0;
+      if (sphere_test(xyz(r0), rec_radius(r1), r, rg.t_from, true, &t) && t <= rg.t_to)
+        b.t = t;
+      else
+        ambiguous = true;  // the interval said hit, pow says miss: let the sequential scan decide
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -360,7 +553,7 @@ static __device__ __noinline__ Hit world_hit_seq(const DScene &s, const RayQ &r,
       k++;  // the QUAD1 record
     } else if (kind == K_SPHERE) {
       double t;
-      if (sphere_test(xyz(r0), rec_radius(r1), r, t_from, &t) && t <= obj_tto) {
+      if (sphere_test(xyz(r0), rec_radius(r1), r, t_from, s.sphere_pow != 0, &t) && t <= obj_tto) {
         obj_t = t;
         obj_rec = k;
         obj_hit = true;
@@ -379,6 +572,7 @@ static __device__ __noinline__ Hit world_hit_seq(const DScene &s, const RayQ &r,
   h.t = ok ? T : 0.0;
   h.rec = best_rec;
   h.seq = 1;
+  h.box = -1;
   return h;
 }
 
@@ -420,13 +614,14 @@ struct TravStats {
   uint32_t nodes, prims;
 };
 
-template <bool STATS>
+template <bool STATS, bool SPH = true, bool EXACT_T = true>
 __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r, double t_from, double t_to,
                                                   TravStats *st) {
   Range rg;
   rg.t_from = t_from;
   rg.t_to = t_to;
   rg.tf_f = float_ge(t_from);
+  rg.lib_pow = s.sphere_pow != 0;
   Best b;
   best_init(b, t_to);
   if (s.sky_obj >= 0) {  // sky.cu:18-27: always a candidate at t = 1e9
@@ -452,7 +647,7 @@ __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r
       if (cb & LEAF_FLAG) {
         int k = (int)ca, end = (int)(ca + (cb & ~LEAF_FLAG));
         while (k < end) {
-          int used = rec_test(s.recs, k, r, rg, b, ambiguous);
+          int used = rec_test<SPH>(s.recs, k, r, rg, b, ambiguous);
           if (STATS) st->prims += used;  // records tested (a parallelogram = 2 triangle records)
           k += used;
         }
@@ -496,11 +691,14 @@ __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r
       cb = e.y;
     }
   }
+  resolve_quad_order(s, b, ambiguous);
+  finalize_sphere_hit<SPH, EXACT_T>(s, r, rg, b, ambiguous);
   if (ambiguous || overflow) return world_hit_seq(s, r, t_from, t_to);
   Hit h;
   h.t = b.rec == REC_NONE ? 0.0 : b.t;
   h.rec = b.rec;
   h.seq = 0;
+  h.box = -1;
   return h;
 }
 
@@ -508,13 +706,14 @@ __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r
 // until it holds a leaf, then the warp tests leaf records together, so node steps and record tests
 // are not interleaved across lanes.  (Round 1 also measured speculative leaf postponement and pop-time culling:
 // both slower; removed.)
-template <bool STATS>
+template <bool STATS, bool SPH = true, bool EXACT_T = true>
 __device__ __forceinline__ Hit world_hit_bvh_ww(const DScene &s, const RayQ &r, double t_from, double t_to,
                                                 TravStats *st) {
   Range rg;
   rg.t_from = t_from;
   rg.t_to = t_to;
   rg.tf_f = float_ge(t_from);
+  rg.lib_pow = s.sphere_pow != 0;
   Best b;
   best_init(b, t_to);
   if (s.sky_obj >= 0) {  // sky.cu:18-27: always a candidate at t = 1e9
@@ -588,27 +787,30 @@ __device__ __forceinline__ Hit world_hit_bvh_ww(const DScene &s, const RayQ &r, 
       if (leaf_b) {
         int k = (int)leaf_a, end = (int)(leaf_a + (leaf_b & ~LEAF_FLAG));
         while (k < end) {
-          int used = rec_test(s.recs, k, r, rg, b, ambiguous);
+          int used = rec_test<SPH>(s.recs, k, r, rg, b, ambiguous);
           if (STATS) st->prims += used;  // records tested (a parallelogram = 2 triangle records)
           k += used;
         }
       }
     }
   }
+  resolve_quad_order(s, b, ambiguous);
+  finalize_sphere_hit<SPH, EXACT_T>(s, r, rg, b, ambiguous);
   if (ambiguous || overflow) return world_hit_seq(s, r, t_from, t_to);
   Hit h;
   h.t = b.rec == REC_NONE ? 0.0 : b.t;
   h.rec = b.rec;
   h.seq = 0;
+  h.box = -1;
   return h;
 }
 
 // Binary-tree traversal loops of the render kernels (identical hits): 0 if-if, 1 while-while.
-template <bool STATS, int TRAV>
+template <bool STATS, int TRAV, bool SPH = true, bool EXACT_T = true>
 __device__ __forceinline__ Hit world_hit_bvh(const DScene &s, const RayQ &r, double t_from, double t_to,
                                              TravStats *st) {
-  if (TRAV == 1) return world_hit_bvh_ww<STATS>(s, r, t_from, t_to, st);
-  return world_hit_bvh_ifif<STATS>(s, r, t_from, t_to, st);
+  if (TRAV == 1) return world_hit_bvh_ww<STATS, SPH, EXACT_T>(s, r, t_from, t_to, st);
+  return world_hit_bvh_ifif<STATS, SPH, EXACT_T>(s, r, t_from, t_to, st);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -631,6 +833,7 @@ __device__ __forceinline__ void sphere_uv(V3 p, float *u, float *v) {
 }
 
 // need_uv: only textured materials read u, v; callers that do not need them skip the arithmetic.
+template <bool SPH = true>
 __device__ __forceinline__ Surface surface_at(const DScene &s, const RayQ &r, const Hit &h, bool need_uv) {
   Surface sf;
   sf.normal = mk(0.f, 0.f, 0.f);
@@ -651,12 +854,14 @@ __device__ __forceinline__ Surface surface_at(const DScene &s, const RayQ &r, co
   sf.obj = __float_as_int(r0.w);
   sf.sub = __float_as_int(r1.w);
   if (sf.kind == K_SKY) return sf;
-  if (sf.kind == K_SPHERE) {
-    V3 c = xyz(r0);
-    V3 p = r.o + float(h.t) * r.d;
-    sf.normal = normalize(p - c);
-    if (need_uv) sphere_uv(sf.normal, &sf.u, &sf.v);
-    return sf;
+  if constexpr (SPH) {
+    if (sf.kind == K_SPHERE) {
+      V3 c = xyz(r0);
+      V3 p = r.o + float(h.t) * r.d;
+      sf.normal = normalize(p - c);
+      if (need_uv) sphere_uv(sf.normal, &sf.u, &sf.v);
+      return sf;
+    }
   }
   V3 e1 = xyz(r1), e2 = xyz(r2);
   V3 n = normalize(cross(e1, e2));
@@ -928,7 +1133,15 @@ __device__ __forceinline__ RayQ camera_sample(const DCamera &cam, int i, int j, 
   x = 2 * x - 1;
   y = 2 * y - 1;
   float lu = 0, lv = 0;
-  if (cam.is_defocus) {
+  if (cam.is_defocus == 2) {
+    // RT_CAMERA_DISK: the lens as a uniform DISK of radius lens_radius (r = R sqrt(u), phi = 2 pi v).  The
+    // reference's DiskRand (camera.cu:74-77) draws two uniforms in (0, lens_radius]: a square in the positive quadrant
+    float c, s;
+    sincos_2pi_scaled(u01(o[3]), &c, &s);
+    const float rad = sqrtf(u01(o[2])) * cam.lens_radius * 1.41421354f;
+    lu = rad * c;
+    lv = rad * s;
+  } else if (cam.is_defocus) {
     lu = u01(o[2]) * cam.lens_radius;
     lv = u01(o[3]) * cam.lens_radius;
   }

@@ -17,7 +17,7 @@ namespace rtc {
 
 constexpr int FLAT_MAX = 32;
 #ifndef RT_FLAT_UNROLL
-#define RT_FLAT_UNROLL 2
+#define RT_FLAT_UNROLL 1
 #endif
 constexpr int kFlatUnroll = RT_FLAT_UNROLL;
 
@@ -45,13 +45,22 @@ struct FlatParamT<true> {
     TF = fminf(fminf(fmaxf(ax_, bx_), fmaxf(ay_, by_)), fminf(fmaxf(az_, bz_), T_HI));           \
   }
 
-template <bool STATS>
+// self_box: the box the ray starts on (the record its path hit last: Hit::box), or -1.  That box always passes the
+// slab test at entry distance t_lo — the ray origin lies inside its padding — so "nearest box first" used to spend
+// its first, best-culling slot on the one candidate that almost never yields a hit, and every other candidate was
+// then tested in INDEX order against an unshrunk bound (profiles/r02_d_cornell_first_cut_ncu_summary.txt: record tests
+// = 45 % of all warp instructions at 12 of 32 lanes, a warp running the 3 candidates of its worst lane for an average
+// of 1.66).  Now the nearest box OTHER than self_box goes first (usually the hit, which culls what lies behind it),
+// then self_box (its own test cannot be skipped: grazing rays do re-hit their own parallelogram beyond t = 1e-3,
+// and the reference shows that acne), then the rest in index order, each re-tested against the closest hit.
+template <bool STATS, bool SPH = true, bool EXACT_T = true>
 __device__ __forceinline__ Hit world_hit_flat(const DScene &s, const FlatItems &fl, const RayQ &r, double t_from,
-                                              double t_to, TravStats *st) {
+                                              double t_to, TravStats *st, int self_box = -1) {
   Range rg;
   rg.t_from = t_from;
   rg.t_to = t_to;
   rg.tf_f = float_ge(t_from);
+  rg.lib_pow = s.sphere_pow != 0;
   Best b;
   best_init(b, t_to);
   if (s.sky_obj >= 0) {  // sky.cu:18-27: always a candidate at t = 1e9
@@ -65,6 +74,7 @@ __device__ __forceinline__ Hit world_hit_flat(const DScene &s, const FlatItems &
     }
   }
   bool ambiguous = false;
+  int hit_box = -1;
   const int n = fl.n;
   if (n > 0) {
     const float idx = slab_rcp(r.d.x), idy = slab_rcp(r.d.y), idz = slab_rcp(r.d.z);
@@ -74,6 +84,10 @@ __device__ __forceinline__ Hit world_hit_flat(const DScene &s, const FlatItems &
     // ---- all boxes, uniformly: hit mask + nearest entry.  Centre / half-extent form: 3 FFMA per axis
     //      (m = c/d - o/d, near = m - h/|d|, far = m + h/|d|) instead of 2 FFMA + min + max.
     const float adx = fabsf(idx), ady = fabsf(idy), adz = fabsf(idz);
+#ifdef RT_FLAT_NO_SELF  // experiment: round-1 order (nearest box first, whichever it is)
+    self_box = -1;
+#endif
+    const uint32_t self_bit = self_box >= 0 ? 1u << self_box : 0u;
     uint32_t mask = 0, bit = 1u, bit_min = 0u;
     float tn_min = CUDART_INF_F;
 #pragma unroll kFlatUnroll
@@ -86,15 +100,22 @@ __device__ __forceinline__ Hit world_hit_flat(const DScene &s, const FlatItems &
                              fminf(__fmaf_rn(he.z, adz, mz), t_hi0));
       const bool hit = tn <= tf * 1.00001f;
       mask |= hit ? bit : 0u;
-      const bool nearer = hit && tn < tn_min;
+      const bool nearer = hit && tn < tn_min && bit != self_bit;
       tn_min = nearer ? tn : tn_min;
       bit_min = nearer ? bit : bit_min;
       bit += bit;
     }
-    int j = __ffs(bit_min) - 1;
     if (STATS) st->nodes += n;
-    if (j >= 0) mask &= ~(1u << j);
-    // ---- candidates: nearest box first, then the mask in index order with a re-test against the closest hit
+    bool self_pending = (mask & self_bit) != 0;
+    mask &= ~self_bit;
+    int j = __ffs(bit_min) - 1;
+    if (j >= 0) {
+      mask &= ~(1u << j);
+    } else if (self_pending) {  // nothing but the ray's own box
+      j = self_box;
+      self_pending = false;
+    }
+    // ---- candidates
     const float4 *__restrict__ leaf = s.nodes + 2 * (size_t)(n - 1);
     uint32_t w_first = 0, w_count = 0;
     if (j >= 0) {
@@ -104,13 +125,22 @@ __device__ __forceinline__ Hit world_hit_flat(const DScene &s, const FlatItems &
     while (j >= 0) {
       int k = (int)w_first;
       const int end = k + (int)w_count;
+      const int rec_before = b.rec;
       while (k < end) {
-        int used = rec_test(s.recs, k, r, rg, b, ambiguous);
+        int used = rec_test<SPH>(s.recs, k, r, rg, b, ambiguous);
         if (STATS) st->prims += used;
         k += used;
       }
+      hit_box = b.rec != rec_before ? j : hit_box;
       const float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
       j = -1;
+      if (self_pending) {
+        self_pending = false;
+        j = self_box;
+        w_first = __float_as_uint(__ldg(leaf + 2 * j).w);
+        w_count = __float_as_uint(__ldg(leaf + 2 * j + 1).w) & ~LEAF_FLAG;
+        continue;
+      }
       while (mask) {
         const int c = __ffs(mask) - 1;
         mask &= mask - 1;
@@ -127,11 +157,14 @@ __device__ __forceinline__ Hit world_hit_flat(const DScene &s, const FlatItems &
       }
     }
   }
+  resolve_quad_order(s, b, ambiguous);
+  finalize_sphere_hit<SPH, EXACT_T>(s, r, rg, b, ambiguous);
   if (ambiguous) return world_hit_seq(s, r, t_from, t_to);
   Hit h;
   h.t = b.rec == REC_NONE ? 0.0 : b.t;
   h.rec = b.rec;
   h.seq = 0;
+  h.box = hit_box;
   return h;
 }
 #undef RT_FLAT_SLAB

@@ -14,19 +14,25 @@
 
 namespace rtc {
 
-// Work distribution of one rt_render call (k_render).  The sample range of the call is cut into chunks of `ch`
-// samples; a SUB-UNIT is (pixel, chunk): the samples one lane renders before it asks for more work.  An ITEM is
-// (8x4-pixel tile, `chunks_per_item` consecutive chunks) = up to 32 * chunks_per_item sub-units: what a warp draws
-// from the global counter with one atomic.  Items are numbered chunk-group major (all tiles of the first group,
-// then the second, ...), so the expensive tiles of an image are spread over the whole launch.
+// Work distribution of one rt_render call (k_render).  A SUB-UNIT is (pixel, chunk of samples): what one lane renders
+// before it asks for more work.  An ITEM is (8x4-pixel tile, some consecutive chunks) = 32 sub-units per chunk: what a
+// warp draws from the global counter with one atomic.  The sample range is cut in two phases:
+//   phase 1 — the first ~3/4 of the samples: chunks of ch1 = 16 samples, r1 chunks per item.  Big pieces: a warp
+//             stays on its tile (its rays keep touching the same part of the tree) and the hand-out is rare;
+//   phase 2 — the rest: chunks of ch2 <= 4 samples, one chunk per item.  Small pieces: whatever the cost of a sample
+//             varies by across the image, the launch ends within a few samples' time on every SM.
+// Items are numbered phase, then chunk group, then tile, so every pass sweeps the whole image and the expensive
+// tiles are spread over the launch.
 struct RenderArgs {
   int32_t height, width;
   int32_t spp_begin, spp_end;
   int32_t max_depth;
   uint32_t k0, k1;
-  int32_t ch, chunks_per_item, n_chunks;
+  int32_t ch1, r1, n_chunks1, spp1;  // phase 1 (spp1 = samples it covers; 0: none)
+  int32_t ch2;                       // phase 2
   int32_t tiles_x, n_tiles;
-  uint32_t n_items;
+  uint32_t tile_stride;  // tile of the i-th item of a sweep = i * tile_stride mod n_tiles (1: raster order)
+  uint32_t n_items1, n_items;
   unsigned int *work_counter;
   long long *fixed;  // [height * width * 3] radiance sums, 2^-30 units
 };
@@ -57,15 +63,16 @@ __device__ __forceinline__ rt_hit make_rt_hit(const DScene &s, const RayQ &r, co
 }
 
 // Traversals (RT_TRAV_*): 0 binary tree if-if, 1 binary tree while-while, 17 8-wide tree if-if, 20 box list.
-template <bool STATS, int TRAV>
+// EXACT_T = false: the caller only uses (float)Hit::t (render kernels; finalize_sphere_hit).
+template <bool STATS, int TRAV, bool SPH = true, bool EXACT_T = true>
 __device__ __forceinline__ Hit world_hit(const DScene &s, const FlatItems *fl, const RayQ &r, double t_from, double t_to,
-                                         TravStats *st) {
+                                         TravStats *st, int self_box = -1) {
   if constexpr (TRAV == 20)
-    return world_hit_flat<STATS>(s, *fl, r, t_from, t_to, st);
+    return world_hit_flat<STATS, SPH, EXACT_T>(s, *fl, r, t_from, t_to, st, self_box);
   else if constexpr (TRAV == 17)
-    return world_hit_wide_ifif<STATS, 8>(s, r, t_from, t_to, st);
+    return world_hit_wide_ifif<STATS, 8, SPH, EXACT_T>(s, r, t_from, t_to, st);
   else
-    return world_hit_bvh<STATS, TRAV>(s, r, t_from, t_to, st);
+    return world_hit_bvh<STATS, TRAV, SPH, EXACT_T>(s, r, t_from, t_to, st);
 }
 
 // ---- parity hook: HitableList::Hit on explicit rays ------------------------------------------------
@@ -112,6 +119,7 @@ __global__ void k_primary_rays(DCamera cam, int height, int width, float *rays) 
 // path continues with `ray` / `T` updated; else the path ends and `L` is its radiance (T * emitted, or 0).
 // A material either emits or scatters (DiffuseLight / Sky never scatter, the others emit 0: material.cu:3-6), so a
 // path contributes at most once, at its end — the back-to-front fold of ray_tracing.cu:50-52 collapses to T * emitted.
+template <bool SPH = true>
 __device__ __forceinline__ bool shade_hit(const DScene &s, const DCamera &cam, RayQ &ray, const Hit &h, const PathKey &pk,
                                           int depth, PhiloxCache *pc, V3 &T, V3 &L) {
   int mat_id;
@@ -138,7 +146,7 @@ __device__ __forceinline__ bool shade_hit(const DScene &s, const DCamera &cam, R
     // Scatter returns false (sky.cu:3-7, diffuse_light.cu:5-9): result = emitted
     float u = 0.f, v = 0.f;
     if (need_uv) {
-      Surface sf = surface_at(s, ray, h, true);
+      Surface sf = surface_at<SPH>(s, ray, h, true);
       u = sf.u;
       v = sf.v;
     }
@@ -146,7 +154,7 @@ __device__ __forceinline__ bool shade_hit(const DScene &s, const DCamera &cam, R
     L = T * emit(s, m, u, v, p);
     return false;
   }
-  Surface sf = surface_at(s, ray, h, need_uv);
+  Surface sf = surface_at<SPH>(s, ray, h, need_uv);
   V3 att;
   RayQ out;
   if (!scatter(s, m, ray, t, sf, pk, depth, scatter_word(cam, depth), pc, &att, &out)) return false;  // Emit() is 0
@@ -191,10 +199,11 @@ struct ShadeRet {
   PhiloxCache pc;
   bool alive;
 };
+template <bool SPH>
 static __device__ __noinline__ ShadeRet shade_hit_call(const DScene &s, const DCamera &cam, RayQ ray, Hit h, PathKey pk,
                                                        int depth, PhiloxCache pc, V3 T) {
   ShadeRet r;
-  r.alive = shade_hit(s, cam, ray, h, pk, depth, &pc, T, r.L);
+  r.alive = shade_hit<SPH>(s, cam, ray, h, pk, depth, &pc, T, r.L);
   r.ray = ray;
   r.T = T;
   r.pc = pc;
@@ -221,7 +230,7 @@ static __device__ __noinline__ CameraRet camera_sample_call(const DCamera &cam, 
 // sub-units of the warp's current item (pixels of one 8x4 tile first, so a warp's primary rays stay coherent); when
 // the item is used up lane 0 draws the next one from the global counter.  Radiance goes to the 64-bit fixed-point
 // sums (rt_device.cuh), so the image does not depend on who rendered what.
-template <bool STATS, int TRAV, int MINB>
+template <bool STATS, int TRAV, int MINB, bool SPH>
 __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, RenderArgs a, RenderCounters *ctr,
                                                       typename FlatParamT<TRAV == 20>::type fl = {}) {
   constexpr unsigned FULL = 0xffffffffu;
@@ -230,7 +239,7 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
   const unsigned lt_mask = (1u << lane) - 1u;
   // warp-uniform: the item being handed out
   uint32_t pool_next = 0, pool_end = 0;
-  int tile_px = 0, tile_py = 0, pool_k0 = 0;
+  int tile_px = 0, tile_py = 0, pool_k0 = 0, pool_ch = 1, pool_kend = 0;
   // lane: the sub-unit being rendered
   int pi = 0, pj = 0, k = 0, k_end = 0;
   bool finished = false, need_new = true;
@@ -246,6 +255,7 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
   RayQ ray;
   ray.o = ray.d = mk(0.f, 0.f, 0.f);
   int depth = 0;
+  int self_box = -1;  // box list: the box the current ray starts on
   unsigned long long n_samples = 0, n_rays = 0, n_rays_ref = 0, n_nodes = 0, n_prims = 0;
   TravStats ts;
   ts.nodes = ts.prims = 0;
@@ -263,13 +273,17 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
           finished |= want;
           break;
         }
-        const uint32_t group = it / (uint32_t)a.n_tiles, tile = it - group * (uint32_t)a.n_tiles;
+        const bool p1 = it < a.n_items1;
+        const uint32_t it2 = p1 ? it : it - a.n_items1;
+        const uint32_t group = it2 / (uint32_t)a.n_tiles;
+        const uint32_t tile = (uint32_t)(((unsigned long long)(it2 - group * (uint32_t)a.n_tiles) * a.tile_stride) % (uint32_t)a.n_tiles);
         tile_px = (int)(tile % (uint32_t)a.tiles_x) * 8;
         tile_py = (int)(tile / (uint32_t)a.tiles_x) * 4;
-        const int c0 = (int)group * a.chunks_per_item;
-        pool_k0 = a.spp_begin + c0 * a.ch;
+        pool_ch = p1 ? a.ch1 : a.ch2;
+        pool_k0 = p1 ? a.spp_begin + (int)group * a.r1 * a.ch1 : a.spp_begin + a.spp1 + (int)group * a.ch2;
+        pool_kend = p1 ? a.spp_begin + a.spp1 : a.spp_end;
         pool_next = 0;
-        pool_end = 32u * (uint32_t)min(a.chunks_per_item, a.n_chunks - c0);
+        pool_end = 32u * (uint32_t)(p1 ? a.r1 : 1);
       }
       const uint32_t rank = __popc(wm & lt_mask), take = min((uint32_t)__popc(wm), pool_end - pool_next);
       if (want && rank < take) {
@@ -277,8 +291,8 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
         pj = tile_px + (int)(su & 7u);
         pi = tile_py + (int)((su >> 3) & 3u);
         if (pi < a.height && pj < a.width) {  // edge tiles: sub-units outside the image are dropped
-          k = pool_k0 + (int)(su >> 5) * a.ch;
-          k_end = min(k + a.ch, a.spp_end);
+          k = pool_k0 + (int)(su >> 5) * pool_ch;
+          k_end = min(k + pool_ch, pool_kend);
           pk.pixel = (uint32_t)(pi * a.width + pj);
           want = false;
         }
@@ -299,13 +313,15 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
       }
       T = mk(1.f, 1.f, 1.f);
       depth = 0;
+      self_box = -1;
       need_new = false;
       n_samples++;
     }
     n_rays_ref++;
     bool alive = depth < a.max_depth;  // ray_tracing.cu:23: the query at depth == limit yields 0
     if (alive) {
-      const Hit h = world_hit<STATS, TRAV>(s, flp, ray, 1e-3, (double)CUDART_INF_F, &ts);
+      const Hit h = world_hit<STATS, TRAV, SPH, false>(s, flp, ray, 1e-3, (double)CUDART_INF_F, &ts, self_box);
+      self_box = h.box;
       n_rays++;
       if (STATS) {
         n_nodes += ts.nodes;
@@ -316,14 +332,14 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
       if (h.rec != REC_NONE) {
         V3 L;
         if constexpr (SLIM) {
-          ShadeRet sr = shade_hit_call(s, cam, ray, h, pk, depth, pc, T);
+          ShadeRet sr = shade_hit_call<SPH>(s, cam, ray, h, pk, depth, pc, T);
           alive = sr.alive;
           ray = sr.ray;
           T = sr.T;
           pc = sr.pc;
           L = sr.L;
         } else {
-          alive = shade_hit(s, cam, ray, h, pk, depth, &pc, T, L);
+          alive = shade_hit<SPH>(s, cam, ray, h, pk, depth, &pc, T, L);
         }
         if (!alive) add_radiance(a.fixed, (int)pk.pixel, L);
       }
@@ -517,7 +533,7 @@ __global__ void __launch_bounds__(128, MINB) k_wf_extend(DScene s, WfState w, in
     RayQ ray;
     ray.o = xyz(ro);
     ray.d = xyz(rd);
-    Hit h = world_hit_bvh<STATS, 0>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
+    Hit h = world_hit_bvh<STATS, 0, true, false>(s, ray, 1e-3, (double)CUDART_INF_F, &ts);
     n_rays++;
     // only the two .w words change: t and the record
     reinterpret_cast<float *>(w.ray_o + slot)[3] = float(h.t);
@@ -749,24 +765,48 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, boo
   return RT_OK;
 }
 
-// Work distribution of a k_render launch over `lanes` resident lanes (RenderArgs): chunks small enough that the last
-// sub-units of the launch are a small part of a lane's share, items small enough that the same holds for warps.
+// Work distribution of a k_render launch (RenderArgs), sized against a lane's share of the samples.  Measured on the
+// B200 (profiles/r02_*): one size does not fit — 16-sample chunks in items of up to 16 chunks left 60 % of the SM
+// cycles of the bunny frame idle behind the last heavy items (a sample on the mesh costs 30x one of the sky);
+// 4-sample chunks everywhere cost the uniform scenes 5-7 % (the hand-out, ~35 warp instructions, then runs in almost
+// every iteration of a warp) and the soups their locality; hence the two phases.  A launch with little work per lane
+// (spheres 400x225x16: 13 samples) is all phase 2 with 1-sample chunks.
+// RT_CHUNK / RT_ITEM_CHUNKS (diagnostics, tests): phase 1 with that chunk size and that many chunks per item over all
+// whole items, the remainder in phase 2 with the same chunk size.
 static void plan_work(const rt_ctx *ctx, RenderArgs &a, int minb) {
   const long long lanes = (long long)ctx->n_sm * minb * 128;
   const long long spp = a.spp_end - a.spp_begin;
   const long long per_lane = std::max<long long>(1, (long long)a.height * a.width * spp / lanes);
   const char *ec = getenv("RT_CHUNK"), *ei = getenv("RT_ITEM_CHUNKS");
-  long long ch = ec ? atoll(ec) : per_lane / 64;
-  ch = std::min<long long>(std::max<long long>(ch, 1), std::max<long long>(1, std::min<long long>(spp, 16)));
-  a.ch = (int)ch;
-  a.n_chunks = (int)((spp + ch - 1) / ch);
-  long long r = ei ? atoll(ei) : per_lane / 32 / ch;
-  r = std::min<long long>(std::max<long long>(r, 1), std::min<long long>(a.n_chunks, 16));
-  a.chunks_per_item = (int)r;
+  long long ch1 = 16, r1 = std::min<long long>(std::max<long long>(per_lane / 1024, 1), 16), spp1 = 0;
+  long long ch2 = std::min<long long>(std::max<long long>(per_lane / 64, 1), 4);
+  if (ec) {
+    ch1 = ch2 = std::min<long long>(std::max<long long>(atoll(ec), 1), 16);
+    r1 = std::min<long long>(std::max<long long>(ei ? atoll(ei) : 1, 1), 16);
+    spp1 = r1 > 1 ? spp / (ch1 * r1) * (ch1 * r1) : 0;
+  } else if (per_lane >= 1024 && spp >= 64) {
+    spp1 = spp * 3 / 4 / (ch1 * r1) * (ch1 * r1);
+  }
+  ch2 = std::min<long long>(ch2, std::max<long long>(spp, 1));
+  a.ch1 = (int)ch1;
+  a.r1 = (int)r1;
+  a.spp1 = (int)spp1;
+  a.n_chunks1 = (int)(spp1 / ch1);
+  a.ch2 = (int)ch2;
   a.tiles_x = (a.width + 7) / 8;
   a.n_tiles = a.tiles_x * ((a.height + 3) / 4);
-  const long long groups = (a.n_chunks + r - 1) / r;
-  a.n_items = (uint32_t)((long long)a.n_tiles * groups);
+  {  // RT_TILE_ORDER (experiment): 0 raster (default), 1 golden-ratio stride (heavy image regions spread over a sweep)
+    const char *eo = getenv("RT_TILE_ORDER");
+    a.tile_stride = 1;
+    if (eo && atoi(eo) == 1) {
+      auto gcd = [](long long x, long long y) { while (y) { long long t = x % y; x = y; y = t; } return x; };
+      long long st = (long long)(a.n_tiles * 0.6180339887) | 1;
+      while (st > 1 && gcd(st, a.n_tiles) != 1) st -= 2;
+      a.tile_stride = (uint32_t)std::max<long long>(st, 1);
+    }
+  }
+  a.n_items1 = (uint32_t)(spp1 / (ch1 * r1) * a.n_tiles);
+  a.n_items = a.n_items1 + (uint32_t)((spp - spp1 + ch2 - 1) / ch2 * a.n_tiles);
 }
 
 // Renders the samples of `p` into the fixed-point sums `fixed` (added).
@@ -798,16 +838,18 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
     const int minb = trav == 0 ? 8 : (trav == 17 ? 5 : 6);
     plan_work(ctx, a, minb);
     const int grid = ctx->n_sm * minb;
-#define RT_LAUNCH(T, M)                                                                   \
-  if (stats_on)                                                                           \
-    k_render<true, T, M><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr);          \
-  else                                                                                    \
-    k_render<false, T, M><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr);
+#define RT_LAUNCH(T, M, ...)                                                                             \
+  if (stats_on && sph)                                                                                   \
+    k_render<true, T, M, true><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr, ##__VA_ARGS__);    \
+  else if (stats_on)                                                                                     \
+    k_render<true, T, M, false><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr, ##__VA_ARGS__);   \
+  else if (sph)                                                                                          \
+    k_render<false, T, M, true><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr, ##__VA_ARGS__);   \
+  else                                                                                                   \
+    k_render<false, T, M, false><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr, ##__VA_ARGS__);
+    const bool sph = ctx->scene.has_spheres != 0;  // scenes without a Sphere run kernels without the FP64 test
     if (trav == 20) {
-      if (stats_on)
-        k_render<true, 20, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr, ctx->flat);
-      else
-        k_render<false, 20, 6><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr, ctx->flat);
+      RT_LAUNCH(20, 6, ctx->flat)
     } else if (trav == 17) {
       RT_LAUNCH(17, 5)
     } else if (trav == 1) {
@@ -824,7 +866,7 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
   }
   ctx->last_iterations = iterations;
   ctx->last_launches = launches;
-  ctx->last_chunk = a.ch;
+  ctx->last_chunk = a.spp1 > 0 ? a.ch1 : a.ch2;
   ctx->last_items = a.n_items;
   (void)stats;
   return RT_OK;

@@ -20,7 +20,7 @@ constexpr int WSTACK = 96;  // up to 7 pushes per level
 
 // Per-lane if-if form over the wide tree (the loop shape that wins on large scenes: a leaf is tested the moment
 // it is reached, no second loop level).  Any subset of lanes may call.  RT_TRAV=17.
-template <bool STATS, int W>
+template <bool STATS, int W, bool SPH = true, bool EXACT_T = true>
 __device__ __forceinline__ Hit world_hit_wide_ifif(const DScene &s, const RayQ &r, double t_from, double t_to,
                                                    TravStats *st) {
   using L = WideLayout<W>;
@@ -28,6 +28,7 @@ __device__ __forceinline__ Hit world_hit_wide_ifif(const DScene &s, const RayQ &
   rg.t_from = t_from;
   rg.t_to = t_to;
   rg.tf_f = float_ge(t_from);
+  rg.lib_pow = s.sphere_pow != 0;
   Best b;
   best_init(b, t_to);
   if (s.sky_obj >= 0) {  // sky.cu:18-27: always a candidate at t = 1e9
@@ -57,7 +58,7 @@ __device__ __forceinline__ Hit world_hit_wide_ifif(const DScene &s, const RayQ &
         int k = (int)(cur & WLEAF_FIRST_MASK);
         const int end = k + (int)((cur >> WLEAF_COUNT_SHIFT) & 7u);
         if (STATS) st->prims += end - k;
-        while (k < end) k += rec_test(s.recs, k, r, rg, b, ambiguous);
+        while (k < end) k += rec_test<SPH>(s.recs, k, r, rg, b, ambiguous);
         t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
       } else {
         const float4 *__restrict__ n = wn + (size_t)L::F4 * cur;
@@ -110,11 +111,14 @@ __device__ __forceinline__ Hit world_hit_wide_ifif(const DScene &s, const RayQ &
       if (!got) break;
     }
   }
+  resolve_quad_order(s, b, ambiguous);
+  finalize_sphere_hit<SPH, EXACT_T>(s, r, rg, b, ambiguous);
   if (ambiguous || overflow) return world_hit_seq(s, r, t_from, t_to);
   Hit h;
   h.t = b.rec == REC_NONE ? 0.0 : b.t;
   h.rec = b.rec;
   h.seq = 0;
+  h.box = -1;
   return h;
 }
 

@@ -387,7 +387,7 @@ rt_build_stats CommitWorld(rt_ctx *ctx, HitableList *d_world, Camera *d_camera) 
   put(rc.u, c.u());
   put(rc.v, c.v());
   put(rc.w, c.w());
-  rc.is_defocus = c.is_defocus_camera() ? 1 : 0;
+  rc.is_defocus = c.is_defocus_camera() ? (EnvInt("RT_CAMERA_DISK", 0) ? 2 : 1) : 0;  // rtcore.h: 2 = uniform disk lens
   rc.lens_radius = c.lens_radius();
   RTAPI_RT(rt_camera_set(ctx, &rc));
   return bs;

@@ -361,3 +361,50 @@ def test_full_size_properties(ctx):
     ctx.render_fixed_device(c.data_ptr(), H, W, 1, 0, seed=11)
     torch.cuda.synchronize()
     assert torch.equal(a, c)
+
+
+def test_rays_through_a_parallelogram_diagonal(ctx):
+    """Parallelogram::Hit answers with its FIRST triangle that hits (parallelogram.cu:25-41); on the shared diagonal
+    both hit, and when the second is closer the answer depends on what HitableList::Hit found before it
+    (hitable_list.cu:11-21).  Rays aimed at the diagonal, with other objects listed before and after the parallelogram,
+    in front of it, behind it and coplanar with it: every traversal returns the oracle's hits (resolve_quad_order; the
+    sequential scan only for what it cannot settle), on a scene with a mesh too (where that scan would test every face)."""
+    rng = np.random.RandomState(12)
+    mats = np.stack([scenes._mat(abi.RT_MAT_LAMBERTIAN, (0.5, 0.5, 0.5)), scenes._mat(abi.RT_MAT_SKY)])
+    quad = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+
+    def rays_at_diagonal(n):
+        s = rng.uniform(0.02, 0.98, n).astype(np.float32)
+        target = np.stack([s, np.float32(1) - s, np.zeros(n, np.float32)], 1)  # x + y = 1: the edge p1-p2
+        origin = (target + rng.normal(size=(n, 3)) * 0.7 + np.array([0, 0, 2.0])).astype(np.float32)
+        origin[n // 2:, 2] *= -1  # from both sides
+        d = (target - origin).astype(np.float32)
+        dot = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]).astype(np.float32) + (d[:, 2] * d[:, 2]).astype(np.float32)
+        d = (d * (np.float32(1) / np.sqrt(dot))[:, None]).astype(np.float32)
+        return np.concatenate([origin, d], 1).astype(np.float32)
+
+    def shifted(dz):
+        return quad + np.array([0, 0, dz], np.float32)
+
+    mesh = (scenes.soup_mesh(5000, seed=9) * np.float32(0.8) + np.array([0.5, 0.5, -1.5], np.float32).repeat(3)).astype(np.float32)
+    layouts = {
+        "alone": [scenes.parallelogram(quad, 0), scenes._hit(abi.RT_HIT_SKY, 1)],
+        "before_in_front": [scenes.parallelogram(shifted(0.5), 0), scenes.parallelogram(quad, 0), scenes._hit(abi.RT_HIT_SKY, 1)],
+        "after_in_front": [scenes._hit(abi.RT_HIT_SKY, 1), scenes.parallelogram(quad, 0), scenes.parallelogram(shifted(0.5), 0)],
+        "coplanar_before_after": [scenes.parallelogram(quad, 0), scenes.parallelogram(quad, 0), scenes.parallelogram(quad[[1, 0, 2]], 0)],
+        "with_mesh": [scenes._hit(abi.RT_HIT_MESH, 0, mesh=0), scenes.parallelogram(quad, 0), scenes._hit(abi.RT_HIT_SKY, 1),
+                      scenes.parallelogram(shifted(-0.25), 0)],
+    }
+    rays = rays_at_diagonal(60000)
+    n_both = 0
+    for name, hs in layouts.items():
+        s = abi.SceneData(np.stack(hs), mats, meshes=[mesh] if name == "with_mesh" else [])
+        ctx.commit(s)
+        o = ck.OracleScene(s)
+        want = o.trace(rays, quirks=0)
+        for mode in (0, 1, 2, 3, 4) + ((5,) if name != "with_mesh" else ()):
+            got = ctx.trace_closest(rays, mode=mode)
+            bad = ck.hits_equal(got, want, ("t", "obj", "sub", "normal", "material"))
+            assert len(bad) == 0, (name, mode, len(bad), rays[bad[:2]], got[bad[:2]], want[bad[:2]])
+        n_both += int((want["sub"] == 1).sum())
+    assert n_both > 1000  # the second triangle does get reported

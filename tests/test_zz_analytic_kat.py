@@ -153,6 +153,15 @@ def test_render_defocus_camera_bit_exact_vs_oracle():
             got, _, st = ctx.render_host(H, W, spp, seed=4321, flags=flags)
             assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), flags
             assert (st.samples, st.rays, st.rays_ref_equiv) == tuple(int(x) for x in cnt)
+        # is_defocus = 2: the lens sampled as a uniform disk (the reference's DiskRand samples a square, camera.cu:74-77)
+        disk = cam.copy()
+        disk["is_defocus"] = 2
+        ctx.set_camera(disk)
+        want2, cnt2 = ck.OracleScene(s, disk).render_product(H, W, 0, spp, 4321)
+        assert (want2 != want).any()
+        got2, _, st2 = ctx.render_host(H, W, spp, seed=4321, flags=abi.RT_RENDER_FUSED)
+        assert np.array_equal(got2.view(np.uint32), want2.view(np.uint32))
+        assert (st2.samples, st2.rays, st2.rays_ref_equiv) == tuple(int(x) for x in cnt2)
     finally:
         ctx.close()
 
