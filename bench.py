@@ -399,7 +399,8 @@ class Runner:
         build = ctx.commit(scene)
         ctx.set_camera(camera)
         count, begin = self.rdist.partition(spp, rank, world)
-        flags = {"auto": 0, "fused": rt.abi.RT_RENDER_FUSED, "wavefront": rt.abi.RT_RENDER_WAVEFRONT}[args.strategy]
+        flags = {"auto": 0, "fused": rt.abi.RT_RENDER_FUSED, "wavefront": rt.abi.RT_RENDER_WAVEFRONT,
+                 "wavefront_raysort": rt.abi.RT_RENDER_WAVEFRONT | rt.abi.RT_RENDER_RAYSORT}[args.strategy]
         sp = self.stream.cuda_stream
         sums = torch.zeros(H, W, 3, device=self.dev, dtype=torch.int64)
         rgb = torch.zeros(H, W, 3, device=self.dev)
@@ -520,7 +521,7 @@ def main():
     ap.add_argument("--only-headline", action="store_true", help="skip the other BASELINE configs and hit_bit_exact")
     ap.add_argument("--spp", type=int, default=0, help="override spp (diagnostic; the headline uses the config's)")
     ap.add_argument("--depth", type=int, default=0, help="override the bounce limit (diagnostic)")
-    ap.add_argument("--strategy", default="auto", choices=["auto", "fused", "wavefront"])
+    ap.add_argument("--strategy", default="auto", choices=["auto", "fused", "wavefront", "wavefront_raysort"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)

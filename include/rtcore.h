@@ -152,6 +152,9 @@ typedef struct rt_render_stats {
   float render_ms;        /* device time, CUDA events on `stream` */
   uint32_t chunk_samples; /* path kernel: samples per (pixel, chunk) sub-unit of the work distribution */
   uint32_t work_items;    /* path kernel: (tile, chunk group) items drawn from the global counter */
+  uint32_t seq_fallbacks; /* path kernel: queries answered by the sequential scan (order-dependent ties the tree walk
+                             could not settle); each costs one test per primitive of the scene */
+  uint32_t max_box_tests_per_ray; /* only with RT_RENDER_PROFILE */
   uint32_t reserved_;
 } rt_render_stats;
 
@@ -170,6 +173,14 @@ int rt_ctx_destroy(rt_ctx *ctx);
  * and the single-thread BVHNode build (bvh.cuh:113-121): copies the description to the device,
  * flattens it into SoA records and builds the unified LBVH on the device. */
 int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *desc, rt_build_stats *stats /*nullable*/);
+
+/* The same from the device-resident object list the scene API's constructors build (include/rtworld.h: tagged records
+ * in device memory, a HitableList record at d_world, a Camera record at d_camera or NULL): walks the list on the
+ * device, expands nested lists and parallelepipeds, deduplicates materials and image textures, commits the scene and
+ * sets the camera.  This is what Main / DistributedMain run after init_world (utils.cu:148-150); a driver of one's own
+ * calls it instead of describing the scene by hand.  lens_mode: rt_camera::is_defocus for a thin-lens camera (1 or 2). */
+int rt_scene_from_world(rt_ctx *ctx, const void *d_world, const void *d_camera, int lens_mode,
+                        rt_build_stats *stats /*nullable*/);
 
 /* Replaces the Camera constructors (camera.cu:6-47). rt_camera_look_at computes the frame with
  * the reference's arithmetic on the host; aperture<0 selects the pinhole constructor. */
@@ -209,7 +220,9 @@ enum {
   RT_RENDER_FUSED = 4,     /* force the persistent path kernel (paths regenerated in registers; the default) */
   RT_RENDER_SORT = 8,      /* wavefront: material-sorted shade queues (one Scatter/Emit body per warp) instead of one queue;
                               same sums, measured 6-9 % slower (profiles/r01_t_wavefront_sorted_queues.txt) */
-  RT_RENDER_WAVEFRONT = 16 /* force the wavefront pipeline (logic/shade -> extend over compacted queues) */
+  RT_RENDER_WAVEFRONT = 16, /* force the wavefront pipeline (logic/shade -> extend over compacted queues) */
+  RT_RENDER_RAYSORT = 128   /* wavefront: reorder the extend queue by (direction octant, origin cell) before every extend
+                               pass (counting sort on the device); same sums */
   /* 32, 64: RT_RENDER_SPLIT / RT_RENDER_ORDERED of ABI 2 (sample slices on side streams, heaviest tile first) are gone:
      the path kernel now draws (tile, sample chunk) work items from a global counter; the bits are ignored. */
 };

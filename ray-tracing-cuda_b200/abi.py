@@ -15,6 +15,7 @@ RT_RENDER_PROFILE = 2
 RT_RENDER_FUSED = 4
 RT_RENDER_SORT = 8
 RT_RENDER_WAVEFRONT = 16
+RT_RENDER_RAYSORT = 128
 # rt_trace_closest modes: the scene's render traversal, HitableList::Hit as a sequential scan, and each traversal by name
 TRACE_DEFAULT, TRACE_SEQUENTIAL, TRACE_IFIF, TRACE_WHILE_WHILE, TRACE_WIDE8, TRACE_BOX_LIST = range(6)
 FIXED_ONE = 1 << 30  # units of the exact radiance sums (rt_render_fixed)
@@ -102,6 +103,8 @@ class RtRenderStats(C.Structure):
         ("render_ms", C.c_float),
         ("chunk_samples", C.c_uint32),
         ("work_items", C.c_uint32),
+        ("seq_fallbacks", C.c_uint32),
+        ("max_box_tests_per_ray", C.c_uint32),
         ("reserved_", C.c_uint32),
     ]
 

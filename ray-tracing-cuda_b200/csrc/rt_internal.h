@@ -44,7 +44,7 @@ struct DevBuf {
 };
 
 struct RenderCounters {  // device-side counters of one rt_render call
-  unsigned long long samples, rays, rays_ref, nodes, prims, reserved[3];
+  unsigned long long samples, rays, rays_ref, nodes, prims, seq_fallbacks, max_nodes, reserved;
 };
 
 }  // namespace rtc

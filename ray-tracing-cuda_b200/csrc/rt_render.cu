@@ -173,7 +173,14 @@ __device__ __forceinline__ void add_radiance(long long *fixed, int idx, V3 L) {
 
 __device__ __forceinline__ void flush_counters(RenderCounters *ctr, unsigned long long samples,
                                                unsigned long long rays, unsigned long long rays_ref,
-                                               unsigned long long nodes, unsigned long long prims) {
+                                               unsigned long long nodes, unsigned long long prims,
+                                               unsigned int seq = 0, unsigned int max_nodes = 0) {
+  seq = __reduce_add_sync(0xffffffffu, seq);
+  max_nodes = __reduce_max_sync(0xffffffffu, max_nodes);
+  if ((threadIdx.x & 31) == 0) {
+    if (seq) atomicAdd(&ctr->seq_fallbacks, (unsigned long long)seq);
+    if (max_nodes) atomicMax(&ctr->max_nodes, (unsigned long long)max_nodes);
+  }
   for (int o = 16; o > 0; o >>= 1) {
     samples += __shfl_xor_sync(0xffffffffu, samples, o);
     rays += __shfl_xor_sync(0xffffffffu, rays, o);
@@ -257,6 +264,7 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
   int depth = 0;
   int self_box = -1;  // box list: the box the current ray starts on
   unsigned long long n_samples = 0, n_rays = 0, n_rays_ref = 0, n_nodes = 0, n_prims = 0;
+  unsigned int n_seq = 0, max_nodes = 0;
   TravStats ts;
   ts.nodes = ts.prims = 0;
   const FlatItems *flp = nullptr;
@@ -323,9 +331,11 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
       const Hit h = world_hit<STATS, TRAV, SPH, false>(s, flp, ray, 1e-3, (double)CUDART_INF_F, &ts, self_box);
       self_box = h.box;
       n_rays++;
+      n_seq += (unsigned int)h.seq;  // the query was answered by the sequential scan (world_hit_seq)
       if (STATS) {
         n_nodes += ts.nodes;
         n_prims += ts.prims;
+        max_nodes = max(max_nodes, ts.nodes);
         ts.nodes = ts.prims = 0;
       }
       alive = false;
@@ -351,7 +361,7 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
       need_new = true;
     }
   }
-  flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims);
+  flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims, n_seq, max_nodes);
 }
 
 // ---- wavefront pipeline ------------------------------------------------------------------------------
@@ -521,14 +531,16 @@ __global__ void __launch_bounds__(256) k_wf_logic(DScene s, DCamera cam, RenderA
   flush_counters(ctr, n_samples, 0, n_rays_ref, 0, 0);
 }
 
+// `queue`: the slots to extend (w.queue[qi], or its reordered copy)
 template <bool STATS, int MINB>
-__global__ void __launch_bounds__(128, MINB) k_wf_extend(DScene s, WfState w, int qi, RenderCounters *ctr) {
+__global__ void __launch_bounds__(128, MINB) k_wf_extend(DScene s, WfState w, int qi, const uint32_t *__restrict__ queue,
+                                                         RenderCounters *ctr) {
   const uint32_t n_in = w.count[qi];
   unsigned long long n_rays = 0, n_nodes = 0, n_prims = 0;
   TravStats ts;
   ts.nodes = ts.prims = 0;
   for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < n_in; q += gridDim.x * blockDim.x) {
-    uint32_t slot = w.queue[qi][q];
+    uint32_t slot = queue[q];
     float4 ro = w.ray_o[slot], rd = w.ray_d[slot];
     RayQ ray;
     ray.o = xyz(ro);
@@ -558,6 +570,68 @@ __global__ void __launch_bounds__(128, MINB) k_wf_extend(DScene s, WfState w, in
 __global__ void k_wf_reset(uint32_t *count, int which, uint32_t *mcount) {
   if (threadIdx.x == 0) count[which] = 0;
   if (threadIdx.x < WF_CLASSES) mcount[which * WF_CLASSES + threadIdx.x] = 0;
+}
+
+// ---- ray reordering for the extend pass (RT_RENDER_RAYSORT) ---------------------------------------------------
+// Bounce rays of a large scene leave a warp's lanes walking unrelated parts of the tree.  Counting sort of the
+// extend queue by (direction octant, 32^3 cell of the origin in the scene box): rays that start close together and
+// head the same way become neighbours.  Three passes over the queue, all sized on the device (no host round trip):
+// histogram, exclusive scan of the 2^18 buckets, scatter.  The order inside a bucket is whatever the atomics give;
+// the image does not depend on it (each slot's hit is its own, sums are exact).
+constexpr int RAYSORT_BUCKETS = 1 << 18;
+__device__ __forceinline__ uint32_t raysort_key(const DScene &s, const float4 ro, const float4 rd) {
+  const float4 lo = __ldg(s.nodes), hi = __ldg(s.nodes + 1);  // node 0 = root: the scene box
+  uint32_t cell[3];
+  const float o[3] = {ro.x, ro.y, ro.z}, l[3] = {lo.x, lo.y, lo.z}, h[3] = {hi.x, hi.y, hi.z};
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    const float e = h[a] - l[a];
+    float x = e > 0.f ? (o[a] - l[a]) / e : 0.f;
+    x = fminf(fmaxf(x, 0.f), 0.999f);
+    cell[a] = (uint32_t)(x * 32.f);
+  }
+  uint32_t m = 0;
+#pragma unroll
+  for (int b = 0; b < 5; b++)
+    m |= ((cell[0] >> b & 1u) << (3 * b + 2)) | ((cell[1] >> b & 1u) << (3 * b + 1)) | ((cell[2] >> b & 1u) << (3 * b));
+  const uint32_t oct = (rd.x < 0.f ? 4u : 0u) | (rd.y < 0.f ? 2u : 0u) | (rd.z < 0.f ? 1u : 0u);
+  return oct << 15 | m;
+}
+__global__ void __launch_bounds__(256) k_wf_hist(DScene s, WfState w, int qi, uint32_t *hist) {
+  const uint32_t n_in = w.count[qi];
+  for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < n_in; q += gridDim.x * blockDim.x) {
+    const uint32_t slot = w.queue[qi][q];
+    atomicAdd(hist + raysort_key(s, w.ray_o[slot], w.ray_d[slot]), 1u);
+  }
+}
+// one block: hist -> exclusive offsets (in place)
+__global__ void __launch_bounds__(1024) k_wf_scan(uint32_t *hist) {
+  __shared__ uint32_t part[1024];
+  constexpr int PER = RAYSORT_BUCKETS / 1024;
+  const int t = threadIdx.x;
+  uint32_t sum = 0;
+  for (int i = 0; i < PER; i++) sum += hist[t * PER + i];
+  part[t] = sum;
+  __syncthreads();
+  for (int o = 1; o < 1024; o <<= 1) {
+    uint32_t v = t >= o ? part[t - o] : 0u;
+    __syncthreads();
+    part[t] += v;
+    __syncthreads();
+  }
+  uint32_t run = part[t] - sum;
+  for (int i = 0; i < PER; i++) {
+    const uint32_t c = hist[t * PER + i];
+    hist[t * PER + i] = run;
+    run += c;
+  }
+}
+__global__ void __launch_bounds__(256) k_wf_scatter(DScene s, WfState w, int qi, uint32_t *offs, uint32_t *sorted) {
+  const uint32_t n_in = w.count[qi];
+  for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < n_in; q += gridDim.x * blockDim.x) {
+    const uint32_t slot = w.queue[qi][q];
+    sorted[atomicAdd(offs + raysort_key(s, w.ray_o[slot], w.ray_d[slot]), 1u)] = slot;
+  }
 }
 
 // ---- resolve: ray_tracing.cu:78-83 + WriteImage's *255 truncation (utils.cu:87-96) ---------------
@@ -708,7 +782,7 @@ extern "C" int rt_primary_rays_host(rt_ctx *ctx, int height, int width, float *h
 // Wavefront driver.  The queue length lives on the device; the host reads it back once per BATCH of iterations
 // (round 1 read it every iteration: a 4-byte D2H + stream sync between every extend and logic pass), the kernels
 // of the iterations launched past the end find an empty queue and return.
-static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, bool sort, RenderCounters *ctr,
+static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, bool sort, bool raysort, RenderCounters *ctr,
                             cudaStream_t st, uint32_t *iterations, uint32_t *launches) {
   size_t n = (size_t)a.height * a.width;
   for (int i = 0; i < 3; i++) RT_CUDA(ctx->wf[i].reserve(n * 16));
@@ -731,6 +805,13 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, boo
     RT_CUDA(ctx->wf[7].reserve(n * 4 * WF_CLASSES));
     w.mqueue = ctx->wf[7].as<uint32_t>();
   }
+  uint32_t *rs_hist = nullptr, *rs_sorted = nullptr;
+  if (raysort) {
+    RT_CUDA(ctx->wf[8].reserve((size_t)RAYSORT_BUCKETS * 4));
+    RT_CUDA(ctx->wf[9].reserve(n * 4));
+    rs_hist = ctx->wf[8].as<uint32_t>();
+    rs_sorted = ctx->wf[9].as<uint32_t>();
+  }
   const int sms = ctx->n_sm;
   // resident blocks per SM the extend kernel is compiled for: long, latency-bound queries want warps, not registers
   const bool big = ctx->scene.n_recs >= 500000;
@@ -746,12 +827,21 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, boo
   uint32_t live = 1;
   while (live) {
     for (int b = 0; b < batch; b++) {
+      const uint32_t *queue = w.queue[qi];
+      if (raysort) {
+        RT_CUDA(cudaMemsetAsync(rs_hist, 0, (size_t)RAYSORT_BUCKETS * 4, st));
+        k_wf_hist<<<gb_l, 256, 0, st>>>(ctx->scene, w, qi, rs_hist);
+        k_wf_scan<<<1, 1024, 0, st>>>(rs_hist);
+        k_wf_scatter<<<gb_l, 256, 0, st>>>(ctx->scene, w, qi, rs_hist, rs_sorted);
+        queue = rs_sorted;
+        *launches += 3;
+      }
       if (stats_on)
-        k_wf_extend<true, 5><<<gb_e, 128, 0, st>>>(ctx->scene, w, qi, ctr);
+        k_wf_extend<true, 5><<<gb_e, 128, 0, st>>>(ctx->scene, w, qi, queue, ctr);
       else if (big)
-        k_wf_extend<false, 10><<<gb_e, 128, 0, st>>>(ctx->scene, w, qi, ctr);
+        k_wf_extend<false, 10><<<gb_e, 128, 0, st>>>(ctx->scene, w, qi, queue, ctr);
       else
-        k_wf_extend<false, 5><<<gb_e, 128, 0, st>>>(ctx->scene, w, qi, ctr);
+        k_wf_extend<false, 5><<<gb_e, 128, 0, st>>>(ctx->scene, w, qi, queue, ctr);
       k_wf_reset<<<1, 32, 0, st>>>(w.count, qi ^ 1, w.mcount);
       k_wf_logic<false><<<gb_l, 256, 0, st>>>(ctx->scene, ctx->camera, a, w, qi, ctr);
       *launches += 3;
@@ -766,14 +856,19 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, boo
 }
 
 // Work distribution of a k_render launch (RenderArgs), sized against a lane's share of the samples.  Measured on the
-// B200 (profiles/r02_*): one size does not fit — 16-sample chunks in items of up to 16 chunks left 60 % of the SM
-// cycles of the bunny frame idle behind the last heavy items (a sample on the mesh costs 30x one of the sky);
-// 4-sample chunks everywhere cost the uniform scenes 5-7 % (the hand-out, ~35 warp instructions, then runs in almost
-// every iteration of a warp) and the soups their locality; hence the two phases.  A launch with little work per lane
-// (spheres 400x225x16: 13 samples) is all phase 2 with 1-sample chunks.
+// B200 (profiles/r02_*):
+//  * 4-sample chunks everywhere cost the uniform scenes 4-5 % (the hand-out, ~35 warp instructions, then runs in
+//    almost every iteration of a warp), so scenes whose cost per ray is BOUNDED BY CONSTRUCTION — the box list: every
+//    ray tests the same <= 32 boxes — get the two phases (Cornell 3 969 -> 4 160 Msamples/s);
+//  * behind a tree the cost of a sample is unbounded in practice: the bunny frame has 8x4 tiles whose rays need 40x the
+//    box tests of the average mesh tile (644 against 14.7 per ray), one such tile as an 80-samples-per-pixel item is
+//    22 ms on one warp, and it held the launch for 39 % of its time (profiles/r02_i_bunny_two_phase_ncu_summary.txt:
+//    one SM active for 130.7 M cycles, the others for 88-90 M).  Tree scenes are therefore all phase 2: 4-sample
+//    chunks, one chunk per item (bunny 7 423 -> 10 222; the 1 M soup pays 5 % for the lost tile locality, 494 -> 468);
+//  * a launch with little work per lane (spheres 400x225x16: 13 samples) uses 1-sample chunks.
 // RT_CHUNK / RT_ITEM_CHUNKS (diagnostics, tests): phase 1 with that chunk size and that many chunks per item over all
 // whole items, the remainder in phase 2 with the same chunk size.
-static void plan_work(const rt_ctx *ctx, RenderArgs &a, int minb) {
+static void plan_work(const rt_ctx *ctx, RenderArgs &a, int minb, bool bounded_cost) {
   const long long lanes = (long long)ctx->n_sm * minb * 128;
   const long long spp = a.spp_end - a.spp_begin;
   const long long per_lane = std::max<long long>(1, (long long)a.height * a.width * spp / lanes);
@@ -784,7 +879,7 @@ static void plan_work(const rt_ctx *ctx, RenderArgs &a, int minb) {
     ch1 = ch2 = std::min<long long>(std::max<long long>(atoll(ec), 1), 16);
     r1 = std::min<long long>(std::max<long long>(ei ? atoll(ei) : 1, 1), 16);
     spp1 = r1 > 1 ? spp / (ch1 * r1) * (ch1 * r1) : 0;
-  } else if (per_lane >= 1024 && spp >= 64) {
+  } else if (bounded_cost && per_lane >= 1024 && spp >= 64) {
     spp1 = spp * 3 / 4 / (ch1 * r1) * (ch1 * r1);
   }
   ch2 = std::min<long long>(ch2, std::max<long long>(spp, 1));
@@ -836,7 +931,7 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
     // resident blocks per SM the kernel is compiled for (register budget): 6 (80 registers) for cache-resident
     // scenes, 5 for the 8-wide tree, 8 (64 registers) from 500 k records up, where the loop is latency bound
     const int minb = trav == 0 ? 8 : (trav == 17 ? 5 : 6);
-    plan_work(ctx, a, minb);
+    plan_work(ctx, a, minb, trav == 20);
     const int grid = ctx->n_sm * minb;
 #define RT_LAUNCH(T, M, ...)                                                                             \
   if (stats_on && sph)                                                                                   \
@@ -861,7 +956,8 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
     RT_CUDA(cudaGetLastError());
     launches = 1;
   } else if (p->spp_count > 0) {
-    int rc = render_wavefront(ctx, a, stats_on, (p->flags & RT_RENDER_SORT) != 0, ctr, st, &iterations, &launches);
+    int rc = render_wavefront(ctx, a, stats_on, (p->flags & RT_RENDER_SORT) != 0, (p->flags & RT_RENDER_RAYSORT) != 0, ctr,
+                              st, &iterations, &launches);
     if (rc) return rc;
   }
   ctx->last_iterations = iterations;
@@ -892,6 +988,8 @@ static int finish_stats(rt_ctx *ctx, rt_render_stats *stats, cudaStream_t st, ui
   stats->render_ms = ms;
   stats->chunk_samples = (uint32_t)ctx->last_chunk;
   stats->work_items = ctx->last_items;
+  stats->seq_fallbacks = (uint32_t)std::min<unsigned long long>(hc.seq_fallbacks, 0xffffffffull);
+  stats->max_box_tests_per_ray = (uint32_t)hc.max_nodes;
   return RT_OK;
 }
 

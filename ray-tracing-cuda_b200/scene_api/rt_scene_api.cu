@@ -16,7 +16,6 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
-#include <map>
 #include <thread>
 
 #include "../../include/rtcore.h"
@@ -79,181 +78,6 @@ void WriteImage(const std::vector<glm::vec3> &pixels, int height, int width, con
                : rt_write_jpeg(path.c_str(), width, height, rgb8.data(), 100));
 }
 
-// ---- flattening: device object list -> rt_hitable / rt_material records -------------------------------
-namespace {
-
-struct FlatRec {
-  rt_hitable h;           // material = -1 here; resolved on the host from material_ptr
-  rt_material m;          // description of *material_ptr (texture = -1, or -2 when tex_obj is an image)
-  unsigned long long material_ptr, tex_obj, faces_ptr;
-  int32_t n_faces, has_uv;
-};
-
-__device__ void DescribeTexture(const Texture *t, FlatRec *out) {
-  if (t && t->rt_kind() == rtapi::kTexImage) {
-    out->m.texture = -2;
-    out->tex_obj = (unsigned long long)static_cast<const ImageTexture *>(t)->image_texture();
-  } else if (t && t->rt_kind() == rtapi::kTexConstant) {
-    glm::vec3 c = static_cast<const ConstantTexture *>(t)->color();
-    out->m.color[0] = c.x, out->m.color[1] = c.y, out->m.color[2] = c.z;
-  }
-}
-
-__device__ void DescribeMaterial(Material *mp, FlatRec *out) {
-  out->material_ptr = (unsigned long long)mp;
-  out->tex_obj = 0;
-  rt_material &m = out->m;
-  m.type = -1;
-  m.texture = -1;
-  m.color[0] = m.color[1] = m.color[2] = 0.f;
-  m.fuzz = 0.f;
-  m.ior = 0.0;
-  if (!mp) return;
-  switch (mp->rt_kind()) {
-    case rtapi::kMatLambertian:
-      m.type = RT_MAT_LAMBERTIAN;
-      DescribeTexture(static_cast<Lambertian *>(mp)->texture_ptr(), out);
-      break;
-    case rtapi::kMatMetal: {
-      m.type = RT_MAT_METAL;
-      glm::vec3 c = static_cast<Metal *>(mp)->albedo();
-      m.color[0] = c.x, m.color[1] = c.y, m.color[2] = c.z;
-      m.fuzz = static_cast<Metal *>(mp)->fuzz();
-      break;
-    }
-    case rtapi::kMatDielectric: {
-      m.type = RT_MAT_DIELECTRIC;
-      glm::vec3 c = static_cast<Dielectric *>(mp)->attenuation();
-      m.color[0] = c.x, m.color[1] = c.y, m.color[2] = c.z;
-      m.ior = static_cast<Dielectric *>(mp)->refractive_index();
-      break;
-    }
-    case rtapi::kMatDiffuseLight:
-      m.type = RT_MAT_DIFFUSE_LIGHT;
-      DescribeTexture(static_cast<DiffuseLight *>(mp)->texture_ptr(), out);
-      break;
-    case rtapi::kMatSky:
-      m.type = RT_MAT_SKY;
-      break;
-    default:
-      break;
-  }
-}
-
-__device__ void ClearRec(FlatRec *r, int type, int group) {
-  memset(r, 0, sizeof(*r));
-  r->h.type = type;
-  r->h.material = -1;
-  r->h.mesh = -1;
-  r->h.group = group;
-}
-__device__ void PutPoint(float *dst, glm::vec3 p) { dst[0] = p.x, dst[1] = p.y, dst[2] = p.z; }
-
-__device__ void PutParallelogram(const Parallelogram &pg, int group, FlatRec *out) {
-  ClearRec(out, RT_HIT_PARALLELOGRAM, group);
-  for (int k = 0; k < 4; k++) PutPoint(out->h.p[k], pg.point(k));
-  DescribeMaterial(pg.material_ptr(), out);
-}
-
-// Number of flat records under one Hitable (nested lists included), and the records themselves.
-__device__ int CountFlat(const Hitable *h) {
-  if (!h) return 0;
-  switch (h->rt_kind()) {
-    case rtapi::kHitList: {
-      const HitableList *l = static_cast<const HitableList *>(h);
-      int n = 0;
-      for (int i = 0; i < l->list_len(); i++) n += CountFlat(l->at(i));
-      return n;
-    }
-    case rtapi::kHitParallelepiped:
-      return static_cast<const Parallelepiped *>(h)->face_count();
-    case rtapi::kHitSphere:
-    case rtapi::kHitTriangle:
-    case rtapi::kHitParallelogram:
-    case rtapi::kHitSky:
-    case rtapi::kHitMesh:
-    case rtapi::kHitMeshUV:
-      return 1;
-    default:
-      return 0;  // AABB and unknown objects are not renderable
-  }
-}
-
-__device__ int EmitFlat(Hitable *h, int group, FlatRec *out) {
-  if (!h) return 0;
-  switch (h->rt_kind()) {
-    case rtapi::kHitList: {
-      HitableList *l = static_cast<HitableList *>(h);
-      int n = 0;
-      for (int i = 0; i < l->list_len(); i++) n += EmitFlat(l->at(i), group, out + n);
-      return n;
-    }
-    case rtapi::kHitParallelepiped: {
-      const Parallelepiped *pp = static_cast<const Parallelepiped *>(h);
-      for (int i = 0; i < pp->face_count(); i++) PutParallelogram(pp->face(i), group, out + i);
-      return pp->face_count();
-    }
-    case rtapi::kHitSphere: {
-      const Sphere *s = static_cast<const Sphere *>(h);
-      ClearRec(out, RT_HIT_SPHERE, -1);
-      PutPoint(out->h.p[0], s->position());
-      out->h.radius = s->radius();
-      DescribeMaterial(s->material_ptr(), out);
-      return 1;
-    }
-    case rtapi::kHitTriangle: {
-      const Triangle *t = static_cast<const Triangle *>(h);
-      ClearRec(out, RT_HIT_TRIANGLE, -1);
-      for (int k = 0; k < 3; k++) PutPoint(out->h.p[k], t->point(k));
-      DescribeMaterial(t->material_ptr(), out);
-      return 1;
-    }
-    case rtapi::kHitParallelogram:
-      PutParallelogram(*static_cast<const Parallelogram *>(h), -1, out);
-      return 1;
-    case rtapi::kHitSky:
-      ClearRec(out, RT_HIT_SKY, -1);
-      DescribeMaterial(static_cast<Sky *>(h)->material_ptr(), out);
-      return 1;
-    case rtapi::kHitMesh: {
-      const BVH<Face<false>, AABB> *b = static_cast<const BVH<Face<false>, AABB> *>(h);
-      ClearRec(out, RT_HIT_MESH, -1);
-      DescribeMaterial(b->material_ptr(), out);
-      out->faces_ptr = (unsigned long long)b->objs();
-      out->n_faces = b->size();
-      out->has_uv = 0;
-      return 1;
-    }
-    case rtapi::kHitMeshUV: {
-      const BVH<Face<true>, AABB> *b = static_cast<const BVH<Face<true>, AABB> *>(h);
-      ClearRec(out, RT_HIT_MESH, -1);
-      DescribeMaterial(b->material_ptr(), out);
-      out->faces_ptr = (unsigned long long)b->objs();
-      out->n_faces = b->size();
-      out->has_uv = 1;
-      return 1;
-    }
-    default:
-      return 0;
-  }
-}
-
-// pass 1: one thread per top-level entry counts its flat records; pass 2 writes them at the scanned offsets
-__global__ void FlattenCount(const HitableList *world, int *counts, int *list_len) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0) *list_len = world->list_len();
-  if (i < world->list_len()) counts[i] = CountFlat(world->at(i));
-}
-__global__ void FlattenEmit(const HitableList *world, const int *offsets, FlatRec *out) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= world->list_len()) return;
-  // a top-level Parallelepiped gets its own group id (its index in the list)
-  int group = world->at(i) && world->at(i)->rt_kind() == rtapi::kHitParallelepiped ? i : -1;
-  EmitFlat(world->at(i), group, out + offsets[i]);
-}
-
-}  // namespace
-
 // ---- host side: commit the flattened world to the core -------------------------------------------------
 namespace {
 
@@ -283,113 +107,11 @@ Options ReadOptions(int height, int width, int spp) {
   return o;
 }
 
-// Walks *d_world on the device, then describes it to the core.  Returns the build statistics.
+// The device-resident object list -> the core (rt_scene_from_world walks the tagged records of include/rtworld.h, whose
+// layout the classes of rt_scene_api.cuh are static_asserted against).  Returns the build statistics.
 rt_build_stats CommitWorld(rt_ctx *ctx, HitableList *d_world, Camera *d_camera) {
-  int *d_counts = nullptr, *d_offsets = nullptr;
-  RTAPI_CUDA(cudaMalloc(&d_counts, sizeof(int) * (HitableList::kMaxHitables + 1)));
-  RTAPI_CUDA(cudaMalloc(&d_offsets, sizeof(int) * HitableList::kMaxHitables));
-  RTAPI_CUDA(cudaMemset(d_counts, 0, sizeof(int) * (HitableList::kMaxHitables + 1)));
-  FlattenCount<<<HitableList::kMaxHitables / 128, 128>>>(d_world, d_counts, d_counts + HitableList::kMaxHitables);
-  std::vector<int> counts(HitableList::kMaxHitables + 1);
-  RTAPI_CUDA(cudaMemcpy(counts.data(), d_counts, sizeof(int) * counts.size(), cudaMemcpyDeviceToHost));
-  int list_len = counts[HitableList::kMaxHitables];
-  CHECK(list_len >= 0 && list_len <= HitableList::kMaxHitables) << "HitableList overflow: " << list_len;
-  std::vector<int> offsets(HitableList::kMaxHitables, 0);
-  int total = 0;
-  for (int i = 0; i < list_len; i++) {
-    offsets[i] = total;
-    total += counts[i];
-  }
-  std::vector<FlatRec> flat((size_t)std::max(total, 1));
-  if (total > 0) {
-    FlatRec *d_flat = nullptr;
-    RTAPI_CUDA(cudaMalloc(&d_flat, sizeof(FlatRec) * total));
-    RTAPI_CUDA(cudaMemcpy(d_offsets, offsets.data(), sizeof(int) * offsets.size(), cudaMemcpyHostToDevice));
-    FlattenEmit<<<HitableList::kMaxHitables / 128, 128>>>(d_world, d_offsets, d_flat);
-    RTAPI_CUDA(cudaMemcpy(flat.data(), d_flat, sizeof(FlatRec) * total, cudaMemcpyDeviceToHost));
-    RTAPI_CUDA(cudaFree(d_flat));
-  }
-  RTAPI_CUDA(cudaFree(d_counts));
-  RTAPI_CUDA(cudaFree(d_offsets));
-
-  // materials deduplicated by object address, image textures by texture object
-  std::vector<rt_hitable> hitables;
-  std::vector<rt_material> materials;
-  std::vector<rt_mesh> meshes;
-  std::vector<rt_texture> textures;
-  std::vector<std::vector<uint8_t>> texels;
-  std::map<unsigned long long, int> material_ids, texture_ids;
-  for (int i = 0; i < total; i++) {
-    FlatRec &r = flat[i];
-    CHECK(r.m.type >= 0) << "hitable " << i << " has no (known) material";
-    auto it = material_ids.find(r.material_ptr);
-    if (it == material_ids.end()) {
-      rt_material m = r.m;
-      if (m.texture == -2) {
-        auto tt = texture_ids.find(r.tex_obj);
-        if (tt == texture_ids.end()) {
-          cudaResourceDesc res;
-          RTAPI_CUDA(cudaGetTextureObjectResourceDesc(&res, (cudaTextureObject_t)r.tex_obj));
-          CHECK(res.resType == cudaResourceTypePitch2D) << "ImageTexture must wrap a pitch2D resource (image_texture.cu:17-38)";
-          rt_texture t;
-          t.height = (int)res.res.pitch2D.height;
-          t.width = (int)res.res.pitch2D.width;
-          t.pitch_bytes = (int64_t)t.width * 4;
-          texels.emplace_back((size_t)t.pitch_bytes * t.height);
-          RTAPI_CUDA(cudaMemcpy2D(texels.back().data(), t.pitch_bytes, res.res.pitch2D.devPtr, res.res.pitch2D.pitchInBytes,
-                                  (size_t)t.width * 4, t.height, cudaMemcpyDeviceToHost));
-          t.h_rgba = nullptr;  // fixed up below (vector growth moves nothing, but keep it explicit)
-          tt = texture_ids.emplace(r.tex_obj, (int)textures.size()).first;
-          textures.push_back(t);
-        }
-        m.texture = tt->second;
-      }
-      it = material_ids.emplace(r.material_ptr, (int)materials.size()).first;
-      materials.push_back(m);
-    }
-    r.h.material = it->second;
-    if (r.h.type == RT_HIT_MESH) {
-      rt_mesh m;
-      m.h_faces = (const float *)r.faces_ptr;  // device memory: rt_scene_commit copies with cudaMemcpyDefault
-      m.n_faces = r.n_faces;
-      m.has_texcoord = r.has_uv;
-      r.h.mesh = (int)meshes.size();
-      meshes.push_back(m);
-    }
-    hitables.push_back(r.h);
-  }
-  for (size_t i = 0; i < textures.size(); i++) textures[i].h_rgba = texels[i].data();
-
-  rt_scene_desc d;
-  memset(&d, 0, sizeof(d));
-  d.hitables = hitables.data();
-  d.n_hitables = (int)hitables.size();
-  d.materials = materials.data();
-  d.n_materials = (int)materials.size();
-  d.meshes = meshes.data();
-  d.n_meshes = (int)meshes.size();
-  d.textures = textures.data();
-  d.n_textures = (int)textures.size();
   rt_build_stats bs;
-  RTAPI_RT(rt_scene_commit(ctx, &d, &bs));
-
-  // the Camera record the callback placement-new'ed on the device
-  alignas(Camera) unsigned char raw[sizeof(Camera)];
-  RTAPI_CUDA(cudaMemcpy(raw, d_camera, sizeof(Camera), cudaMemcpyDeviceToHost));
-  const Camera &c = *reinterpret_cast<const Camera *>(raw);
-  rt_camera rc;
-  memset(&rc, 0, sizeof(rc));
-  auto put = [](float *dst, glm::vec3 v) { dst[0] = v.x, dst[1] = v.y, dst[2] = v.z; };
-  put(rc.position, c.position());
-  put(rc.lower_left_corner, c.lower_left_corner());
-  put(rc.horizontal, c.horizontal());
-  put(rc.vertical, c.vertical());
-  put(rc.u, c.u());
-  put(rc.v, c.v());
-  put(rc.w, c.w());
-  rc.is_defocus = c.is_defocus_camera() ? (EnvInt("RT_CAMERA_DISK", 0) ? 2 : 1) : 0;  // rtcore.h: 2 = uniform disk lens
-  rc.lens_radius = c.lens_radius();
-  RTAPI_RT(rt_camera_set(ctx, &rc));
+  RTAPI_RT(rt_scene_from_world(ctx, d_world, d_camera, EnvInt("RT_CAMERA_DISK", 0) ? 2 : 1, &bs));
   return bs;
 }
 

@@ -23,6 +23,7 @@
 #include <curand_kernel.h>
 #include <glog/logging.h>
 #include <mpi.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #include <functional>
@@ -32,22 +33,29 @@
 #include <tuple>
 #include <vector>
 
-// ---- type tags -----------------------------------------------------------------------------------
+#include "../../include/rtworld.h"
+
+// ---- type tags: the values of include/rtworld.h (the records rt_scene_from_world walks) ---------------
 namespace rtapi {
 enum HitableKind : int32_t {
-  kHitNone = 0,
-  kHitList = 1,
-  kHitSphere = 2,
-  kHitTriangle = 3,
-  kHitParallelogram = 4,
-  kHitParallelepiped = 5,
-  kHitSky = 6,
-  kHitMesh = 7,      // BVH<Face<false>, AABB>
-  kHitMeshUV = 8,    // BVH<Face<true>, AABB>
-  kHitAABB = 9
+  kHitNone = RT_WORLD_HIT_NONE,
+  kHitList = RT_WORLD_HIT_LIST,
+  kHitSphere = RT_WORLD_HIT_SPHERE,
+  kHitTriangle = RT_WORLD_HIT_TRIANGLE,
+  kHitParallelogram = RT_WORLD_HIT_PARALLELOGRAM,
+  kHitParallelepiped = RT_WORLD_HIT_PARALLELEPIPED,
+  kHitSky = RT_WORLD_HIT_SKY,
+  kHitMesh = RT_WORLD_HIT_MESH,      // BVH<Face<false>, AABB>
+  kHitMeshUV = RT_WORLD_HIT_MESH_UV, // BVH<Face<true>, AABB>
+  kHitAABB = RT_WORLD_HIT_AABB
 };
-enum MaterialKind : int32_t { kMatNone = 0, kMatLambertian = 1, kMatMetal = 2, kMatDielectric = 3, kMatDiffuseLight = 4, kMatSky = 5 };
-enum TextureKind : int32_t { kTexNone = 0, kTexConstant = 1, kTexImage = 2 };
+enum MaterialKind : int32_t {
+  kMatNone = RT_WORLD_MAT_NONE, kMatLambertian = RT_WORLD_MAT_LAMBERTIAN, kMatMetal = RT_WORLD_MAT_METAL,
+  kMatDielectric = RT_WORLD_MAT_DIELECTRIC, kMatDiffuseLight = RT_WORLD_MAT_DIFFUSE_LIGHT, kMatSky = RT_WORLD_MAT_SKY
+};
+enum TextureKind : int32_t { kTexNone = RT_WORLD_TEX_NONE, kTexConstant = RT_WORLD_TEX_CONSTANT, kTexImage = RT_WORLD_TEX_IMAGE };
+// layout checks against the records of rtworld.h (member offsets through a friend of every class)
+struct LayoutCheck;
 }  // namespace rtapi
 
 // ---- cuda_copyable.cuh:6-19 ----------------------------------------------------------------------
@@ -89,6 +97,7 @@ struct HitRecord {
 
 // ---- textures/texture.cuh, constant_texture.cuh, image_texture.cuh --------------------------------
 class Texture : public CudaCopyable {
+  friend struct rtapi::LayoutCheck;
  public:
   __host__ __device__ int32_t rt_kind() const { return rt_kind_; }
 
@@ -97,6 +106,7 @@ class Texture : public CudaCopyable {
 };
 
 class ConstantTexture : public Texture {
+  friend struct rtapi::LayoutCheck;
  public:
   __host__ __device__ ConstantTexture() : color_(0.f) { rt_kind_ = rtapi::kTexConstant; }
   __host__ __device__ ConstantTexture(glm::vec3 color) : color_(color) { rt_kind_ = rtapi::kTexConstant; }
@@ -108,6 +118,7 @@ class ConstantTexture : public Texture {
 };
 
 class ImageTexture : public Texture {
+  friend struct rtapi::LayoutCheck;
  public:
   __host__ __device__ ImageTexture(cudaTextureObject_t image_texture) : image_texture_(image_texture) {
     rt_kind_ = rtapi::kTexImage;
@@ -122,6 +133,7 @@ class ImageTexture : public Texture {
 
 // ---- material.cuh:13-20 and the five materials ----------------------------------------------------
 class Material : public CudaCopyable {
+  friend struct rtapi::LayoutCheck;
  public:
   __host__ __device__ int32_t rt_kind() const { return rt_kind_; }
 
@@ -130,6 +142,7 @@ class Material : public CudaCopyable {
 };
 
 class Lambertian : public Material {
+  friend struct rtapi::LayoutCheck;
  public:
   __host__ __device__ Lambertian(glm::vec3 color) : texture_ptr_(nullptr), color_(color), use_constant_tex_(true) {
     rt_kind_ = rtapi::kMatLambertian;
@@ -145,7 +158,8 @@ class Lambertian : public Material {
   bool use_constant_tex_;
 };
 
-class Metal : public Material {  // metal.cuh:8-9: constructors are device-only; fuzz clamped to <= 1 (metal.cu:10)
+class Metal : public Material {
+  friend struct rtapi::LayoutCheck;  // metal.cuh:8-9: constructors are device-only; fuzz clamped to <= 1 (metal.cu:10)
  public:
   Metal() = delete;
   __device__ Metal(glm::vec3 albedo) : albedo_(albedo), fuzz_(0.f) { rt_kind_ = rtapi::kMatMetal; }
@@ -161,6 +175,7 @@ class Metal : public Material {  // metal.cuh:8-9: constructors are device-only;
 };
 
 class Dielectric : public Material {
+  friend struct rtapi::LayoutCheck;
  public:
   Dielectric() = delete;
   __device__ __host__ Dielectric(glm::vec3 attenuation, double refractive_index)
@@ -176,6 +191,7 @@ class Dielectric : public Material {
 };
 
 class DiffuseLight : public Material {
+  friend struct rtapi::LayoutCheck;
  public:
   DiffuseLight() = delete;
   __host__ __device__ DiffuseLight(Texture *texture_ptr) : texture_ptr_(texture_ptr) {
@@ -194,6 +210,7 @@ class SkyMaterial : public Material {
 
 // ---- hitable.cuh:19-23, hitable_list.cuh:8-22 -----------------------------------------------------
 class Hitable {
+  friend struct rtapi::LayoutCheck;
  public:
   __host__ __device__ int32_t rt_kind() const { return rt_kind_; }
 
@@ -202,6 +219,7 @@ class Hitable {
 };
 
 class HitableList : public Hitable {
+  friend struct rtapi::LayoutCheck;
  public:
   constexpr static int kMaxHitables = 1024;
   __host__ __device__ HitableList() { rt_kind_ = rtapi::kHitList; }
@@ -218,6 +236,7 @@ class HitableList : public Hitable {
 
 // ---- sphere.cuh:8-25 -----------------------------------------------------------------------------
 class Sphere : public Hitable {
+  friend struct rtapi::LayoutCheck;
  public:
   Sphere() = delete;
   __host__ __device__ Sphere(glm::vec3 position, double radius, Material *material_ptr)
@@ -236,6 +255,7 @@ class Sphere : public Hitable {
 
 // ---- triangle.cuh:7-17 ---------------------------------------------------------------------------
 class Triangle : public Hitable {
+  friend struct rtapi::LayoutCheck;
  public:
   Triangle() = delete;
   __host__ __device__ Triangle(glm::vec3 p[], Material *material_ptr) : material_ptr_(material_ptr) {
@@ -252,6 +272,7 @@ class Triangle : public Hitable {
 
 // ---- parallelogram.cuh:7-17; p[3] = p[1] + p[2] - p[0] (parallelogram.cu:10-15) ---------------------
 class Parallelogram : public Hitable {
+  friend struct rtapi::LayoutCheck;
  public:
   __host__ __device__ Parallelogram() : material_ptr_(nullptr) { rt_kind_ = rtapi::kHitParallelogram; }
   __host__ __device__ Parallelogram(glm::vec3 p[3], Material *material_ptr) : material_ptr_(material_ptr) {
@@ -269,6 +290,7 @@ class Parallelogram : public Hitable {
 
 // ---- parallelepiped.cuh:16-29: six parallelograms in AddCorner order (parallelepiped.cu:25-32) ------
 class Parallelepiped : public Hitable {
+  friend struct rtapi::LayoutCheck;
  public:
   Parallelepiped() = delete;
   __host__ __device__ Parallelepiped(glm::vec3 p[4], Material *material_ptr) {  // parallelepiped.cu:8-18
@@ -317,6 +339,7 @@ class Parallelepiped : public Hitable {
 
 // ---- sky.cuh:8-26 ----------------------------------------------------------------------------------
 class Sky : public Hitable {
+  friend struct rtapi::LayoutCheck;
  public:
   __host__ __device__ Sky() { rt_kind_ = rtapi::kHitSky; }
   __device__ __host__ Material *material_ptr() { return &material_; }
@@ -360,6 +383,7 @@ static_assert(sizeof(Face<false>) == 36 && sizeof(Face<true>) == 60, "Face<> lay
 // ---- bvh.cuh:161-183: BVH<T, BV> — registers the mesh; one material per mesh ------------------------
 template <typename T, typename BV>
 class BVH : public Hitable {
+  friend struct rtapi::LayoutCheck;
  public:
   __host__ __device__ explicit BVH(T *objs, int n, Material *material_ptr)
       : objs_(objs), n_(n), material_ptr_(material_ptr) {
@@ -377,6 +401,7 @@ class BVH : public Hitable {
 
 // ---- camera.cuh:10-35; constructors in the reference's expression order (camera.cu:6-47) ------------
 class Camera : public CudaCopyable {
+  friend struct rtapi::LayoutCheck;
  private:
   glm::vec3 position_, lower_left_corner_, horizontal_, vertical_, u_, v_, w_;
   bool is_defocus_camera_;
@@ -420,6 +445,67 @@ class Camera : public CudaCopyable {
   __host__ __device__ bool is_defocus_camera() const { return is_defocus_camera_; }
   __host__ __device__ double lens_radius() const { return lens_radius_; }
 };
+
+// ---- the classes above ARE the records of include/rtworld.h -------------------------------------------
+#pragma nv_diag_suppress 1427  // offsetof on classes with bases: conditionally supported, exactly what is being checked
+namespace rtapi {
+struct LayoutCheck {
+#define RTAPI_SAME(CLS, MEMBER, REC, FIELD) \
+  static_assert(offsetof(CLS, MEMBER) == offsetof(REC, FIELD), #CLS "::" #MEMBER " is not at " #REC "::" #FIELD)
+#define RTAPI_SIZE(CLS, REC) static_assert(sizeof(CLS) == sizeof(REC), #CLS " and " #REC " differ in size")
+  RTAPI_SIZE(ConstantTexture, rt_world_constant_texture);
+  RTAPI_SAME(ConstantTexture, rt_kind_, rt_world_constant_texture, kind);
+  RTAPI_SAME(ConstantTexture, color_, rt_world_constant_texture, color);
+  RTAPI_SIZE(ImageTexture, rt_world_image_texture);
+  RTAPI_SAME(ImageTexture, image_texture_, rt_world_image_texture, texture_object);
+  RTAPI_SIZE(Lambertian, rt_world_lambertian);
+  RTAPI_SAME(Lambertian, rt_kind_, rt_world_lambertian, kind);
+  RTAPI_SAME(Lambertian, texture_ptr_, rt_world_lambertian, texture);
+  RTAPI_SAME(Lambertian, color_, rt_world_lambertian, color);
+  RTAPI_SAME(Lambertian, use_constant_tex_, rt_world_lambertian, use_constant_texture);
+  RTAPI_SIZE(Metal, rt_world_metal);
+  RTAPI_SAME(Metal, albedo_, rt_world_metal, albedo);
+  RTAPI_SAME(Metal, fuzz_, rt_world_metal, fuzz);
+  RTAPI_SIZE(Dielectric, rt_world_dielectric);
+  RTAPI_SAME(Dielectric, attenuation_, rt_world_dielectric, attenuation);
+  RTAPI_SAME(Dielectric, refractive_index_, rt_world_dielectric, refractive_index);
+  RTAPI_SIZE(DiffuseLight, rt_world_diffuse_light);
+  RTAPI_SAME(DiffuseLight, texture_ptr_, rt_world_diffuse_light, texture);
+  RTAPI_SIZE(SkyMaterial, rt_world_sky_material);
+  RTAPI_SIZE(HitableList, rt_world_list);
+  RTAPI_SAME(HitableList, rt_kind_, rt_world_list, kind);
+  RTAPI_SAME(HitableList, list_, rt_world_list, list);
+  RTAPI_SAME(HitableList, list_len_, rt_world_list, len);
+  static_assert(HitableList::kMaxHitables == RT_WORLD_MAX_HITABLES, "kMaxHitables");
+  RTAPI_SIZE(Sphere, rt_world_sphere);
+  RTAPI_SAME(Sphere, radius_, rt_world_sphere, radius);
+  RTAPI_SAME(Sphere, position_, rt_world_sphere, position);
+  RTAPI_SAME(Sphere, material_ptr_, rt_world_sphere, material);
+  RTAPI_SIZE(Triangle, rt_world_triangle);
+  RTAPI_SAME(Triangle, p_, rt_world_triangle, p);
+  RTAPI_SAME(Triangle, material_ptr_, rt_world_triangle, material);
+  RTAPI_SIZE(Parallelogram, rt_world_parallelogram);
+  RTAPI_SAME(Parallelogram, p_, rt_world_parallelogram, p);
+  RTAPI_SAME(Parallelogram, material_ptr_, rt_world_parallelogram, material);
+  RTAPI_SIZE(Parallelepiped, rt_world_parallelepiped);
+  RTAPI_SAME(Parallelepiped, faces_, rt_world_parallelepiped, faces);
+  RTAPI_SAME(Parallelepiped, n_, rt_world_parallelepiped, n_faces);
+  RTAPI_SIZE(Sky, rt_world_sky);
+  RTAPI_SAME(Sky, material_, rt_world_sky, material);
+  typedef BVH<Face<false>, AABB> MeshBVH;
+  RTAPI_SIZE(MeshBVH, rt_world_mesh);
+  RTAPI_SAME(MeshBVH, objs_, rt_world_mesh, faces);
+  RTAPI_SAME(MeshBVH, n_, rt_world_mesh, n_faces);
+  RTAPI_SAME(MeshBVH, material_ptr_, rt_world_mesh, material);
+  RTAPI_SIZE(Camera, rt_world_camera);
+  RTAPI_SAME(Camera, position_, rt_world_camera, position);
+  RTAPI_SAME(Camera, w_, rt_world_camera, w);
+  RTAPI_SAME(Camera, is_defocus_camera_, rt_world_camera, is_defocus);
+  RTAPI_SAME(Camera, lens_radius_, rt_world_camera, lens_radius);
+#undef RTAPI_SAME
+#undef RTAPI_SIZE
+};
+}  // namespace rtapi
 
 // ---- ray_tracing.cuh:9-15 ----------------------------------------------------------------------------
 struct Layer {

@@ -232,8 +232,10 @@ def test_render_bit_exact_vs_oracle(ctx, name, hw, spp):
     s, cam, o = _setup(ctx, name)
     H, W = hw
     want, cnt = o.render_product(H, W, 0, spp, 1234)
-    # wavefront: the single shade queue (default) and material-sorted queues (SORT) give the same sums
-    for flags in (abi.RT_RENDER_FUSED, abi.RT_RENDER_WAVEFRONT, abi.RT_RENDER_WAVEFRONT | abi.RT_RENDER_SORT):
+    # wavefront: the single shade queue (default), material-sorted queues (SORT) and a reordered extend queue (RAYSORT)
+    # give the same sums
+    for flags in (abi.RT_RENDER_FUSED, abi.RT_RENDER_WAVEFRONT, abi.RT_RENDER_WAVEFRONT | abi.RT_RENDER_SORT,
+                  abi.RT_RENDER_WAVEFRONT | abi.RT_RENDER_RAYSORT):
         got, _, st = ctx.render_host(H, W, spp, seed=1234, flags=flags)
         diff = np.nonzero((got.view(np.uint32) != want.view(np.uint32)).any(axis=2))
         assert len(diff[0]) == 0, (flags, len(diff[0]), got[diff][:3], want[diff][:3])
