@@ -760,6 +760,10 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   {
     const char *env = getenv("RT_STRATEGY");
     ctx->opt_wavefront = env && strcmp(env, "wavefront") == 0;
+    env = getenv("RT_STREAM");
+    ctx->opt_stream = !(env && atoi(env) == 0);
+    env = getenv("RT_STREAM_THR");
+    ctx->stream_thr = env ? std::min(std::max(atoi(env), 1), 32) : 8;
   }
   if (ctx->trav == 17) {
     int rc = ensure_wide_tree(ctx, st);

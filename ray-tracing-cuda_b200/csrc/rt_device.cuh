@@ -614,9 +614,14 @@ struct TravStats {
   uint32_t nodes, prims;
 };
 
-template <bool STATS, bool SPH = true, bool EXACT_T = true>
+// SM_LEVELS > 0: the first SM_LEVELS entries of the traversal stack live in shared memory (sm = this thread's column of
+// a [SM_LEVELS][blockDim.x] array, consecutive lanes in consecutive banks), only deeper entries in local memory.  On
+// the soups the per-thread local stack is what fills L1 — 1024 threads x ~20 live entries x 8 B = 160 KB of the SM's
+// 256 KB — and its pops were the largest single source of long-scoreboard stalls
+// (profiles/r01_j_soup10m_fused_ncu_summary.txt: `stack[--sp]` 325 096 samples against 54 629 for the node loads).
+template <bool STATS, bool SPH = true, bool EXACT_T = true, int SM_LEVELS = 0>
 __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r, double t_from, double t_to,
-                                                  TravStats *st) {
+                                                  TravStats *st, uint2 *sm = nullptr) {
   Range rg;
   rg.t_from = t_from;
   rg.t_to = t_to;
@@ -639,7 +644,7 @@ __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r
     const float idx = slab_rcp(r.d.x), idy = slab_rcp(r.d.y), idz = slab_rcp(r.d.z);
     const float nox = -(r.o.x * idx), noy = -(r.o.y * idy), noz = -(r.o.z * idz);
     const float t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
-    uint2 stack[STACK_SIZE];
+    uint2 stack[STACK_SIZE - SM_LEVELS];
     int sp = 0;
     uint32_t ca = s.root_a, cb = s.root_b;
     const float4 *__restrict__ nodes = s.nodes;
@@ -666,7 +671,12 @@ __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r
         if (hl && hr) {
           bool left_first = ln <= rn;
           if (sp < STACK_SIZE) {
-            stack[sp++] = left_first ? make_uint2(ra, rb) : make_uint2(la, lb);
+            const uint2 e = left_first ? make_uint2(ra, rb) : make_uint2(la, lb);
+            if (SM_LEVELS > 0 && sp < SM_LEVELS)
+              sm[sp * blockDim.x] = e;
+            else
+              stack[sp - SM_LEVELS] = e;
+            sp++;
           } else {
             overflow = true;
           }
@@ -686,7 +696,8 @@ __device__ __forceinline__ Hit world_hit_bvh_ifif(const DScene &s, const RayQ &r
         }
       }
       if (sp == 0) break;
-      uint2 e = stack[--sp];
+      --sp;
+      const uint2 e = (SM_LEVELS > 0 && sp < SM_LEVELS) ? sm[sp * blockDim.x] : stack[sp - SM_LEVELS];
       ca = e.x;
       cb = e.y;
     }
@@ -806,11 +817,11 @@ __device__ __forceinline__ Hit world_hit_bvh_ww(const DScene &s, const RayQ &r, 
 }
 
 // Binary-tree traversal loops of the render kernels (identical hits): 0 if-if, 1 while-while.
-template <bool STATS, int TRAV, bool SPH = true, bool EXACT_T = true>
+template <bool STATS, int TRAV, bool SPH = true, bool EXACT_T = true, int SM_LEVELS = 0>
 __device__ __forceinline__ Hit world_hit_bvh(const DScene &s, const RayQ &r, double t_from, double t_to,
-                                             TravStats *st) {
+                                             TravStats *st, uint2 *sm = nullptr) {
   if (TRAV == 1) return world_hit_bvh_ww<STATS, SPH, EXACT_T>(s, r, t_from, t_to, st);
-  return world_hit_bvh_ifif<STATS, SPH, EXACT_T>(s, r, t_from, t_to, st);
+  return world_hit_bvh_ifif<STATS, SPH, EXACT_T, SM_LEVELS>(s, r, t_from, t_to, st, sm);
 }
 
 // ------------------------------------------------------------------------------------------------

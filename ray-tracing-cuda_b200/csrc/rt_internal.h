@@ -63,6 +63,8 @@ struct rt_ctx {
   int n_sm = 148;
   int trav = 0;               // traversal of the render kernel for the committed scene (default_trav)
   bool opt_wavefront = false; // RT_STRATEGY=wavefront at commit: the default strategy of rt_render
+  bool opt_stream = true;     // binary-tree if-if scenes render with k_render_stream (RT_STREAM=0 at commit: k_render)
+  int stream_thr = 8;         // RT_STREAM_THR at commit
   bool has_wide = false;      // the 8-wide tree exists for the committed scene
   int n_wide = 0;
   rtc::FlatItems flat{};  // box list of scenes with <= FLAT_MAX primitives (flat.n = 0: none)

@@ -32,6 +32,7 @@ struct RenderArgs {
   int32_t ch2;                       // phase 2
   int32_t tiles_x, n_tiles;
   uint32_t tile_stride;  // tile of the i-th item of a sweep = i * tile_stride mod n_tiles (1: raster order)
+  int32_t stream_thr;    // k_render_stream: lanes between two queries are served once this many wait
   uint32_t n_items1, n_items;
   unsigned int *work_counter;
   long long *fixed;  // [height * width * 3] radiance sums, 2^-30 units
@@ -64,15 +65,18 @@ __device__ __forceinline__ rt_hit make_rt_hit(const DScene &s, const RayQ &r, co
 
 // Traversals (RT_TRAV_*): 0 binary tree if-if, 1 binary tree while-while, 17 8-wide tree if-if, 20 box list.
 // EXACT_T = false: the caller only uses (float)Hit::t (render kernels; finalize_sphere_hit).
-template <bool STATS, int TRAV, bool SPH = true, bool EXACT_T = true>
+#ifndef RT_SM_STACK
+#define RT_SM_STACK 16  // shared-memory levels of the traversal stack of the large-scene kernel (TRAV 0); 0: all local
+#endif
+template <bool STATS, int TRAV, bool SPH = true, bool EXACT_T = true, int SM_LEVELS = 0>
 __device__ __forceinline__ Hit world_hit(const DScene &s, const FlatItems *fl, const RayQ &r, double t_from, double t_to,
-                                         TravStats *st, int self_box = -1) {
+                                         TravStats *st, int self_box = -1, uint2 *sm = nullptr) {
   if constexpr (TRAV == 20)
     return world_hit_flat<STATS, SPH, EXACT_T>(s, *fl, r, t_from, t_to, st, self_box);
   else if constexpr (TRAV == 17)
     return world_hit_wide_ifif<STATS, 8, SPH, EXACT_T>(s, r, t_from, t_to, st);
   else
-    return world_hit_bvh<STATS, TRAV, SPH, EXACT_T>(s, r, t_from, t_to, st);
+    return world_hit_bvh<STATS, TRAV, SPH, EXACT_T, SM_LEVELS>(s, r, t_from, t_to, st, sm);
 }
 
 // ---- parity hook: HitableList::Hit on explicit rays ------------------------------------------------
@@ -227,6 +231,58 @@ static __device__ __noinline__ CameraRet camera_sample_call(const DCamera &cam, 
   return r;
 }
 
+// The hand-out of sub-units to the lanes of a warp (see k_render).  Warp-synchronous: every lane of the warp calls it
+// in every iteration; `want` = this lane has run out of samples.  The lanes that want work are ranked by ballot and
+// take consecutive sub-units of the warp's current item; when the item is used up lane 0 draws the next one from the
+// global counter.  A lane that gets nothing because the launch has run out of items becomes `finished`.
+struct WorkPool {
+  uint32_t next = 0, end = 0;
+  int tile_px = 0, tile_py = 0, k0 = 0, ch = 1, kend = 0;
+};
+__device__ __forceinline__ void hand_out(const RenderArgs &a, WorkPool &p, bool want, bool &finished, int &pi, int &pj,
+                                         int &k, int &k_end, uint32_t &pixel) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  unsigned wm = __ballot_sync(FULL, want);
+  while (wm) {
+    if (p.next >= p.end) {  // warp-uniform: draw the next item
+      uint32_t it = 0;
+      if (lane == 0) it = atomicAdd(a.work_counter, 1u);
+      it = __shfl_sync(FULL, it, 0);
+      if (it >= a.n_items) {
+        finished |= want;
+        break;
+      }
+      const bool p1 = it < a.n_items1;
+      const uint32_t it2 = p1 ? it : it - a.n_items1;
+      const uint32_t group = it2 / (uint32_t)a.n_tiles;
+      const uint32_t tile = (uint32_t)(((unsigned long long)(it2 - group * (uint32_t)a.n_tiles) * a.tile_stride) % (uint32_t)a.n_tiles);
+      p.tile_px = (int)(tile % (uint32_t)a.tiles_x) * 8;
+      p.tile_py = (int)(tile / (uint32_t)a.tiles_x) * 4;
+      p.ch = p1 ? a.ch1 : a.ch2;
+      p.k0 = p1 ? a.spp_begin + (int)group * a.r1 * a.ch1 : a.spp_begin + a.spp1 + (int)group * a.ch2;
+      p.kend = p1 ? a.spp_begin + a.spp1 : a.spp_end;
+      p.next = 0;
+      p.end = 32u * (uint32_t)(p1 ? a.r1 : 1);
+    }
+    const uint32_t rank = __popc(wm & lt_mask), take = min((uint32_t)__popc(wm), p.end - p.next);
+    if (want && rank < take) {
+      const uint32_t su = p.next + rank;
+      pj = p.tile_px + (int)(su & 7u);
+      pi = p.tile_py + (int)((su >> 3) & 3u);
+      if (pi < a.height && pj < a.width) {  // edge tiles: sub-units outside the image are dropped
+        k = p.k0 + (int)(su >> 5) * p.ch;
+        k_end = min(k + p.ch, p.kend);
+        pixel = (uint32_t)(pi * a.width + pj);
+        want = false;
+      }
+    }
+    p.next += take;
+    wm = __ballot_sync(FULL, want);
+  }
+}
+
 // ---- the render kernel -------------------------------------------------------------------------------------------
 // A persistent grid (blocks = SMs x MINB) of independent warps.  Every lane renders sub-units — (pixel, chunk of
 // a.ch samples), samples in increasing order, a path regenerated in registers the moment the previous one ends —
@@ -242,11 +298,7 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
                                                       typename FlatParamT<TRAV == 20>::type fl = {}) {
   constexpr unsigned FULL = 0xffffffffu;
   constexpr bool SLIM = MINB >= 8;  // 64 registers: shading and camera sampling out of line
-  const int lane = threadIdx.x & 31;
-  const unsigned lt_mask = (1u << lane) - 1u;
-  // warp-uniform: the item being handed out
-  uint32_t pool_next = 0, pool_end = 0;
-  int tile_px = 0, tile_py = 0, pool_k0 = 0, pool_ch = 1, pool_kend = 0;
+  WorkPool pool;  // warp-uniform: the item being handed out
   // lane: the sub-unit being rendered
   int pi = 0, pj = 0, k = 0, k_end = 0;
   bool finished = false, need_new = true;
@@ -269,45 +321,11 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
   ts.nodes = ts.prims = 0;
   const FlatItems *flp = nullptr;
   if constexpr (TRAV == 20) flp = &fl;
+  constexpr int SM_LEVELS = TRAV == 0 ? RT_SM_STACK : 0;
+  __shared__ uint2 s_stack[SM_LEVELS > 0 ? SM_LEVELS : 1][SM_LEVELS > 0 ? 128 : 1];
+  uint2 *const sm = SM_LEVELS > 0 ? &s_stack[0][threadIdx.x] : nullptr;
   for (;;) {
-    bool want = !finished && need_new && k >= k_end;
-    unsigned wm = __ballot_sync(FULL, want);
-    while (wm) {
-      if (pool_next >= pool_end) {  // warp-uniform: draw the next item
-        uint32_t it = 0;
-        if (lane == 0) it = atomicAdd(a.work_counter, 1u);
-        it = __shfl_sync(FULL, it, 0);
-        if (it >= a.n_items) {
-          finished |= want;
-          break;
-        }
-        const bool p1 = it < a.n_items1;
-        const uint32_t it2 = p1 ? it : it - a.n_items1;
-        const uint32_t group = it2 / (uint32_t)a.n_tiles;
-        const uint32_t tile = (uint32_t)(((unsigned long long)(it2 - group * (uint32_t)a.n_tiles) * a.tile_stride) % (uint32_t)a.n_tiles);
-        tile_px = (int)(tile % (uint32_t)a.tiles_x) * 8;
-        tile_py = (int)(tile / (uint32_t)a.tiles_x) * 4;
-        pool_ch = p1 ? a.ch1 : a.ch2;
-        pool_k0 = p1 ? a.spp_begin + (int)group * a.r1 * a.ch1 : a.spp_begin + a.spp1 + (int)group * a.ch2;
-        pool_kend = p1 ? a.spp_begin + a.spp1 : a.spp_end;
-        pool_next = 0;
-        pool_end = 32u * (uint32_t)(p1 ? a.r1 : 1);
-      }
-      const uint32_t rank = __popc(wm & lt_mask), take = min((uint32_t)__popc(wm), pool_end - pool_next);
-      if (want && rank < take) {
-        const uint32_t su = pool_next + rank;
-        pj = tile_px + (int)(su & 7u);
-        pi = tile_py + (int)((su >> 3) & 3u);
-        if (pi < a.height && pj < a.width) {  // edge tiles: sub-units outside the image are dropped
-          k = pool_k0 + (int)(su >> 5) * pool_ch;
-          k_end = min(k + pool_ch, pool_kend);
-          pk.pixel = (uint32_t)(pi * a.width + pj);
-          want = false;
-        }
-      }
-      pool_next += take;
-      wm = __ballot_sync(FULL, want);
-    }
+    hand_out(a, pool, !finished && need_new && k >= k_end, finished, pi, pj, k, k_end, pk.pixel);
     if (__all_sync(FULL, finished)) break;
     if (finished) continue;
     if (need_new) {
@@ -328,7 +346,7 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
     n_rays_ref++;
     bool alive = depth < a.max_depth;  // ray_tracing.cu:23: the query at depth == limit yields 0
     if (alive) {
-      const Hit h = world_hit<STATS, TRAV, SPH, false>(s, flp, ray, 1e-3, (double)CUDART_INF_F, &ts, self_box);
+      const Hit h = world_hit<STATS, TRAV, SPH, false, SM_LEVELS>(s, flp, ray, 1e-3, (double)CUDART_INF_F, &ts, self_box, sm);
       self_box = h.box;
       n_rays++;
       n_seq += (unsigned int)h.seq;  // the query was answered by the sequential scan (world_hit_seq)
@@ -362,6 +380,187 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
     }
   }
   flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims, n_seq, max_nodes);
+}
+
+// ---- the render kernel for large scenes: one traversal STEP per loop iteration ---------------------------------
+// On a scene far larger than the caches a closest-hit query is a chain of dependent node fetches (the 10 M-triangle
+// soup: 137 two-box steps per ray, 64 % of all stall samples waiting for node data), and the queries of a warp's
+// lanes differ several-fold in length.  k_render runs a query to its end inside a function, so every lane waits for
+// the longest query of its warp: 6-8 of 32 lanes issue node fetches (profiles/r02_n_soup10m_ncu_summary.txt) and the
+// memory system sees a quarter of the requests it could.  Here the query is unrolled into the render loop: one
+// iteration = one step (an inner node: two box tests, descend / push / pop; or a leaf: its record tests) of every
+// lane's OWN query, and a lane whose query has ended shades its hit, scatters or starts its next sample, and begins
+// the next query in the same iteration — while the other lanes keep walking.  A lane is idle only while the few lanes
+// that finished are being shaded.  Same arithmetic, same visit order per ray, same draws: the sums are bit-identical
+// to k_render's (and the wavefront pipeline's).
+// Round 1 tried this shape twice (a while-while walker per round, and a warp-voted state machine with deferred
+// minority work) and lost to the plain loop both times to register pressure; this form keeps the per-lane state
+// minimal (no Philox cache, 32-bit counters, shading out of line by value) and the stack in shared memory.
+template <bool STATS, bool SPH>
+#ifndef RT_STREAM_MINB
+#define RT_STREAM_MINB 8
+#endif
+__global__ void __launch_bounds__(128, RT_STREAM_MINB) k_render_stream(DScene s, DCamera cam, RenderArgs a, RenderCounters *ctr) {
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr int SM_LEVELS = RT_SM_STACK > 0 ? RT_SM_STACK : 16;
+  __shared__ uint2 s_stack[SM_LEVELS][128];
+  uint2 *const sm = &s_stack[0][threadIdx.x];
+  uint2 lstack[STACK_SIZE - SM_LEVELS];
+  WorkPool pool;
+  int pi = 0, pj = 0, k = 0, k_end = 0;
+  bool finished = false, need_new = true;
+  bool walking = false;  // a query of this lane is in progress
+  bool pending = false;  // ... or has ended and its hit has not been shaded yet
+  PathKey pk;
+  pk.pixel = 0;
+  pk.sample = 0;
+  pk.k0 = a.k0;
+  pk.k1 = a.k1;
+  V3 T = mk(1.f, 1.f, 1.f);
+  RayQ ray;
+  ray.o = ray.d = mk(0.f, 0.f, 0.f);
+  int depth = 0;
+  // the query (world_hit_bvh_ifif's locals)
+  Range rg;
+  rg.t_from = 1e-3;
+  rg.t_to = (double)CUDART_INF_F;
+  rg.tf_f = float_ge(1e-3);
+  rg.lib_pow = s.sphere_pow != 0;
+  const float t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
+  Best b;
+  best_init(b, rg.t_to);
+  bool ambiguous = false, overflow = false;
+  float idx = 0.f, idy = 0.f, idz = 0.f, nox = 0.f, noy = 0.f, noz = 0.f;
+  uint32_t ca = 0, cb = 0;
+  int sp = 0;
+  uint32_t n_samples = 0, n_rays = 0, n_rays_ref = 0, n_seq = 0, n_nodes = 0, n_prims = 0;
+  const float4 *__restrict__ nodes = s.nodes;
+  for (;;) {
+    // the lanes between two queries are served together: when `stream_thr` of them wait, or nobody walks any more
+    const unsigned waiting = __ballot_sync(FULL, !walking && !finished), walkers = __ballot_sync(FULL, walking);
+    if (waiting == 0u && walkers == 0u) break;
+    const bool serve = __popc(waiting) >= a.stream_thr || walkers == 0u;
+    if (serve) hand_out(a, pool, !finished && !walking && !pending && need_new && k >= k_end, finished, pi, pj, k, k_end, pk.pixel);
+    if (serve && !walking && !finished) {
+      // ---- between two queries of this lane: shade the hit, scatter or start the next sample, begin the next query
+      if (pending) {
+        pending = false;
+        resolve_quad_order(s, b, ambiguous);
+        finalize_sphere_hit<SPH, false>(s, ray, rg, b, ambiguous);
+        Hit h;
+        if (ambiguous || overflow) {
+          h = world_hit_seq(s, ray, rg.t_from, rg.t_to);
+        } else {
+          h.t = b.rec == REC_NONE ? 0.0 : b.t;
+          h.rec = b.rec;
+          h.seq = 0;
+          h.box = -1;
+        }
+        n_rays++;
+        n_seq += (uint32_t)h.seq;
+        bool alive = false;
+        if (h.rec != REC_NONE) {
+          PhiloxCache pc;
+          pc.block = PHILOX_NO_BLOCK;
+          pc.w2 = pc.w3 = 0;
+          ShadeRet sr = shade_hit_call<SPH>(s, cam, ray, h, pk, depth, pc, T);
+          alive = sr.alive;
+          ray = sr.ray;
+          T = sr.T;
+          if (!alive) add_radiance(a.fixed, (int)pk.pixel, sr.L);
+        }
+        if (alive) {
+          depth++;
+        } else {
+          k++;
+          need_new = true;
+        }
+      }
+      if (need_new && k < k_end) {
+        pk.sample = (uint32_t)k;
+        ray = camera_sample_call(cam, pi, pj, a.height, a.width, pk).ray;
+        T = mk(1.f, 1.f, 1.f);
+        depth = 0;
+        need_new = false;
+        n_samples++;
+      }
+      if (!need_new) {
+        n_rays_ref++;
+        if (depth < a.max_depth) {  // ray_tracing.cu:23: the query at depth == limit yields 0
+          best_init(b, rg.t_to);
+          if (s.sky_obj >= 0) {  // sky.cu:18-27: always a candidate at t = 1e9
+            b.t = 1e9;
+            b.t_f = 1e9f;
+            b.rec = REC_SKY;
+            b.obj = s.sky_obj;
+            b.sub = 0;
+          }
+          ambiguous = overflow = false;
+          idx = slab_rcp(ray.d.x), idy = slab_rcp(ray.d.y), idz = slab_rcp(ray.d.z);
+          nox = -(ray.o.x * idx), noy = -(ray.o.y * idy), noz = -(ray.o.z * idz);
+          ca = s.root_a, cb = s.root_b;
+          sp = 0;
+          pending = true;
+          walking = s.n_recs > 0;
+        } else {
+          k++;
+          need_new = true;
+        }
+      }
+    }
+    if (walking) {
+      // ---- one step of world_hit_bvh_ifif
+      bool pop = true;
+      if (cb & LEAF_FLAG) {
+        int q = (int)ca;
+        const int end = (int)(ca + (cb & ~LEAF_FLAG));
+        while (q < end) {
+          const int used = rec_test<SPH>(s.recs, q, ray, rg, b, ambiguous);
+          if (STATS) n_prims += used;
+          q += used;
+        }
+      } else {
+        if (STATS) n_nodes += 2;
+        const float4 l0 = __ldg(nodes + 2 * (size_t)ca), l1 = __ldg(nodes + 2 * (size_t)ca + 1);
+        const float4 r0 = __ldg(nodes + 2 * (size_t)cb), r1 = __ldg(nodes + 2 * (size_t)cb + 1);
+        const float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
+        float ln, lf, rn, rf;
+        slab2(l0, l1, r0, r1, idx, idy, idz, nox, noy, noz, t_lo, t_hi, ln, lf, rn, rf);
+        const bool hl = ln <= lf * 1.00001f, hr = rn <= rf * 1.00001f;
+        const uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
+        const uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
+        if (hl | hr) {
+          const bool left_first = hl & (!hr | (ln <= rn));
+          if (hl & hr) {
+            if (sp < STACK_SIZE) {
+              const uint2 e = left_first ? make_uint2(ra, rb) : make_uint2(la, lb);
+              if (sp < SM_LEVELS)
+                sm[sp * 128] = e;
+              else
+                lstack[sp - SM_LEVELS] = e;
+              sp++;
+            } else {
+              overflow = true;
+            }
+          }
+          ca = left_first ? la : ra;
+          cb = left_first ? lb : rb;
+          pop = false;
+        }
+      }
+      if (pop) {
+        if (sp == 0) {
+          walking = false;
+        } else {
+          --sp;
+          const uint2 e = sp < SM_LEVELS ? sm[sp * 128] : lstack[sp - SM_LEVELS];
+          ca = e.x;
+          cb = e.y;
+        }
+      }
+    }
+  }
+  flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims, n_seq, 0u);
 }
 
 // ---- wavefront pipeline ------------------------------------------------------------------------------
@@ -930,8 +1129,9 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
     const int trav = ctx->trav;
     // resident blocks per SM the kernel is compiled for (register budget): 6 (80 registers) for cache-resident
     // scenes, 5 for the 8-wide tree, 8 (64 registers) from 500 k records up, where the loop is latency bound
-    const int minb = trav == 0 ? 8 : (trav == 17 ? 5 : 6);
+    const int minb = trav == 0 ? (ctx->opt_stream ? RT_STREAM_MINB : 8) : (trav == 17 ? 5 : 6);
     plan_work(ctx, a, minb, trav == 20);
+    a.stream_thr = ctx->stream_thr;
     const int grid = ctx->n_sm * minb;
 #define RT_LAUNCH(T, M, ...)                                                                             \
   if (stats_on && sph)                                                                                   \
@@ -949,6 +1149,15 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
       RT_LAUNCH(17, 5)
     } else if (trav == 1) {
       RT_LAUNCH(1, 6)
+    } else if (ctx->opt_stream) {
+      if (stats_on && sph)
+        k_render_stream<true, true><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr);
+      else if (stats_on)
+        k_render_stream<true, false><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr);
+      else if (sph)
+        k_render_stream<false, true><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr);
+      else
+        k_render_stream<false, false><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr);
     } else {
       RT_LAUNCH(0, 8)
     }
