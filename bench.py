@@ -270,26 +270,36 @@ def hit_bit_exact(rt, ctx, name, H, W, scene, camspec, oracle_budget_s=8.0):
         # argument list left to right, g++ (the host build the oracle is pinned to) right to left; the GPU reference
         # therefore renders the "ltr" scene, and so do we here
         scene_b, cam_b, _ = rt.scenes.spheres(arg_order="ltr")
-    ctx.commit(scene_b)
     camera = rt.core.camera_look_at(cam_b)
+    # (a) oracle: the reference's semantics on the host (its own BVH, AABB::Hit included); a stride keeps it in budget.
+    # The oracle is pinned to the reference's HOST build, whose pow() is glibc's (correctly rounded); the reference's
+    # CUDA build and the product call CUDA's pow, 1 ulp off on 6-14 % of operands (pow_kat_device).  The comparison
+    # with the oracle therefore commits the scene with RT_SPHERE_POW=ieee; `mismatch_vs_oracle_cuda_pow` is the count
+    # in the product's default mode (sphere hits only).
+    os.environ["RT_SPHERE_POW"] = "ieee"
+    try:
+        ctx.commit(scene_b)
+        ctx.set_camera(camera)
+        rays = ctx.primary_rays(H, W)
+        mine_ieee = ctx.trace_closest(rays)
+    finally:
+        del os.environ["RT_SPHERE_POW"]
+    ctx.commit(scene_b)
     ctx.set_camera(camera)
-    rays = ctx.primary_rays(H, W)
     mine = ctx.trace_closest(rays)
-    # (a) oracle: the reference's semantics on the host (its own BVH, AABB::Hit included); a stride keeps it in budget
     o = ck.OracleScene(scene_b, camera)
     stride = 1
     t0 = time.perf_counter()
-    probe = o.trace(rays[::64], quirks=1)
+    o.trace(rays[::64], quirks=1)
     dt = (time.perf_counter() - t0) * 64
     while dt / stride > oracle_budget_s:
         stride *= 2
     want = o.trace(rays[::stride], quirks=1) if stride > 1 else o.trace(rays, quirks=1)
-    got = mine[::stride]
     fields = ("t", "obj", "sub", "normal", "material")
-    bad = ck.hits_equal(got, want, fields)
-    out["mismatch_vs_oracle"] = int(len(bad))
+    out["mismatch_vs_oracle"] = int(len(ck.hits_equal(mine_ieee[::stride], want, fields)))
+    out["mismatch_vs_oracle_cuda_pow"] = int(len(ck.hits_equal(mine[::stride], want, fields)))
     out["oracle_rays"] = int(len(want))
-    del probe
+    out["oracle_note"] = "oracle = reference semantics on the host; product committed with RT_SPHERE_POW=ieee for this column"
     # (b), (c) the reference's CUDA code
     tmp = tempfile.mkdtemp()
     ref_scene, extra = _ref_cuda_args(name, scene_b, tmp)
@@ -457,14 +467,15 @@ class Runner:
         issue_peak = self.props.multi_processor_count * 4 * sm_mhz * 1e6
         achieved = thread_inst / 32.0 / (kern_ms * 1e-3)
         is_soup = name.startswith("soup")
-        base_name = "spheres" if name == "spheres" else workload
+        base_name = workload
         traffic = consts.get("dram_bytes_per_launch", {}).get(base_name)
         if traffic is not None and is_soup:  # soups: node / record misses scale with the samples of the launch
             traffic = int(traffic * float(count) / consts.get("dram_bytes_capture_spp", {}).get(base_name, count))
         roofline = {"bound": "issue", "achieved": achieved / 1e9, "peak": issue_peak / 1e9, "unit": "Gwarp-inst/s",
                     "frac": achieved / issue_peak, "traffic": traffic,
-                    "traffic_source": "dram bytes of the committed ncu capture of this workload (profiles/constants.json), "
-                                      "not measured in this run",
+                    "traffic_source": "dram__bytes_read+write of the committed ncu capture of this workload (profiles/constants.json"
+                                      f", captured at {consts.get('dram_bytes_capture_spp', {}).get(base_name)} spp"
+                                      + (", scaled to this launch's samples" if is_soup else "") + "); not measured in this run",
                     "kernel": "k_render" if fused_run else "k_wf_extend", "kernel_ms": kern_ms, "sm_mhz": sm_mhz,
                     "peak_source": "148 SMs x 4 issue slots x sampled SM clock (B200_PROFILING.md / SURVEY 8d); not a tensor or HBM bound",
                     "algorithmic": {"box_tests_per_ray": boxes / max(float(st_prof.rays), 1.0),
@@ -497,8 +508,7 @@ class Runner:
                        "d2h_bytes_per_step": H * W * 12},
                "gpu_launches": int(st.kernel_launches * steps),
                "roofline": roofline, "clocks": clocks,
-               "build": {"ms": build.build_ms, "max_depth": build.max_depth, "sah": build.sah_cost,
-                         "wide_nodes": build.n_wide_nodes, "wide_depth": build.wide_depth}}
+               "build": {"ms": build.build_ms, "max_depth": build.max_depth, "sah": build.sah_cost}}
         if baselines and is_soup:
             out["cpu_baseline"] = {"unavailable": "the host reference build scans meshes with 2048-triangle leaves (bvh.cuh:71-98): "
                                                   "no bounded sample of a 1M+ triangle frame finishes in the bench budget"}

@@ -137,8 +137,7 @@ typedef struct rt_build_stats {
   float build_ms;       /* device time of the BVH build (CUDA events) */
   float upload_ms;
   float sah_cost;
-  int32_t n_wide_nodes; /* 256-byte 8-wide nodes collapsed from the binary tree (the render kernels' tree) */
-  int32_t wide_depth;   /* levels of the wide tree */
+  int32_t reserved_[2];
 } rt_build_stats;
 
 typedef struct rt_render_stats {
@@ -194,7 +193,7 @@ int rt_camera_look_at(const float position[3], const float look_at[3], const flo
  * pass Ray::direction_, i.e. already normalized by Ray::Ray, ray.cu:8-11).
  * mode 0: the traversal the committed scene renders with (product path); mode 1: sequential scan over every
  * primitive in list order, as HitableList::Hit executes it; modes 2..5: one specific traversal of the render kernel
- * (2 binary tree if-if, 3 binary tree while-while, 4 8-wide tree, 5 box list — scenes of at most 32 primitives only).
+ * (2 binary tree if-if, 3 binary tree while-while, 4 box list — scenes of at most 32 primitives only).
  * All modes must return identical hits. */
 int rt_trace_closest_host(rt_ctx *ctx, const float *h_rays, int64_t n, double t_from, double t_to,
                           int mode, rt_hit *h_hits);

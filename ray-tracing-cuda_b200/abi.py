@@ -17,7 +17,7 @@ RT_RENDER_SORT = 8
 RT_RENDER_WAVEFRONT = 16
 RT_RENDER_RAYSORT = 128
 # rt_trace_closest modes: the scene's render traversal, HitableList::Hit as a sequential scan, and each traversal by name
-TRACE_DEFAULT, TRACE_SEQUENTIAL, TRACE_IFIF, TRACE_WHILE_WHILE, TRACE_WIDE8, TRACE_BOX_LIST = range(6)
+TRACE_DEFAULT, TRACE_SEQUENTIAL, TRACE_IFIF, TRACE_WHILE_WHILE, TRACE_BOX_LIST = range(5)
 FIXED_ONE = 1 << 30  # units of the exact radiance sums (rt_render_fixed)
 
 material_dtype = np.dtype(
@@ -86,8 +86,8 @@ class RtBuildStats(C.Structure):
         ("build_ms", C.c_float),
         ("upload_ms", C.c_float),
         ("sah_cost", C.c_float),
-        ("n_wide_nodes", C.c_int32),
-        ("wide_depth", C.c_int32),
+        ("reserved0_", C.c_int32),
+        ("reserved1_", C.c_int32),
     ]
 
 

@@ -255,85 +255,6 @@ __global__ void k_refit(const uint32_t *left, const uint32_t *right, const uint3
   }
 }
 
-// ---- wide collapse: binary tree -> 8 children per node ---------------------------------------------
-// One thread per wide node of the current level.  Starting from the two children of its binary
-// node it keeps opening the inner child with the largest surface area until 8 slots are used or
-// only leaves are left (the greedy collapse of Wald et al. 2008 / Ylitie et al. 2017).  Inner
-// children get a wide-node index (atomic counter) and go to the next level's queue.  WRITE = false
-// only counts (sizes the node buffer).
-template <bool WRITE, int W>
-__global__ void k_wide_expand(const float4 *__restrict__ nodes, const uint2 *__restrict__ in_q, int n_in, uint2 *out_q,
-                              uint32_t *counters /* [0] next-level queue length, [1] wide nodes allocated */,
-                              float4 *wnodes) {
-  int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n_in) return;
-  const uint32_t bn = in_q[t].x, wn = in_q[t].y;
-  uint32_t slot[W];
-  using L = WideLayout<W>;
-  int n;
-  {
-    uint32_t a = __float_as_uint(nodes[2 * (size_t)bn].w), b = __float_as_uint(nodes[2 * (size_t)bn + 1].w);
-    if (b & LEAF_FLAG) {  // the whole scene is one leaf
-      slot[0] = bn;
-      n = 1;
-    } else {
-      slot[0] = a;
-      slot[1] = b;
-      n = 2;
-    }
-  }
-  while (n < W) {
-    int best = -1;
-    float best_area = -1.f;
-    for (int i = 0; i < n; i++) {
-      float4 lo = nodes[2 * (size_t)slot[i]], hi = nodes[2 * (size_t)slot[i] + 1];
-      if (__float_as_uint(hi.w) & LEAF_FLAG) continue;
-      float ar = half_area(lo, hi);
-      if (ar > best_area) {
-        best_area = ar;
-        best = i;
-      }
-    }
-    if (best < 0) break;
-    uint32_t a = __float_as_uint(nodes[2 * (size_t)slot[best]].w), b = __float_as_uint(nodes[2 * (size_t)slot[best] + 1].w);
-    slot[best] = a;
-    slot[n++] = b;
-  }
-  float *f = WRITE ? reinterpret_cast<float *>(wnodes + (size_t)L::F4 * wn) : nullptr;
-  uint32_t *u = reinterpret_cast<uint32_t *>(f);
-  for (int i = 0; i < W; i++) {
-    if (i >= n) {
-      if (WRITE) {
-        f[i] = f[W + i] = f[2 * W + i] = CUDART_INF_F;
-        f[3 * W + i] = f[4 * W + i] = f[5 * W + i] = -CUDART_INF_F;
-        u[6 * W + i] = WREF_EMPTY;
-      }
-      continue;
-    }
-    float4 lo = nodes[2 * (size_t)slot[i]], hi = nodes[2 * (size_t)slot[i] + 1];
-    uint32_t a = __float_as_uint(lo.w), b = __float_as_uint(hi.w);
-    uint32_t ref;
-    if (b & LEAF_FLAG) {
-      ref = WLEAF | ((b & ~LEAF_FLAG) << WLEAF_COUNT_SHIFT) | a;
-    } else {
-      ref = atomicAdd(counters + 1, 1u);
-      uint32_t q = atomicAdd(counters + 0, 1u);
-      if (out_q) out_q[q] = make_uint2(slot[i], ref);
-    }
-    if (WRITE) {
-      f[i] = lo.x, f[W + i] = lo.y, f[2 * W + i] = lo.z;
-      f[3 * W + i] = hi.x, f[4 * W + i] = hi.y, f[5 * W + i] = hi.z;
-      u[6 * W + i] = ref;
-    }
-  }
-  if (WRITE) {
-    u[7 * W] = (1u << n) - 1u;
-    u[7 * W + 1] = (uint32_t)n;
-    for (int q = 2; q < W; q++) u[7 * W + q] = 0;
-  }
-}
-
-
 }  // namespace rtc
 
 // =================================================================================================
@@ -371,61 +292,6 @@ inline HostRec tri_rec(const float p0[3], const float p1[3], const float p2[3], 
 }
 
 }  // namespace
-
-// The 8-wide tree is derived from the binary tree ON DEMAND: rt_scene_commit builds it when the scene renders with it
-// (4 k - 500 k records), rt_trace_closest when mode 4 asks for it.  The collapse runs level by level; its two queues
-// live in scratch[6] / [7] (bp_lo / bp_hi of the build, dead after k_emit and sized for one entry per build primitive).
-int rtc::ensure_wide_tree(rt_ctx *ctx, cudaStream_t st) {
-  if (ctx->has_wide || ctx->scene.n_recs <= 0) return RT_OK;
-  if ((size_t)ctx->scene.n_recs > (size_t)WLEAF_FIRST_MASK) {
-    set_error("wide tree: too many records for the wide-node leaf encoding");
-    return RT_ERR_LIMIT;
-  }
-  DevBuf *S = ctx->scratch;
-  RT_CUDA(S[10].reserve(32));
-  uint32_t *cnt = S[10].as<uint32_t>();
-  const int f4 = WideLayout<8>::F4;
-  int n_w = 0;
-  for (int pass = 0; pass < 2; pass++) {
-    uint2 *in = S[6].as<uint2>(), *out = S[7].as<uint2>();
-    uint2 seed = make_uint2(0u, 0u);
-    uint32_t c[2] = {0u, 1u};
-    RT_CUDA(cudaMemcpyAsync(in, &seed, sizeof(seed), cudaMemcpyHostToDevice, st));
-    RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
-    int n_in = 1, levels = 0;
-    while (n_in > 0) {
-      const float4 *bn = ctx->nodes.as<float4>();
-      float4 *wn = pass ? ctx->wnodes.as<float4>() : nullptr;
-      if (pass == 0)
-        k_wide_expand<false, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
-      else
-        k_wide_expand<true, 8><<<nblk(n_in), 256, 0, st>>>(bn, in, n_in, out, cnt, wn);
-      RT_CUDA(cudaMemcpyAsync(c, cnt, sizeof(c), cudaMemcpyDeviceToHost, st));
-      RT_CUDA(cudaStreamSynchronize(st));
-      n_in = (int)c[0];
-      c[0] = 0;
-      RT_CUDA(cudaMemcpyAsync(cnt, c, sizeof(c), cudaMemcpyHostToDevice, st));
-      std::swap(in, out);
-      levels++;
-    }
-    if (pass == 0) {
-      n_w = (int)c[1];
-      RT_CUDA(ctx->wnodes.reserve((size_t)n_w * f4 * 16));
-    } else if ((int)c[1] != n_w) {
-      set_error("wide tree: collapse passes disagree");
-      return RT_ERR_CUDA;
-    }
-    ctx->build_stats.wide_depth = levels;
-  }
-  ctx->n_wide = n_w;
-  ctx->scene.wnodes = ctx->wnodes.as<float4>();
-  ctx->scene.n_wnodes = n_w;
-  ctx->build_stats.n_wide_nodes = n_w;
-  ctx->has_wide = true;
-  RT_CUDA(cudaGetLastError());
-  return RT_OK;
-}
-
 
 extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_stats *stats) {
   if (!ctx || !d) {
@@ -633,7 +499,7 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   uint32_t root_words[2] = {0, LEAF_FLAG};
   if (n_bp > 0) {
     const char *env = getenv("RT_MAX_LEAF");
-    int max_leaf = env ? std::min(std::max(1, atoi(env)), WLEAF_MAX_COUNT) : 4;
+    int max_leaf = env ? std::min(std::max(1, atoi(env)), 7) : 4;
     env = getenv("RT_SAH_CT");
     float c_trav = env ? (float)atof(env) : 1.2f;
     // S[3] bp_first, S[6] bp_lo, S[7] bp_hi, S[8] scene bounds + keys, S[9] vals ...
@@ -706,10 +572,6 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   }
   DScene &s = ctx->scene;
   s.nodes = ctx->nodes.as<float4>();
-  s.wnodes = nullptr;  // derived tree: built on demand (ensure_wide_tree)
-  s.n_wnodes = 0;
-  ctx->has_wide = false;
-  ctx->n_wide = 0;
   s.recs = ctx->recs.as<float4>();
   s.recs_seq = recs_seq;
   s.face_uv = any_uv ? ctx->face_uv.as<float>() : nullptr;
@@ -752,25 +614,13 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   ctx->has_scene = true;
 
   rt_build_stats &bs = ctx->build_stats;
-  bs.n_wide_nodes = 0;
-  bs.wide_depth = 0;
+  bs.reserved_[0] = bs.reserved_[1] = 0;
   // the traversal this scene renders with (RT_TRAV / RT_STRATEGY are read here, once per commit) and its tree;
   // part of the build time
   ctx->trav = default_trav(ctx);
   {
     const char *env = getenv("RT_STRATEGY");
     ctx->opt_wavefront = env && strcmp(env, "wavefront") == 0;
-    env = getenv("RT_STREAM");
-    ctx->opt_stream = !(env && atoi(env) == 0);
-    env = getenv("RT_STREAM_THR");
-    ctx->stream_thr = env ? std::min(std::max(atoi(env), 1), 32) : 8;
-  }
-  if (ctx->trav == 17) {
-    int rc = ensure_wide_tree(ctx, st);
-    if (rc) {
-      ctx->has_scene = false;
-      return rc;
-    }
   }
   RT_CUDA(cudaEventRecord(ctx->ev1, st));
   RT_CUDA(cudaEventSynchronize(ctx->ev1));

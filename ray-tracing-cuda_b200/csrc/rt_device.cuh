@@ -61,24 +61,6 @@ constexpr uint32_t LEAF_FLAG = 0x80000000u;
 constexpr int REC_NONE = -1, REC_SKY = -2;
 constexpr int STACK_SIZE = 64;
 
-// ------------------------------------------------------------------------------------------------
-// Wide nodes (256 B = 16 x float4): the binary LBVH collapsed to 8 children per node (rt_build.cu,
-// k_wide_expand).  Child boxes are stored per component so that a ray picks its near / far planes
-// by address (its direction octant) instead of by min/max:
-//   float4 0,1 lo.x[0..7]   2,3 lo.y   4,5 lo.z   6,7 hi.x   8,9 hi.y   10,11 hi.z
-//   float4 12,13 ref[0..7]   14 {valid-children mask, child count, -, -}   15 unused
-// ref: inner child = index of its wide node; leaf child = WLEAF | count << 28 | first record;
-// empty slot = WREF_EMPTY with an inverted box.
-// ------------------------------------------------------------------------------------------------
-constexpr int WIDE = 8, WNODE_F4 = 16;
-template <int W>
-struct WideLayout {
-  static constexpr int G = W / 4, F4 = 8 * G, HI = 3 * G, REF = 6 * G, META = 7 * G;
-};
-constexpr uint32_t WLEAF = 0x80000000u, WREF_EMPTY = 0xffffffffu;
-constexpr int WLEAF_COUNT_SHIFT = 28, WLEAF_MAX_COUNT = 7;
-constexpr uint32_t WLEAF_FIRST_MASK = (1u << WLEAF_COUNT_SHIFT) - 1;
-
 struct DMaterial {  // 32 B, two float4 loads
   float4 color_fuzz;  // albedo / attenuation / emission, Metal fuzz
   int32_t type;       // RT_MAT_*
@@ -95,7 +77,6 @@ struct DTexture {
 
 struct DScene {
   const float4 *nodes;     // 32-byte nodes: {lo.xyz, a}, {hi.xyz, b}
-  const float4 *wnodes;    // 256-byte wide nodes (8 children), node 0 = root; null when n_recs == 0
   const float4 *recs;      // records in BVH (Morton) order, 3 float4 each
   const float4 *recs_seq;  // records in list order (Append order; faces in post-sort order; incl. SKY)
   const float *face_uv;    // per BVH-order record: 6 floats (Face<true> texcoords), or null
@@ -103,7 +84,7 @@ struct DScene {
   const DMaterial *mats;
   const DTexture *textures;
   uint32_t root_a, root_b;  // the root's (a, b) words
-  int32_t n_recs, n_recs_seq, n_nodes, n_wnodes;
+  int32_t n_recs, n_recs_seq, n_nodes;
   int32_t sky_obj, sky_mat;  // first Sky in the list, or -1
   int32_t has_spheres;
   int32_t sphere_pow;  // 1: Sphere::Hit's pow() calls go to CUDA's pow like the reference's (sphere_test); 0: IEEE x * x / sqrt

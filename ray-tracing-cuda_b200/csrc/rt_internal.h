@@ -52,7 +52,6 @@ struct RenderCounters {  // device-side counters of one rt_render call
 struct rt_ctx;
 namespace rtc {
 int default_trav(const rt_ctx *ctx);                  // rt_render.cu: the scene's traversal (RT_TRAV overrides), read at commit
-int ensure_wide_tree(rt_ctx *ctx, cudaStream_t st);   // rt_build.cu: the 8-wide tree, derived from the binary tree on demand
 }  // namespace rtc
 
 struct rt_ctx {
@@ -63,14 +62,10 @@ struct rt_ctx {
   int n_sm = 148;
   int trav = 0;               // traversal of the render kernel for the committed scene (default_trav)
   bool opt_wavefront = false; // RT_STRATEGY=wavefront at commit: the default strategy of rt_render
-  bool opt_stream = true;     // binary-tree if-if scenes render with k_render_stream (RT_STREAM=0 at commit: k_render)
-  int stream_thr = 8;         // RT_STREAM_THR at commit
-  bool has_wide = false;      // the 8-wide tree exists for the committed scene
-  int n_wide = 0;
   rtc::FlatItems flat{};  // box list of scenes with <= FLAT_MAX primitives (flat.n = 0: none)
   rt_camera camera_host{};
   // scene storage
-  rtc::DevBuf nodes, wnodes, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;
+  rtc::DevBuf nodes, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;
   std::vector<void *> tex_allocs;
   // build scratch
   rtc::DevBuf scratch[12];

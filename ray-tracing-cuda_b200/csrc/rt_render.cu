@@ -10,7 +10,7 @@
 #include <string>
 
 #include "rt_internal.h"
-#include "rt_wide.cuh"
+#include "rt_flat.cuh"
 
 namespace rtc {
 
@@ -32,7 +32,6 @@ struct RenderArgs {
   int32_t ch2;                       // phase 2
   int32_t tiles_x, n_tiles;
   uint32_t tile_stride;  // tile of the i-th item of a sweep = i * tile_stride mod n_tiles (1: raster order)
-  int32_t stream_thr;    // k_render_stream: lanes between two queries are served once this many wait
   uint32_t n_items1, n_items;
   unsigned int *work_counter;
   long long *fixed;  // [height * width * 3] radiance sums, 2^-30 units
@@ -63,7 +62,7 @@ __device__ __forceinline__ rt_hit make_rt_hit(const DScene &s, const RayQ &r, co
   return o;
 }
 
-// Traversals (RT_TRAV_*): 0 binary tree if-if, 1 binary tree while-while, 17 8-wide tree if-if, 20 box list.
+// Traversals (RT_TRAV): 0 binary tree if-if, 1 binary tree while-while, 20 box list.
 // EXACT_T = false: the caller only uses (float)Hit::t (render kernels; finalize_sphere_hit).
 #ifndef RT_SM_STACK
 #define RT_SM_STACK 16  // shared-memory levels of the traversal stack of the large-scene kernel (TRAV 0); 0: all local
@@ -73,15 +72,13 @@ __device__ __forceinline__ Hit world_hit(const DScene &s, const FlatItems *fl, c
                                          TravStats *st, int self_box = -1, uint2 *sm = nullptr) {
   if constexpr (TRAV == 20)
     return world_hit_flat<STATS, SPH, EXACT_T>(s, *fl, r, t_from, t_to, st, self_box);
-  else if constexpr (TRAV == 17)
-    return world_hit_wide_ifif<STATS, 8, SPH, EXACT_T>(s, r, t_from, t_to, st);
   else
     return world_hit_bvh<STATS, TRAV, SPH, EXACT_T, SM_LEVELS>(s, r, t_from, t_to, st, sm);
 }
 
 // ---- parity hook: HitableList::Hit on explicit rays ------------------------------------------------
-// mode 1 sequential scan, 2 if-if, 3 while-while, 4 8-wide tree, 5 box list (mode 0 is resolved by the host to the
-// traversal the scene renders with).
+// mode 1 sequential scan, 2 if-if, 3 while-while, 4 box list (mode 0 is resolved by the host to the traversal the
+// scene renders with).
 __global__ void __launch_bounds__(128) k_trace_closest(DScene s, FlatItems fl, const float *__restrict__ rays, int64_t n,
                                                        double t_from, double t_to, int mode, rt_hit *out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -93,8 +90,7 @@ __global__ void __launch_bounds__(128) k_trace_closest(DScene s, FlatItems fl, c
   switch (mode) {
     case 1: h = world_hit_seq(s, r, t_from, t_to); break;
     case 3: h = world_hit<false, 1>(s, &fl, r, t_from, t_to, nullptr); break;
-    case 4: h = world_hit<false, 17>(s, &fl, r, t_from, t_to, nullptr); break;
-    case 5: h = world_hit<false, 20>(s, &fl, r, t_from, t_to, nullptr); break;
+    case 4: h = world_hit<false, 20>(s, &fl, r, t_from, t_to, nullptr); break;
     default: h = world_hit<false, 0>(s, &fl, r, t_from, t_to, nullptr); break;
   }
   out[i] = make_rt_hit(s, r, h);
@@ -380,187 +376,6 @@ __global__ void __launch_bounds__(128, MINB) k_render(DScene s, DCamera cam, Ren
     }
   }
   flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims, n_seq, max_nodes);
-}
-
-// ---- the render kernel for large scenes: one traversal STEP per loop iteration ---------------------------------
-// On a scene far larger than the caches a closest-hit query is a chain of dependent node fetches (the 10 M-triangle
-// soup: 137 two-box steps per ray, 64 % of all stall samples waiting for node data), and the queries of a warp's
-// lanes differ several-fold in length.  k_render runs a query to its end inside a function, so every lane waits for
-// the longest query of its warp: 6-8 of 32 lanes issue node fetches (profiles/r02_n_soup10m_ncu_summary.txt) and the
-// memory system sees a quarter of the requests it could.  Here the query is unrolled into the render loop: one
-// iteration = one step (an inner node: two box tests, descend / push / pop; or a leaf: its record tests) of every
-// lane's OWN query, and a lane whose query has ended shades its hit, scatters or starts its next sample, and begins
-// the next query in the same iteration — while the other lanes keep walking.  A lane is idle only while the few lanes
-// that finished are being shaded.  Same arithmetic, same visit order per ray, same draws: the sums are bit-identical
-// to k_render's (and the wavefront pipeline's).
-// Round 1 tried this shape twice (a while-while walker per round, and a warp-voted state machine with deferred
-// minority work) and lost to the plain loop both times to register pressure; this form keeps the per-lane state
-// minimal (no Philox cache, 32-bit counters, shading out of line by value) and the stack in shared memory.
-template <bool STATS, bool SPH>
-#ifndef RT_STREAM_MINB
-#define RT_STREAM_MINB 8
-#endif
-__global__ void __launch_bounds__(128, RT_STREAM_MINB) k_render_stream(DScene s, DCamera cam, RenderArgs a, RenderCounters *ctr) {
-  constexpr unsigned FULL = 0xffffffffu;
-  constexpr int SM_LEVELS = RT_SM_STACK > 0 ? RT_SM_STACK : 16;
-  __shared__ uint2 s_stack[SM_LEVELS][128];
-  uint2 *const sm = &s_stack[0][threadIdx.x];
-  uint2 lstack[STACK_SIZE - SM_LEVELS];
-  WorkPool pool;
-  int pi = 0, pj = 0, k = 0, k_end = 0;
-  bool finished = false, need_new = true;
-  bool walking = false;  // a query of this lane is in progress
-  bool pending = false;  // ... or has ended and its hit has not been shaded yet
-  PathKey pk;
-  pk.pixel = 0;
-  pk.sample = 0;
-  pk.k0 = a.k0;
-  pk.k1 = a.k1;
-  V3 T = mk(1.f, 1.f, 1.f);
-  RayQ ray;
-  ray.o = ray.d = mk(0.f, 0.f, 0.f);
-  int depth = 0;
-  // the query (world_hit_bvh_ifif's locals)
-  Range rg;
-  rg.t_from = 1e-3;
-  rg.t_to = (double)CUDART_INF_F;
-  rg.tf_f = float_ge(1e-3);
-  rg.lib_pow = s.sphere_pow != 0;
-  const float t_lo = rg.tf_f - fabsf(rg.tf_f) * 1e-5f;
-  Best b;
-  best_init(b, rg.t_to);
-  bool ambiguous = false, overflow = false;
-  float idx = 0.f, idy = 0.f, idz = 0.f, nox = 0.f, noy = 0.f, noz = 0.f;
-  uint32_t ca = 0, cb = 0;
-  int sp = 0;
-  uint32_t n_samples = 0, n_rays = 0, n_rays_ref = 0, n_seq = 0, n_nodes = 0, n_prims = 0;
-  const float4 *__restrict__ nodes = s.nodes;
-  for (;;) {
-    // the lanes between two queries are served together: when `stream_thr` of them wait, or nobody walks any more
-    const unsigned waiting = __ballot_sync(FULL, !walking && !finished), walkers = __ballot_sync(FULL, walking);
-    if (waiting == 0u && walkers == 0u) break;
-    const bool serve = __popc(waiting) >= a.stream_thr || walkers == 0u;
-    if (serve) hand_out(a, pool, !finished && !walking && !pending && need_new && k >= k_end, finished, pi, pj, k, k_end, pk.pixel);
-    if (serve && !walking && !finished) {
-      // ---- between two queries of this lane: shade the hit, scatter or start the next sample, begin the next query
-      if (pending) {
-        pending = false;
-        resolve_quad_order(s, b, ambiguous);
-        finalize_sphere_hit<SPH, false>(s, ray, rg, b, ambiguous);
-        Hit h;
-        if (ambiguous || overflow) {
-          h = world_hit_seq(s, ray, rg.t_from, rg.t_to);
-        } else {
-          h.t = b.rec == REC_NONE ? 0.0 : b.t;
-          h.rec = b.rec;
-          h.seq = 0;
-          h.box = -1;
-        }
-        n_rays++;
-        n_seq += (uint32_t)h.seq;
-        bool alive = false;
-        if (h.rec != REC_NONE) {
-          PhiloxCache pc;
-          pc.block = PHILOX_NO_BLOCK;
-          pc.w2 = pc.w3 = 0;
-          ShadeRet sr = shade_hit_call<SPH>(s, cam, ray, h, pk, depth, pc, T);
-          alive = sr.alive;
-          ray = sr.ray;
-          T = sr.T;
-          if (!alive) add_radiance(a.fixed, (int)pk.pixel, sr.L);
-        }
-        if (alive) {
-          depth++;
-        } else {
-          k++;
-          need_new = true;
-        }
-      }
-      if (need_new && k < k_end) {
-        pk.sample = (uint32_t)k;
-        ray = camera_sample_call(cam, pi, pj, a.height, a.width, pk).ray;
-        T = mk(1.f, 1.f, 1.f);
-        depth = 0;
-        need_new = false;
-        n_samples++;
-      }
-      if (!need_new) {
-        n_rays_ref++;
-        if (depth < a.max_depth) {  // ray_tracing.cu:23: the query at depth == limit yields 0
-          best_init(b, rg.t_to);
-          if (s.sky_obj >= 0) {  // sky.cu:18-27: always a candidate at t = 1e9
-            b.t = 1e9;
-            b.t_f = 1e9f;
-            b.rec = REC_SKY;
-            b.obj = s.sky_obj;
-            b.sub = 0;
-          }
-          ambiguous = overflow = false;
-          idx = slab_rcp(ray.d.x), idy = slab_rcp(ray.d.y), idz = slab_rcp(ray.d.z);
-          nox = -(ray.o.x * idx), noy = -(ray.o.y * idy), noz = -(ray.o.z * idz);
-          ca = s.root_a, cb = s.root_b;
-          sp = 0;
-          pending = true;
-          walking = s.n_recs > 0;
-        } else {
-          k++;
-          need_new = true;
-        }
-      }
-    }
-    if (walking) {
-      // ---- one step of world_hit_bvh_ifif
-      bool pop = true;
-      if (cb & LEAF_FLAG) {
-        int q = (int)ca;
-        const int end = (int)(ca + (cb & ~LEAF_FLAG));
-        while (q < end) {
-          const int used = rec_test<SPH>(s.recs, q, ray, rg, b, ambiguous);
-          if (STATS) n_prims += used;
-          q += used;
-        }
-      } else {
-        if (STATS) n_nodes += 2;
-        const float4 l0 = __ldg(nodes + 2 * (size_t)ca), l1 = __ldg(nodes + 2 * (size_t)ca + 1);
-        const float4 r0 = __ldg(nodes + 2 * (size_t)cb), r1 = __ldg(nodes + 2 * (size_t)cb + 1);
-        const float t_hi = b.t_f + fabsf(b.t_f) * 1e-5f;
-        float ln, lf, rn, rf;
-        slab2(l0, l1, r0, r1, idx, idy, idz, nox, noy, noz, t_lo, t_hi, ln, lf, rn, rf);
-        const bool hl = ln <= lf * 1.00001f, hr = rn <= rf * 1.00001f;
-        const uint32_t la = __float_as_uint(l0.w), lb = __float_as_uint(l1.w);
-        const uint32_t ra = __float_as_uint(r0.w), rb = __float_as_uint(r1.w);
-        if (hl | hr) {
-          const bool left_first = hl & (!hr | (ln <= rn));
-          if (hl & hr) {
-            if (sp < STACK_SIZE) {
-              const uint2 e = left_first ? make_uint2(ra, rb) : make_uint2(la, lb);
-              if (sp < SM_LEVELS)
-                sm[sp * 128] = e;
-              else
-                lstack[sp - SM_LEVELS] = e;
-              sp++;
-            } else {
-              overflow = true;
-            }
-          }
-          ca = left_first ? la : ra;
-          cb = left_first ? lb : rb;
-          pop = false;
-        }
-      }
-      if (pop) {
-        if (sp == 0) {
-          walking = false;
-        } else {
-          --sp;
-          const uint2 e = sp < SM_LEVELS ? sm[sp * 128] : lstack[sp - SM_LEVELS];
-          ca = e.x;
-          cb = e.y;
-        }
-      }
-    }
-  }
-  flush_counters(ctr, n_samples, n_rays, n_rays_ref, n_nodes, n_prims, n_seq, 0u);
 }
 
 // ---- wavefront pipeline ------------------------------------------------------------------------------
@@ -893,17 +708,18 @@ int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
 }  // namespace
 
 // Traversal of the render kernel, chosen at commit (RT_TRAV overrides it for diagnostics, read once per commit).
-// Measured in round 1 (profiles/r01_h_variants_sweep.txt, r01_o_wide_ifif_sweep.txt, r01_v_box_list_sweep.txt):
 //   <= 32 primitives (Cornell, birthday): no tree — box list, every lane tests every box (rt_flat.cuh);
 //   <= 4096 records (spheres): binary tree, while-while loop — incoherent bounce rays in an L1-resident tree;
-//   meshes up to 500 k records (bunny): 8-wide tree, if-if loop — 1-2 dependent steps instead of 6;
-//   larger (soups): binary tree, if-if loop at 64 registers — latency bound, 32 warps/SM beat fewer, fatter steps.
+//   larger (bunny, soups): binary tree, if-if loop at 64 registers with the first stack levels in shared memory.
+// Round 1 also kept an 8-wide tree for 4 k - 500 k records (bunny +13 % over the binary if-if loop of the time); with
+// the shared-memory stack the binary loop is level with it (bunny 10 208 vs 9 956 Msamples/s,
+// profiles/r02_opq_large_scene_experiments.txt) and the wide tree, its builder and its kernel are gone.
 int rtc::default_trav(const rt_ctx *ctx) {
-  int dflt = ctx->scene.n_recs <= 4096 ? 1 : (ctx->scene.n_recs < 500000 ? 17 : 0);
+  int dflt = ctx->scene.n_recs <= 4096 ? 1 : 0;
   if (ctx->flat.n > 0) dflt = 20;
   const char *e = getenv("RT_TRAV");
   int v = e ? atoi(e) : dflt;
-  if (v != 0 && v != 1 && v != 17 && v != 20) v = dflt;
+  if (v != 0 && v != 1 && v != 20) v = dflt;
   if (v == 20 && ctx->flat.n == 0) v = dflt;
   return v;
 }
@@ -913,8 +729,7 @@ static int mode_to_trav(const rt_ctx *ctx, int mode) {
     case 0: return ctx->trav;
     case 2: return 0;
     case 3: return 1;
-    case 4: return 17;
-    case 5: return 20;
+    case 4: return 20;
     default: return -1;  // 1: sequential scan
   }
 }
@@ -923,7 +738,7 @@ extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t
                                        rt_hit *d_hits, void *stream) {
   int rc = check_ready(ctx, false, "rt_trace_closest");
   if (rc) return rc;
-  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 5)) {
+  if (n < 0 || (n > 0 && (!d_rays || !d_hits)) || (mode < 0 || mode > 4)) {
     set_error("rt_trace_closest: bad argument");
     return RT_ERR_INVALID;
   }
@@ -931,14 +746,10 @@ extern "C" int rt_trace_closest_device(rt_ctx *ctx, const float *d_rays, int64_t
   RT_CUDA(cudaSetDevice(ctx->device));
   const int trav = mode_to_trav(ctx, mode);
   if (trav == 20 && ctx->flat.n == 0 && ctx->scene.n_recs > 0) {
-    set_error("rt_trace_closest: mode 5 (box list) needs a scene of at most 32 primitives");
+    set_error("rt_trace_closest: mode 4 (box list) needs a scene of at most 32 primitives");
     return RT_ERR_INVALID;
   }
-  if (trav == 17) {
-    rc = ensure_wide_tree(ctx, (cudaStream_t)stream);
-    if (rc) return rc;
-  }
-  const int kmode = trav < 0 ? 1 : (trav == 0 ? 2 : (trav == 1 ? 3 : (trav == 17 ? 4 : 5)));
+  const int kmode = trav < 0 ? 1 : (trav == 0 ? 2 : (trav == 1 ? 3 : 4));
   k_trace_closest<<<nblk((size_t)n, 128), 128, 0, (cudaStream_t)stream>>>(ctx->scene, ctx->flat, d_rays, n, t_from, t_to,
                                                                           kmode, d_hits);
   RT_CUDA(cudaGetLastError());
@@ -1127,11 +938,10 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
   if (record_begin) RT_CUDA(cudaEventRecord(ctx->ev0, st));
   if (p->spp_count > 0 && fused) {
     const int trav = ctx->trav;
-    // resident blocks per SM the kernel is compiled for (register budget): 6 (80 registers) for cache-resident
-    // scenes, 5 for the 8-wide tree, 8 (64 registers) from 500 k records up, where the loop is latency bound
-    const int minb = trav == 0 ? (ctx->opt_stream ? RT_STREAM_MINB : 8) : (trav == 17 ? 5 : 6);
+    // resident blocks per SM the kernel is compiled for (register budget): 6 (80 registers) for the cache-resident
+    // scenes (box list, while-while), 8 (64 registers) for the if-if loop of large scenes, which is latency bound
+    const int minb = trav == 0 ? 8 : 6;
     plan_work(ctx, a, minb, trav == 20);
-    a.stream_thr = ctx->stream_thr;
     const int grid = ctx->n_sm * minb;
 #define RT_LAUNCH(T, M, ...)                                                                             \
   if (stats_on && sph)                                                                                   \
@@ -1145,19 +955,8 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
     const bool sph = ctx->scene.has_spheres != 0;  // scenes without a Sphere run kernels without the FP64 test
     if (trav == 20) {
       RT_LAUNCH(20, 6, ctx->flat)
-    } else if (trav == 17) {
-      RT_LAUNCH(17, 5)
     } else if (trav == 1) {
       RT_LAUNCH(1, 6)
-    } else if (ctx->opt_stream) {
-      if (stats_on && sph)
-        k_render_stream<true, true><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr);
-      else if (stats_on)
-        k_render_stream<true, false><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr);
-      else if (sph)
-        k_render_stream<false, true><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr);
-      else
-        k_render_stream<false, false><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr);
     } else {
       RT_LAUNCH(0, 8)
     }

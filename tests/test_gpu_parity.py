@@ -102,12 +102,12 @@ def test_sequential_scan_mode_bit_exact(ctx, name):
 def test_degenerate_directions(ctx, name):
     """Rays with direction components exactly +-0 / denormal / 1e-30 and origins exactly on box planes: the
     slab tests (FFMA form, clamped reciprocal) must never cull a record the reference accepts.  Every
-    traversal (the scene's default, binary if-if / while-while, 8-wide) against the oracle's exhaustive scan."""
+    traversal (the scene's default, binary if-if / while-while) against the oracle's exhaustive scan."""
     s, cam, o = _setup(ctx, name)
     lo, hi = _BOX[name]
     rr = ck.degenerate_rays(40000, 33, lo, hi)
     want = o.trace(rr, quirks=0)
-    for mode in (0, 2, 3, 4):
+    for mode in (0, 2, 3):
         got = ctx.trace_closest(rr, mode=mode)
         bad = ck.hits_equal(got, want, _fields(name))
         assert len(bad) == 0, (mode, len(bad), rr[bad[:3]], got[bad[:3]], want[bad[:3]])
@@ -115,13 +115,13 @@ def test_degenerate_directions(ctx, name):
 
 @pytest.mark.parametrize("name", ["cornell_box", "spheres", "bunny9k", "soup100k"])
 def test_traversal_variants_identical(ctx, name):
-    """Every traversal of the render kernel (mode 2 binary if-if, 3 binary while-while, 4 8-wide tree; the box list
-    has its own test) returns the oracle's hits."""
+    """Every tree traversal of the render kernel (mode 2 binary if-if, 3 binary while-while; the box list has its own
+    test) returns the oracle's hits."""
     s, cam, o = _setup(ctx, name)
     lo, hi = _BOX[name]
     rr = np.concatenate([ctx.primary_rays(54, 96), ck.random_rays(30000, 21, lo, hi)])
     want = o.trace(rr, quirks=0)
-    for mode in (2, 3, 4):
+    for mode in (2, 3):
         got = ctx.trace_closest(rr, mode=mode)
         bad = ck.hits_equal(got, want, _fields(name))
         assert len(bad) == 0, (mode, len(bad), got[bad[:3]], want[bad[:3]])
@@ -129,7 +129,7 @@ def test_traversal_variants_identical(ctx, name):
 
 @pytest.mark.parametrize("name", ["cornell_box", "birthday", "mixed30"])
 def test_box_list_traversal(ctx, name):
-    """Mode 5: the box-list traversal of scenes with at most 32 primitives (every box tested by every lane, nearest
+    """Mode 4: the box-list traversal of scenes with at most 32 primitives (every box tested by every lane, nearest
     box first, the rest re-tested against the closest hit) returns the oracle's hits on random, primary and
     degenerate rays; larger scenes refuse the mode."""
     if name == "mixed30":
@@ -158,17 +158,17 @@ def test_box_list_traversal(ctx, name):
         rr = np.concatenate([ctx.primary_rays(54, 96), ck.random_rays(40000, 5, lo, hi)])
     rr = np.concatenate([rr, ck.degenerate_rays(20000, 34, lo, hi)])
     want = o.trace(rr, quirks=0)
-    got = ctx.trace_closest(rr, mode=5)
+    got = ctx.trace_closest(rr, mode=4)
     bad = ck.hits_equal(got, want, fields)
     assert len(bad) == 0, (len(bad), rr[bad[:3]], got[bad[:3]], want[bad[:3]])
     # ranges other than the render default
     for rng_ in ((0.0, 1e9), (1e-3, 300.0)):
-        got = ctx.trace_closest(rr[:20000], *rng_, mode=5)
+        got = ctx.trace_closest(rr[:20000], *rng_, mode=4)
         assert len(ck.hits_equal(got, o.trace(rr[:20000], *rng_, quirks=0), fields)) == 0, rng_
     # a scene with more than 32 primitives has no box list
     _setup(ctx, "spheres")
     with pytest.raises(Exception):
-        ctx.trace_closest(rr[:10], mode=5)
+        ctx.trace_closest(rr[:10], mode=4)
 
 
 def test_mixed_scene_all_primitive_types(ctx):
@@ -264,13 +264,13 @@ def test_render_bit_exact_vs_oracle(ctx, name, hw, spp):
 @pytest.mark.parametrize("name,hw,spp", [("cornell_box", (72, 128), 8), ("spheres", (54, 96), 8), ("bunny9k", (54, 96), 4)])
 def test_render_kernel_variants_bit_exact(ctx, name, hw, spp, monkeypatch):
     """Every traversal the render kernel is compiled for (RT_TRAV, read at commit: 0 binary if-if at 64 registers,
-    1 binary while-while, 17 8-wide tree, 20 box list where the scene has one) renders the oracle's image."""
+    1 binary while-while, 20 box list where the scene has one) renders the oracle's image."""
     s, cam = _named(name)
     camera = rt.core.camera_look_at(cam)
     o = ck.OracleScene(s, camera)
     H, W = hw
     want, cnt = o.render_product(H, W, 0, spp, 99)
-    for trav in (0, 1, 17, 20):
+    for trav in (0, 1, 20):
         monkeypatch.setenv("RT_TRAV", str(trav))
         ctx.commit(s)
         ctx.set_camera(camera)
@@ -327,10 +327,10 @@ def test_max_depth_and_resolve(ctx):
         assert np.abs(rgb - ref_rgb).max() <= 1e-6
 
 
-def test_wide_tree_full_size(ctx):
-    """A 1 M-triangle soup (the oracle would need minutes): the 8-wide tree and the binary while-while loop return
-    exactly the hits of the binary if-if loop on 400 k primary and random rays, and on rays scaled far away from the
-    scene box."""
+def test_traversals_agree_at_full_size(ctx):
+    """A 1 M-triangle soup (the oracle would need minutes): the binary while-while loop returns exactly the hits of the
+    binary if-if loop (shared-memory stack, the product path at this size) on 400 k primary and random rays, and on rays
+    scaled far away from the scene box."""
     s, cam = scenes.soup(1000000)
     ctx.commit(s)
     ctx.set_camera(rt.core.camera_look_at(cam))
@@ -340,7 +340,7 @@ def test_wide_tree_full_size(ctx):
     rr = np.concatenate([rr, far])
     want = ctx.trace_closest(rr, mode=2)
     assert (want["obj"] >= 0).mean() > 0.3
-    for mode in (3, 4):
+    for mode in (3, 0):
         got = ctx.trace_closest(rr, mode=mode)
         bad = ck.hits_equal(got, want)
         assert len(bad) == 0, (mode, len(bad), rr[bad[:3]], got[bad[:3]], want[bad[:3]])
@@ -404,7 +404,7 @@ def test_rays_through_a_parallelogram_diagonal(ctx):
         ctx.commit(s)
         o = ck.OracleScene(s)
         want = o.trace(rays, quirks=0)
-        for mode in (0, 1, 2, 3, 4) + ((5,) if name != "with_mesh" else ()):
+        for mode in (0, 1, 2, 3) + ((4,) if name != "with_mesh" else ()):
             got = ctx.trace_closest(rays, mode=mode)
             bad = ck.hits_equal(got, want, ("t", "obj", "sub", "normal", "material"))
             assert len(bad) == 0, (name, mode, len(bad), rays[bad[:2]], got[bad[:2]], want[bad[:2]])

@@ -15,7 +15,7 @@ for name, hw in (("spheres", (27, 48)), ("bunny9k", (27, 48))):
     scene, cam = (rt.scenes.spheres(10086, "rtl")[:2] if name == "spheres" else rt.scenes.bunny(rt.scenes.bunny_mesh(9000)))
     ctx.commit(scene); ctx.set_camera(rt.core.camera_look_at(cam))
     rays = ctx.primary_rays(*hw)
-    for mode in (0, 1, 2, 3, 4):
+    for mode in (0, 1, 2, 3):
         ctx.trace_closest(rays, mode=mode)
     for flags in (rt.abi.RT_RENDER_FUSED, rt.abi.RT_RENDER_WAVEFRONT, rt.abi.RT_RENDER_WAVEFRONT | rt.abi.RT_RENDER_SORT,
                   rt.abi.RT_RENDER_FUSED | rt.abi.RT_RENDER_PROFILE):
