@@ -508,7 +508,9 @@ class Runner:
                        "d2h_bytes_per_step": H * W * 12},
                "gpu_launches": int(st.kernel_launches * steps),
                "roofline": roofline, "clocks": clocks,
-               "build": {"ms": build.build_ms, "max_depth": build.max_depth, "sah": build.sah_cost}}
+               "build": {"ms": build.build_ms, "max_depth": build.max_depth, "sah": build.sah_cost,
+                         "tree": "ploc" if build.reserved0_ > 0 else "lbvh", "ploc_rounds": abs(build.reserved0_),
+                         "sah_other_tree": float(np.array([build.reserved1_], np.int32).view(np.float32)[0]) if build.reserved0_ else None}}
         if baselines and is_soup:
             out["cpu_baseline"] = {"unavailable": "the host reference build scans meshes with 2048-triangle leaves (bvh.cuh:71-98): "
                                                   "no bounded sample of a 1M+ triangle frame finishes in the bench budget"}

@@ -136,8 +136,10 @@ typedef struct rt_build_stats {
   int32_t max_depth;
   float build_ms;       /* device time of the BVH build (CUDA events) */
   float upload_ms;
-  float sah_cost;
-  int32_t reserved_[2];
+  float sah_cost;       /* of the tree the traversal walks */
+  int32_t reserved_[2]; /* large scenes build two trees and keep the one of lower SAH cost: [0] > 0: PLOC rounds, the
+                           clustered tree was kept; < 0: it was built and rejected; 0: not tried.  [1] float bits of the
+                           SAH cost of the tree that was NOT kept */
 } rt_build_stats;
 
 typedef struct rt_render_stats {

@@ -63,7 +63,7 @@ extern "C" int rt_ctx_destroy(rt_ctx *c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   rt_nccl_destroy(c);  // a caller that forgot it does not leak the communicator
-  DevBuf *bufs[] = {&c->nodes, &c->recs, &c->recs_seq, &c->face_uv, &c->face_uv_seq, &c->mats, &c->textures,
+  DevBuf *bufs[] = {&c->nodes, &c->nodes_ploc, &c->recs, &c->recs_seq, &c->face_uv, &c->face_uv_seq, &c->mats, &c->textures,
                     &c->tex_pixels, &c->counters, &c->accum_tmp, &c->fixed_tmp, &c->rgb_tmp, &c->rgb8_tmp, &c->rays_tmp,
                     &c->hits_tmp};
   for (DevBuf *b : bufs) b->release();

@@ -65,7 +65,7 @@ struct rt_ctx {
   rtc::FlatItems flat{};  // box list of scenes with <= FLAT_MAX primitives (flat.n = 0: none)
   rt_camera camera_host{};
   // scene storage
-  rtc::DevBuf nodes, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;
+  rtc::DevBuf nodes, nodes_ploc, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;
   std::vector<void *> tex_allocs;
   // build scratch
   rtc::DevBuf scratch[12];
