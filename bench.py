@@ -25,6 +25,7 @@ import sys
 import tempfile
 import threading
 import time
+import zlib
 
 import numpy as np
 
@@ -344,6 +345,13 @@ def pow_kat():
         return {"error": repr(e)[:160]}
 
 
+class DeviceArray:
+    """A raw device address as something torch.as_tensor can wrap without a copy."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
 class Runner:
     """One context per process; benches one workload at a time."""
 
@@ -416,20 +424,34 @@ class Runner:
         rgb = torch.zeros(H, W, 3, device=self.dev)
         rgb_host = torch.zeros(H, W, 3).pin_memory()
         CLEAR = rt.abi.RT_RENDER_CLEAR
+        # N > 1: the sums of all ranks are added, resolved and gathered at rank 0 by one kernel per rank over NVLink
+        # peer memory (rt_reduce_resolve_peers; --reduce nccl = one ncclReduce of the sums + a resolve at rank 0).
+        peers = world > 1 and args.reduce == "peers"
+        sums_ptr = sums.data_ptr()
+        if peers:
+            sums_ptr, _, rgb_ptr = self.rdist.open_peer_frame(ctx, H, W)
+            rgb = torch.as_tensor(DeviceArray(rgb_ptr, (H, W, 3), "<f4"), device=self.dev)
+
+        def reduce_to_root(resolve):
+            if peers:
+                ctx.reduce_resolve_peers(spp, 0, sp)
+            else:
+                if world > 1:
+                    ctx.reduce_fixed(None, sums_ptr, H * W * 3, 0, sp)
+                if resolve and rank == 0:
+                    ctx.resolve_fixed_device(sums_ptr, H, W, spp, None, rgb.data_ptr(), None, sp)
 
         def step_device():
-            ctx.render_fixed_device(sums.data_ptr(), H, W, count, begin, depth, seed=1, flags=flags | CLEAR, stream=sp)
+            ctx.render_fixed_device(sums_ptr, H, W, count, begin, depth, seed=1, flags=flags | CLEAR, stream=sp)
             if world > 1:
-                ctx.reduce_fixed(None, sums.data_ptr(), H * W * 3, 0, sp)
+                reduce_to_root(False)
 
         def step_e2e():
             ctx.commit(scene)  # host description -> device records + BVH (H2D inside)
             ctx.set_camera(camera)
-            ctx.render_fixed_device(sums.data_ptr(), H, W, count, begin, depth, seed=1, flags=flags | CLEAR, stream=sp)
-            if world > 1:
-                ctx.reduce_fixed(None, sums.data_ptr(), H * W * 3, 0, sp)
+            ctx.render_fixed_device(sums_ptr, H, W, count, begin, depth, seed=1, flags=flags | CLEAR, stream=sp)
+            reduce_to_root(True)
             if rank == 0:
-                ctx.resolve_fixed_device(sums.data_ptr(), H, W, spp, None, rgb.data_ptr(), None, sp)
                 rgb_host.copy_(rgb, non_blocking=True)
             self.stream.synchronize()
 
@@ -439,11 +461,19 @@ class Runner:
         clocks = self.sampler.region(t0, t1) if rank == 0 else None
         # one more step for ray counts and the kernel-only time, then a stats launch (counters of the same frame at
         # reduced spp: per-ray figures are spp independent)
-        st = ctx.render_fixed_device(sums.data_ptr(), H, W, count, begin, depth, seed=1, flags=flags | CLEAR, stream=sp)
+        st = ctx.render_fixed_device(sums_ptr, H, W, count, begin, depth, seed=1, flags=flags | CLEAR, stream=sp)
         prof_spp = max(1, min(count, 4))
-        st_prof = ctx.render_fixed_device(sums.data_ptr(), H, W, prof_spp, begin, depth, seed=1,
+        st_prof = ctx.render_fixed_device(sums_ptr, H, W, prof_spp, begin, depth, seed=1,
                                           flags=flags | CLEAR | rt.abi.RT_RENDER_PROFILE, stream=sp)
         ms_e2e = self.timed(step_e2e, max(1, min(steps, 3)), 1)
+        if peers:
+            ctx.peer_frame_check(sp)  # raises if a rank timed out inside the reduce
+            image_crc = int(zlib.crc32(rgb_host.numpy().tobytes())) if rank == 0 else 0
+            del rgb
+            self.barrier()
+            ctx.peer_frame_destroy()
+        else:
+            image_crc = int(zlib.crc32(rgb_host.numpy().tobytes())) if rank == 0 else 0
         rays = torch.tensor([float(st.rays), float(st.rays_ref_equiv)], device=self.dev, dtype=torch.float64)
         if world > 1:
             self.dist.all_reduce(rays)
@@ -499,6 +529,9 @@ class Runner:
                "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                "dtype": "f32", "data": "synthetic",
                "config": {"workload": label, "partition": f"spp/{world}",
+                          "reduce": ("nvlink peer frames, one kernel per rank (sum + resolve + gather)" if peers else
+                                     "ncclReduce int64 + resolve at rank 0") if world > 1 else None,
+                          "image_crc32": image_crc,
                           "l2": "flushed between timed steps (256 MiB write)", "strategy": args.strategy,
                           "prims": build.n_prims, "nodes": build.n_nodes,
                           "chunk_samples": int(st.chunk_samples), "work_items": int(st.work_items)},
@@ -506,7 +539,7 @@ class Runner:
                "rays_per_sample": float(rays[0].item()) / samples, "frame_ms": ms,
                "e2e": {"value": samples / ms_e2e / 1e3, "unit": "Msamples/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
                        "d2h_bytes_per_step": H * W * 12},
-               "gpu_launches": int(st.kernel_launches * steps),
+               "gpu_launches": int((st.kernel_launches + (3 if peers else 0)) * steps),
                "roofline": roofline, "clocks": clocks,
                "build": {"ms": build.build_ms, "max_depth": build.max_depth, "sah": build.sah_cost,
                          "tree": "ploc" if build.reserved0_ > 0 else "lbvh", "ploc_rounds": abs(build.reserved0_),
@@ -534,6 +567,8 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override spp (diagnostic; the headline uses the config's)")
     ap.add_argument("--depth", type=int, default=0, help="override the bounce limit (diagnostic)")
     ap.add_argument("--strategy", default="auto", choices=["auto", "fused", "wavefront", "wavefront_raysort"])
+    ap.add_argument("--reduce", default="peers", choices=["peers", "nccl"],
+                    help="N > 1: one kernel over NVLink peer frames (default) or ncclReduce + resolve at rank 0")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)

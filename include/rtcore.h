@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 3
+#define RT_ABI_VERSION 4
 
 enum {
   RT_OK = 0,
@@ -288,6 +288,31 @@ int rt_reduce_fixed(rt_ctx *ctx, void *nccl_comm, int64_t *d_accum_fixed, int64_
 int rt_nccl_unique_id(char out_id[128]);
 int rt_nccl_init(rt_ctx *ctx, const char id[128], int world_size, int rank);
 int rt_nccl_destroy(rt_ctx *ctx);
+
+/* ---- The reduce as one kernel over NVLink peer memory (no NCCL call) -------------------------------------------
+ * Replaces D2H + MPI_Reduce + the host post-processing loop of GatherImageData (utils.cu:115-130, 232-241) for
+ * ranks that are processes of ONE node.  Each rank owns a "peer frame" (exact sums | float sums | resolved image)
+ * that the other ranks map through CUDA IPC; after its render, rank r sums slice r of the image over the frames of
+ * all ranks, resolves it and stores it into the root's frame.  The root's image is the one-GPU image bit for bit.
+ *
+ *   rank r:  rt_peer_frame_create(ctx, H, W, handle_r)          -> 64-byte handle, shipped to the other ranks by the
+ *            rt_peer_frame_open(ctx, world, r, handles)            caller's own plumbing (file, MPI, torch.distributed)
+ *            rt_peer_frame_buffers(ctx, &sums, &accum, &rgb)
+ *   frame:   rt_render_fixed(ctx, &params(RT_RENDER_CLEAR), sums, ...)      every rank, its own sample range
+ *            rt_reduce_resolve_peers(ctx, spp_total, root, stream)           every rank, same stream as the render
+ *            root: accum / rgb of ITS frame now hold the whole image (stream-ordered)
+ * Every rank must call rt_reduce_resolve_peers the same number of times.  A rank that does not arrive within
+ * RT_PEER_TIMEOUT_MS (environment, default 5000) makes rt_peer_frame_check return RT_ERR_CUDA on the ranks that
+ * waited for it; nothing hangs.  world_size 1 is allowed (no handle is opened; the call is a plain resolve). */
+#define RT_PEER_HANDLE_BYTES 64
+int rt_peer_frame_create(rt_ctx *ctx, int height, int width, char out_handle[RT_PEER_HANDLE_BYTES]);
+int rt_peer_frame_open(rt_ctx *ctx, int world_size, int rank, const char (*handles)[RT_PEER_HANDLE_BYTES]);
+int rt_peer_frame_buffers(rt_ctx *ctx, int64_t **d_accum_fixed /*nullable*/, float **d_accum_rgb /*nullable*/,
+                          float **d_rgb /*nullable*/);
+int rt_reduce_resolve_peers(rt_ctx *ctx, int spp_total, int root, void *stream);
+/* Synchronises `stream`; RT_ERR_CUDA if a wait of rt_reduce_resolve_peers timed out since the last check. */
+int rt_peer_frame_check(rt_ctx *ctx, void *stream);
+int rt_peer_frame_destroy(rt_ctx *ctx);
 
 /* Image writers replacing stbi_write_jpg in WriteImage (utils.cu:87-96). */
 int rt_write_jpeg(const char *path, int width, int height, const uint8_t *h_rgb8, int quality);

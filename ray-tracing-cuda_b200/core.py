@@ -51,13 +51,19 @@ def lib():
     L.rt_render_host.argtypes = [vp, C.POINTER(abi.RtRenderParams), vp, vp, C.POINTER(abi.RtRenderStats)]
     L.rt_get_workload.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]
     L.rt_reduce.argtypes = [vp, vp, vp, i64, C.c_int, vp]
+    L.rt_peer_frame_create.argtypes = [vp, C.c_int, C.c_int, vp]
+    L.rt_peer_frame_open.argtypes = [vp, C.c_int, C.c_int, vp]
+    L.rt_peer_frame_buffers.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    L.rt_reduce_resolve_peers.argtypes = [vp, C.c_int, C.c_int, vp]
+    L.rt_peer_frame_check.argtypes = [vp, vp]
+    L.rt_peer_frame_destroy.argtypes = [vp]
     L.rt_nccl_unique_id.argtypes = [vp]
     L.rt_nccl_init.argtypes = [vp, vp, C.c_int, C.c_int]
     L.rt_nccl_destroy.argtypes = [vp]
     L.rt_write_jpeg.argtypes = [C.c_char_p, C.c_int, C.c_int, vp, C.c_int]
     L.rt_write_ppm.argtypes = [C.c_char_p, C.c_int, C.c_int, vp]
     L.rt_write_pfm.argtypes = [C.c_char_p, C.c_int, C.c_int, vp]
-    if L.rt_abi_version() != 3:
+    if L.rt_abi_version() != 4:
         raise RtError("librtcore.so ABI version mismatch")
     _lib = L
     return L
@@ -166,6 +172,33 @@ class Context:
 
     def reduce(self, nccl_comm, d_accum_ptr, n_floats, root=0, stream=None):
         _check(lib().rt_reduce(self._h, nccl_comm, d_accum_ptr, n_floats, root, stream))
+
+    # ---- the reduce over NVLink peer memory (rt_peer.cu; replaces utils.cu:115-130, 232-241 without NCCL) ----
+    def peer_frame_create(self, height, width):
+        """Allocate this rank's frame; returns the 64-byte CUDA IPC handle the other ranks open."""
+        buf = C.create_string_buffer(64)
+        _check(lib().rt_peer_frame_create(self._h, height, width, buf))
+        return buf.raw
+
+    def peer_frame_open(self, world_size, rank, handles):
+        """handles: the 64-byte handle of every rank, in rank order (own entry is not opened)."""
+        blob = C.create_string_buffer(b"".join(bytes(h) for h in handles), 64 * world_size) if world_size > 1 else None
+        _check(lib().rt_peer_frame_open(self._h, world_size, rank, blob))
+
+    def peer_frame_buffers(self):
+        """Device addresses (exact sums int64, float sums, resolved image) of THIS rank's frame."""
+        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        _check(lib().rt_peer_frame_buffers(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def reduce_resolve_peers(self, spp_total, root=0, stream=None):
+        _check(lib().rt_reduce_resolve_peers(self._h, spp_total, root, stream))
+
+    def peer_frame_check(self, stream=None):
+        _check(lib().rt_peer_frame_check(self._h, stream))
+
+    def peer_frame_destroy(self):
+        lib().rt_peer_frame_destroy(self._h)
 
     def nccl_init(self, unique_id, world_size, rank):
         """Bind an NCCL communicator to this context from a 128-byte ncclUniqueId (see nccl_unique_id)."""

@@ -24,6 +24,7 @@ extern "C" const char *rt_last_error_string(void) { return g_err.c_str(); }
 
 extern "C" int rt_ctx_destroy(rt_ctx *c);
 extern "C" int rt_nccl_destroy(rt_ctx *ctx);
+extern "C" int rt_peer_frame_destroy(rt_ctx *ctx);
 
 extern "C" int rt_ctx_create(int device, rt_ctx **out) {
   if (!out) {
@@ -63,6 +64,7 @@ extern "C" int rt_ctx_destroy(rt_ctx *c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   rt_nccl_destroy(c);  // a caller that forgot it does not leak the communicator
+  rt_peer_frame_destroy(c);
   DevBuf *bufs[] = {&c->nodes, &c->nodes_ploc, &c->recs, &c->recs_seq, &c->face_uv, &c->face_uv_seq, &c->mats, &c->textures,
                     &c->tex_pixels, &c->counters, &c->accum_tmp, &c->fixed_tmp, &c->rgb_tmp, &c->rgb8_tmp, &c->rays_tmp,
                     &c->hits_tmp};

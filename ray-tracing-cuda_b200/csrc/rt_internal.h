@@ -78,4 +78,6 @@ struct rt_ctx {
   rt_build_stats build_stats{};
   // nccl (loaded lazily)
   void *nccl_comm = nullptr;
+  // peer frame of the NVLink reduce (rt_peer.cu)
+  void *peer = nullptr;
 };

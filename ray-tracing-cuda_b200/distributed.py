@@ -6,9 +6,10 @@ are added at the root.  Differences by design:
   * rank r renders the GLOBAL sample indices [begin_r, begin_r + count_r) — the Philox key is
     (pixel, global sample, bounce), so N ranks compute the same estimator as one (the reference
     seeds every rank identically and renders duplicates);
-  * the reduce is one ncclReduce on the device accumulation buffer over NVLink (rt_reduce), not a
-    D2H copy + host MPI_Reduce (utils.cu:124,232-238).
-torch.distributed is plumbing only: rendezvous, the 128-byte ncclUniqueId broadcast, barriers.
+  * the reduce runs on the device over NVLink, not as a D2H copy + host MPI_Reduce (utils.cu:124,232-238):
+    one kernel per rank over CUDA-IPC peer frames that sums, resolves and gathers (open_peer_frame +
+    rt_reduce_resolve_peers, the default), or one ncclReduce of the exact sums (bind_nccl + rt_reduce_fixed).
+torch.distributed is plumbing only: rendezvous, the handle / ncclUniqueId exchange, barriers.
 """
 import os
 
@@ -65,6 +66,18 @@ def bind_nccl(ctx):
     uid = core.nccl_unique_id() if rank == 0 else b"\0" * 128
     uid = broadcast_bytes(uid, 128, 0)
     ctx.nccl_init(uid, world, rank)
+
+
+def open_peer_frame(ctx, height, width):
+    """Every rank allocates its frame, the 64-byte IPC handles travel over the default process group, every rank maps
+    the others (rt_peer.cu).  Returns the (sums, accum, rgb) device addresses of this rank's frame."""
+    import torch.distributed as dist
+
+    rank, world = (dist.get_rank(), dist.get_world_size()) if dist.is_available() and dist.is_initialized() else (0, 1)
+    mine = ctx.peer_frame_create(height, width)
+    handles = [broadcast_bytes(mine if rank == r else b"\0" * 64, 64, r) for r in range(world)] if world > 1 else [mine]
+    ctx.peer_frame_open(world, rank, handles)
+    return ctx.peer_frame_buffers()
 
 
 def reduce_on_cpu(local_accum, root=0):

@@ -198,10 +198,58 @@ void BindNccl(rt_ctx *ctx, int rank, int world_size) {
   if (rank == 0) unlink(path.c_str());  // every rank has joined once ncclCommInitRank returns
 }
 
+// Peer frames (rtcore.h, rt_peer_frame_*): every rank publishes the 64-byte CUDA IPC handle of its frame in its own
+// file next to the NCCL one and reads the others'.  Returns the files this rank wrote (removed once the first reduce
+// has shown that every rank has opened every frame).
+struct PeerRecord {
+  char magic[8];
+  int32_t world_size, rank;
+  char handle[RT_PEER_HANDLE_BYTES];
+};
+std::string OpenPeerFrames(rt_ctx *ctx, int rank, int world_size, int height, int width) {
+  std::vector<PeerRecord> recs(world_size);
+  memset(recs.data(), 0, sizeof(PeerRecord) * world_size);
+  PeerRecord &mine = recs[rank];
+  memcpy(mine.magic, "RTPEER01", 8);
+  mine.world_size = world_size;
+  mine.rank = rank;
+  RTAPI_RT(rt_peer_frame_create(ctx, height, width, mine.handle));
+  const std::string base = RendezvousPath() + ".frame";
+  const std::string path = base + std::to_string(rank), tmp = path + ".tmp";
+  unlink(path.c_str());
+  unlink(tmp.c_str());
+  int fd = open(tmp.c_str(), O_CREAT | O_EXCL | O_WRONLY, 0600);
+  CHECK(fd >= 0) << "cannot create " << tmp << ": " << strerror(errno);
+  CHECK(write(fd, &mine, sizeof(mine)) == (ssize_t)sizeof(mine)) << "short write to " << tmp;
+  close(fd);
+  CHECK(rename(tmp.c_str(), path.c_str()) == 0) << "cannot publish " << path;
+  for (int r = 0; r < world_size; r++) {
+    if (r == rank) continue;
+    const std::string other = base + std::to_string(r);
+    bool ok = false;
+    for (int tries = 0; tries < 6000 && !ok; tries++) {
+      int f = open(other.c_str(), O_RDONLY);
+      if (f >= 0) {
+        ok = read(f, &recs[r], sizeof(PeerRecord)) == (ssize_t)sizeof(PeerRecord) &&
+             memcmp(recs[r].magic, "RTPEER01", 8) == 0 && recs[r].world_size == world_size && recs[r].rank == r;
+        close(f);
+      }
+      if (!ok) std::this_thread::sleep_for(std::chrono::milliseconds(10));
+    }
+    CHECK(ok) << "rank " << rank << ": no peer frame of rank " << r << " at " << other << " after 60 s";
+  }
+  std::vector<char> handles((size_t)world_size * RT_PEER_HANDLE_BYTES);
+  for (int r = 0; r < world_size; r++) memcpy(&handles[(size_t)r * RT_PEER_HANDLE_BYTES], recs[r].handle, RT_PEER_HANDLE_BYTES);
+  RTAPI_RT(rt_peer_frame_open(ctx, world_size, rank,
+                              reinterpret_cast<const char(*)[RT_PEER_HANDLE_BYTES]>(handles.data())));
+  return path;
+}
+
 // The part of Main / DistributedMain after init_world: flatten, build, render, (reduce), resolve, write.
 // Both drivers honour the launcher (rtrun -n N, torchrun, mpirun): with N ranks each renders its GetWorkload share of
-// the samples (utils.cu:111-113), the exact sums are reduced to rank 0 (one ncclReduce) and rank 0 writes the image —
-// the same bits as one rank renders alone.  The reference's Main is single-GPU only (utils.cu:132-179); `mpi` tells
+// the samples (utils.cu:111-113), the exact sums are added into rank 0's frame by one kernel per rank over NVLink peer
+// memory (rt_reduce_resolve_peers; RT_REDUCE=nccl: one ncclReduce instead) and rank 0 writes the image — the same
+// bits as one rank renders alone.  The reference's Main is single-GPU only (utils.cu:132-179); `mpi` tells
 // whether the scene itself initialised MPI and bound its device (spheres.cu:83-98) or Main has to.
 void RenderWorld(curandState **d_states, Camera **d_camera, HitableList **d_world, glm::vec3 **d_image,
                  nvstd::function<void(HitableList *, Camera *)> init_world, int height, int width, int spp,
@@ -242,11 +290,20 @@ void RenderWorld(curandState **d_states, Camera **d_camera, HitableList **d_worl
   int spp_begin = 0;
   int local_spp = rt_get_workload(rank, world_size, o.spp, &spp_begin);
   if (distributed || world_size > 1) LOG(INFO) << "[" << rank << " / " << world_size << "] workload: " << local_spp;
-  if (world_size > 1) BindNccl(ctx, rank, world_size);
+  const char *reduce_env = getenv("RT_REDUCE");
+  const bool peers = world_size > 1 && !(reduce_env && strcmp(reduce_env, "nccl") == 0);
+  std::string peer_file;
+  if (world_size > 1 && !peers) BindNccl(ctx, rank, world_size);
 
-  // the accumulation buffer: exact 64-bit sums (rtcore.h, summation contract)
+  // the accumulation buffer: exact 64-bit sums (rtcore.h, summation contract); inside this rank's peer frame when
+  // the ranks reduce over NVLink
   int64_t *d_sums = nullptr;
-  RTAPI_CUDA(cudaMalloc(&d_sums, n * 3 * sizeof(int64_t)));
+  if (peers) {
+    peer_file = OpenPeerFrames(ctx, rank, world_size, o.height, o.width);
+    RTAPI_RT(rt_peer_frame_buffers(ctx, &d_sums, nullptr, nullptr));
+  } else {
+    RTAPI_CUDA(cudaMalloc(&d_sums, n * 3 * sizeof(int64_t)));
+  }
   rt_render_params p;
   p.height = o.height;
   p.width = o.width;
@@ -262,8 +319,14 @@ void RenderWorld(curandState **d_states, Camera **d_camera, HitableList **d_worl
   else
     LOG(INFO) << "Ray tracing finished in " << rs.render_ms << "ms.";
 
-  // utils.cu:124 (MPI_Reduce of host copies) -> one ncclReduce of the device buffer
-  if (world_size > 1) RTAPI_RT(rt_reduce_fixed(ctx, nullptr, d_sums, (int64_t)n * 3, 0, nullptr));
+  // utils.cu:124 (MPI_Reduce of host copies) -> the ranks' sums added into rank 0's frame over NVLink
+  if (peers) {
+    RTAPI_RT(rt_reduce_resolve_peers(ctx, std::max(o.spp, 1), 0, nullptr));
+    RTAPI_RT(rt_peer_frame_check(ctx, nullptr));
+    unlink(peer_file.c_str());  // every rank has opened every frame by now
+  } else if (world_size > 1) {
+    RTAPI_RT(rt_reduce_fixed(ctx, nullptr, d_sums, (int64_t)n * 3, 0, nullptr));
+  }
   float *image = reinterpret_cast<float *>(*d_image);
   if (rank == 0) {
     // ray_tracing.cu:78-83 / utils.cu:126-129 on the device, then WriteImage's *255 truncation.  *d_image is left as
@@ -284,10 +347,12 @@ void RenderWorld(curandState **d_states, Camera **d_camera, HitableList **d_worl
     RTAPI_RT(rt_resolve_fixed(ctx, d_sums, o.height, o.width, std::max(o.spp, 1), image, nullptr, nullptr, nullptr));
   }
   RTAPI_CUDA(cudaDeviceSynchronize());
-  RTAPI_CUDA(cudaFree(d_sums));
+  if (!peers) RTAPI_CUDA(cudaFree(d_sums));
   double total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
   WriteStats(o, rank, world_size, bs, rs, local_spp, total_ms);
-  if (world_size > 1) rt_nccl_destroy(ctx);
+  if (world_size > 1 && !peers) rt_nccl_destroy(ctx);
+  // (peer frames: rt_peer_frame_check returned only after every rank had stored its slice, so nobody reads a frame
+  // another rank is about to free)
   RTAPI_RT(rt_ctx_destroy(ctx));
 }
 

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) >= 20, names
     for n in names:
         assert hasattr(lib, n), f"librtcore.so lacks {n} declared in include/rtcore.h"
-    assert lib.rt_abi_version() == 3
+    assert lib.rt_abi_version() == 4
 
 
 def test_record_sizes_match_header():
