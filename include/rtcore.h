@@ -251,6 +251,19 @@ int rt_render(rt_ctx *ctx, const rt_render_params *params, float *d_accum_rgb,
 int rt_render_fixed(rt_ctx *ctx, const rt_render_params *params, int64_t *d_accum_fixed,
                     rt_render_stats *stats /*nullable*/, void *stream);
 
+/* rt_render for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments and result as rt_render (the same bits in d_accum_rgb), but the call's scratch — the exact int64
+ * sums and the kernel's counters — is a fixed device array inside the library instead of context buffers, so the
+ * call performs no cudaMalloc / cudaFree and synchronises nothing.  Limits: height * width <= RT_STATIC_MAX_PIXELS
+ * (RT_ERR_LIMIT beyond it); path kernel only (RT_RENDER_WAVEFRONT / SORT / RAYSORT / PROFILE: RT_ERR_INVALID); no
+ * stats.  The array (6 MiB) is held by every GPU that loads the library until exit and is shared by ALL calls and
+ * contexts of a device: it is cleared at the start of every call, and two calls that overlap on the GPU (different
+ * streams, or two contexts of one device) race — serialise them.  Scene and camera are committed beforehand (those
+ * calls allocate). */
+#define RT_STATIC_MAX_PIXELS 262144 /* e.g. 512 x 512, 640 x 400 */
+int rt_render_static(rt_ctx *ctx, const rt_render_params *params, float *d_accum_rgb, void *stream);
+
 /* Replaces the post-processing tail of PathTracing (ray_tracing.cu:78-83) and the host loops in
  * GatherImageData / WriteImage (utils.cu:126-129, 87-96): out = sqrt(clamp(accum/spp_total,0,1));
  * either output may be NULL.  d_rgb8 gets trunc(out*255) like WriteImage. */

@@ -45,6 +45,7 @@ def lib():
     L.rt_primary_rays_host.argtypes = [vp, C.c_int, C.c_int, vp]
     L.rt_render.argtypes = [vp, C.POINTER(abi.RtRenderParams), vp, C.POINTER(abi.RtRenderStats), vp]
     L.rt_render_fixed.argtypes = [vp, C.POINTER(abi.RtRenderParams), vp, C.POINTER(abi.RtRenderStats), vp]
+    L.rt_render_static.argtypes = [vp, C.POINTER(abi.RtRenderParams), vp, vp]
     L.rt_resolve.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp]
     L.rt_resolve_fixed.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp]
     L.rt_reduce_fixed.argtypes = [vp, vp, vp, i64, C.c_int, vp]
@@ -158,6 +159,12 @@ class Context:
         st = abi.RtRenderStats()
         _check(lib().rt_render_fixed(self._h, C.byref(p), d_fixed_ptr, C.byref(st), stream))
         return st
+
+    def render_static_device(self, d_accum_ptr, height, width, spp_count, spp_begin=0, max_depth=10, seed=0, flags=0,
+                             stream=None):
+        """rt_render_static: rt_render with its scratch in the library's static device array (no allocation)."""
+        p = self.params(height, width, spp_count, spp_begin, max_depth, seed, flags)
+        _check(lib().rt_render_static(self._h, C.byref(p), d_accum_ptr, stream))
 
     def resolve_fixed_device(self, d_fixed_ptr, height, width, spp_total, d_accum_ptr=None, d_rgb_ptr=None,
                              d_rgb8_ptr=None, stream=None):

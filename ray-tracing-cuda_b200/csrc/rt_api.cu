@@ -45,6 +45,7 @@ extern "C" int rt_ctx_create(int device, rt_ctx **out) {
     return RT_ERR_INVALID;
   }
   RT_CUDA(cudaSetDevice(device));
+  static_scratch_setup(device);  // once per device, with it current (rt_render_static)
   rt_ctx *c = new rt_ctx();
   c->device = device;
   cudaError_t ee = cudaEventCreate(&c->ev0);

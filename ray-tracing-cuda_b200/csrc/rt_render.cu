@@ -1044,6 +1044,103 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *p, float *d_accum_
   return finish_stats(ctx, stats, st, 1);
 }
 
+// ---- rt_render_static: rt_render without any allocation ------------------------------------------------------------
+// The scratch of rt_render (the exact int64 sums of the call + the counters / work counter of the kernel) lives in
+// one file-scope device array instead of the context's cudaMalloc'ed buffers.  Every GPU that loads the library
+// holds the array (6 MiB) until exit.  In host code `g_static_scratch` is only a stand-in for the symbol: the device
+// address comes from cudaGetSymbolAddress, resolved once per device at rt_ctx_create (static_scratch_setup).
+constexpr size_t STATIC_SUMS_BYTES = (size_t)RT_STATIC_MAX_PIXELS * 3 * sizeof(long long);
+constexpr size_t STATIC_CTR_BYTES = 256;  // RenderCounters (64 B) + the work counter, as render_into_fixed lays them out
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SUMS_BYTES + STATIC_CTR_BYTES];
+static_assert(sizeof(RenderCounters) + 64 <= STATIC_CTR_BYTES, "counter block");
+
+namespace {
+constexpr int STATIC_MAX_DEVICES = 64;
+void *g_static_ptr[STATIC_MAX_DEVICES] = {};
+cudaError_t g_static_err[STATIC_MAX_DEVICES] = {};
+bool g_static_done[STATIC_MAX_DEVICES] = {};
+}  // namespace
+
+namespace rtc {
+// Called with `device` current (rt_ctx_create).  A failure is remembered and reported by rt_render_static; it does
+// not fail the context.
+void static_scratch_setup(int device) {
+  if (device < 0 || device >= STATIC_MAX_DEVICES || g_static_done[device]) return;
+  void *ptr = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+  if (e != cudaSuccess) cudaGetLastError();
+  g_static_ptr[device] = e == cudaSuccess ? ptr : nullptr;
+  g_static_err[device] = e;
+  g_static_done[device] = true;
+}
+}  // namespace rtc
+
+extern "C" int rt_render_static(rt_ctx *ctx, const rt_render_params *p, float *d_accum_rgb, void *stream) {
+  int rc = check_params(ctx, p, d_accum_rgb, "rt_render_static");
+  if (rc) return rc;
+  const size_t n = (size_t)p->height * p->width;
+  if (n > (size_t)RT_STATIC_MAX_PIXELS) {
+    set_error("rt_render_static: height * width = " + std::to_string(n) + " exceeds RT_STATIC_MAX_PIXELS = " +
+              std::to_string((long long)RT_STATIC_MAX_PIXELS) + " (the size of the static scratch array); use rt_render");
+    return RT_ERR_LIMIT;
+  }
+  if (p->flags & (RT_RENDER_WAVEFRONT | RT_RENDER_PROFILE | RT_RENDER_SORT | RT_RENDER_RAYSORT)) {
+    set_error("rt_render_static: the wavefront pipeline and the profile counters need allocated buffers; use rt_render");
+    return RT_ERR_INVALID;
+  }
+  const int dev = ctx->device;
+  if (dev < 0 || dev >= STATIC_MAX_DEVICES || !g_static_done[dev] || !g_static_ptr[dev]) {
+    set_error(std::string("rt_render_static: no address for the static scratch array on this device (") +
+              (dev >= 0 && dev < STATIC_MAX_DEVICES && g_static_done[dev] ? cudaGetErrorString(g_static_err[dev])
+                                                                           : "device not set up") + ")");
+    return RT_ERR_CUDA;
+  }
+  RT_CUDA(cudaSetDevice(dev));
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned char *base = static_cast<unsigned char *>(g_static_ptr[dev]);
+  long long *sums = reinterpret_cast<long long *>(base);
+  RenderCounters *ctr = reinterpret_cast<RenderCounters *>(base + STATIC_SUMS_BYTES);
+  // the array keeps the last call's contents: the sums of this call and the counters start at zero
+  RT_CUDA(cudaMemsetAsync(sums, 0, n * 24, st));
+  RT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(RenderCounters) + 64, st));
+  if (p->spp_count > 0) {
+    RenderArgs a;
+    memset(&a, 0, sizeof(a));
+    a.height = p->height;
+    a.width = p->width;
+    a.spp_begin = p->spp_begin;
+    a.spp_end = p->spp_begin + p->spp_count;
+    a.max_depth = p->max_depth;
+    a.k0 = (uint32_t)p->seed;
+    a.k1 = (uint32_t)(p->seed >> 32);
+    a.fixed = sums;
+    a.work_counter = reinterpret_cast<unsigned int *>(ctr + 1);
+    const int trav = ctx->trav;
+    const int minb = trav == 0 ? 8 : 6;
+    plan_work(ctx, a, minb, trav == 20);
+    const int grid = ctx->n_sm * minb;
+    const bool sph = ctx->scene.has_spheres != 0;
+#define RT_LAUNCH_STATIC(T, M, ...)                                                                      \
+  if (sph)                                                                                               \
+    k_render<false, T, M, true><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr, ##__VA_ARGS__);   \
+  else                                                                                                   \
+    k_render<false, T, M, false><<<grid, 128, 0, st>>>(ctx->scene, ctx->camera, a, ctr, ##__VA_ARGS__);
+    if (trav == 20) {
+      RT_LAUNCH_STATIC(20, 6, ctx->flat)
+    } else if (trav == 1) {
+      RT_LAUNCH_STATIC(1, 6)
+    } else {
+      RT_LAUNCH_STATIC(0, 8)
+    }
+#undef RT_LAUNCH_STATIC
+    RT_CUDA(cudaGetLastError());
+  }
+  k_fixed_to_accum<<<nblk(n * 3, 256), 256, 0, st>>>(sums, (int64_t)n * 3, d_accum_rgb,
+                                                     (p->flags & RT_RENDER_CLEAR) ? 1 : 0);
+  RT_CUDA(cudaGetLastError());
+  return RT_OK;
+}
+
 extern "C" int rt_resolve(rt_ctx *ctx, const float *d_accum_rgb, int height, int width, int spp_total, float *d_rgb,
                           uint8_t *d_rgb8, void *stream) {
   if (!ctx || !d_accum_rgb || height <= 0 || width <= 0 || spp_total <= 0) {
