@@ -51,11 +51,16 @@ __global__ void k_face_records(const float *faces, int stride, const uint32_t *p
 }
 
 // ---- build primitives ----------------------------------------------------------------------------
+// Every step of the build is a per-element body d_*(i, ...) with two callers: the grid-wide kernel k_* below it (one
+// launch per step) and k_build_small, which runs ALL steps of a small scene in one block (one launch per commit).
+__device__ __forceinline__ uint32_t d_head_flag(const float4 *recs, int i) {
+  uint32_t kind = __float_as_uint(recs[3 * (size_t)i + 2].w) & KIND_MASK;
+  return (kind == K_TRI || kind == K_QUAD0 || kind == K_SPHERE) ? 1u : 0u;
+}
 __global__ void k_head_flags(const float4 *recs, int n, uint32_t *flags) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  uint32_t kind = __float_as_uint(recs[3 * (size_t)i + 2].w) & KIND_MASK;
-  flags[i] = (kind == K_TRI || kind == K_QUAD0 || kind == K_SPHERE) ? 1u : 0u;
+  flags[i] = d_head_flag(recs, i);
 }
 __global__ void k_scatter_heads(const uint32_t *flags, const uint32_t *pos, int n, uint32_t *bp_first) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -83,10 +88,8 @@ __device__ __forceinline__ void rec_bounds(const float4 *recs, size_t k, V3 &lo,
 }
 
 // Padded box per build primitive + centroid bounds of the scene (ordered-int atomics).
-__global__ void k_bp_bounds(const float4 *recs, const uint32_t *bp_first, int n_bp, float4 *bp_lo, float4 *bp_hi,
-                            uint32_t *scene_bounds) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_bp) return;
+__device__ __forceinline__ void d_bp_bounds(int i, const float4 *recs, const uint32_t *bp_first, float4 *bp_lo,
+                                            float4 *bp_hi, uint32_t *scene_bounds) {
   size_t k = bp_first[i];
   V3 lo = mk(CUDART_INF_F, CUDART_INF_F, CUDART_INF_F), hi = mk(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
   rec_bounds(recs, k, lo, hi);
@@ -113,6 +116,12 @@ __global__ void k_bp_bounds(const float4 *recs, const uint32_t *bp_first, int n_
   atomicMax(scene_bounds + 4, float_orderable(c.y));
   atomicMax(scene_bounds + 5, float_orderable(c.z));
 }
+__global__ void k_bp_bounds(const float4 *recs, const uint32_t *bp_first, int n_bp, float4 *bp_lo, float4 *bp_hi,
+                            uint32_t *scene_bounds) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_bp) return;
+  d_bp_bounds(i, recs, bp_first, bp_lo, bp_hi, scene_bounds);
+}
 
 __device__ __forceinline__ float orderable_float(uint32_t u) {
   return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
@@ -126,10 +135,7 @@ __device__ __forceinline__ uint64_t expand21(uint64_t v) {
   v = (v | v << 2) & 0x1249249249249249ull;
   return v;
 }
-__global__ void k_morton(const float4 *bp_lo, const float4 *bp_hi, int n_bp, const uint32_t *scene_bounds,
-                         uint64_t *keys, uint32_t *vals) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_bp) return;
+__device__ __forceinline__ uint64_t d_morton(int i, const float4 *bp_lo, const float4 *bp_hi, const uint32_t *scene_bounds) {
   float4 lo = bp_lo[i], hi = bp_hi[i];
   float c[3] = {(lo.x + hi.x) * 0.5f, (lo.y + hi.y) * 0.5f, (lo.z + hi.z) * 0.5f};
   uint64_t q[3];
@@ -140,7 +146,13 @@ __global__ void k_morton(const float4 *bp_lo, const float4 *bp_hi, int n_bp, con
     x = fmin(fmax(x * 2097152.0, 0.0), 2097151.0);
     q[a] = (uint64_t)x;
   }
-  keys[i] = expand21(q[0]) << 2 | expand21(q[1]) << 1 | expand21(q[2]);
+  return expand21(q[0]) << 2 | expand21(q[1]) << 1 | expand21(q[2]);
+}
+__global__ void k_morton(const float4 *bp_lo, const float4 *bp_hi, int n_bp, const uint32_t *scene_bounds,
+                         uint64_t *keys, uint32_t *vals) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_bp) return;
+  keys[i] = d_morton(i, bp_lo, bp_hi, scene_bounds);
   vals[i] = i;
 }
 
@@ -151,11 +163,10 @@ __global__ void k_sorted_nrec(const float4 *bp_lo, const uint32_t *order, int n_
 }
 
 // Records copied into BVH (Morton) order; single-primitive leaf nodes written; per-leaf SAH data.
-__global__ void k_emit(const float4 *recs_seq, const float *uv_seq, const uint32_t *bp_first, const float4 *bp_lo,
-                       const float4 *bp_hi, const uint32_t *order, const uint32_t *off, int n_bp, float4 *recs,
-                       float *uv, float4 *nodes, float *cost, int *depth) {
-  int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n_bp) return;
+__device__ __forceinline__ void d_emit(int j, const float4 *recs_seq, const float *uv_seq, const uint32_t *bp_first,
+                                       const float4 *bp_lo, const float4 *bp_hi, const uint32_t *order,
+                                       const uint32_t *off, int n_bp, float4 *recs, float *uv, float4 *nodes,
+                                       float *cost, int *depth) {
   uint32_t bp = order[j];
   size_t src = bp_first[bp];
   uint32_t dst = off[j], n = off[j + 1] - off[j];
@@ -171,6 +182,13 @@ __global__ void k_emit(const float4 *recs_seq, const float *uv_seq, const uint32
   cost[node] = (float)n;
   depth[node] = 1;
 }
+__global__ void k_emit(const float4 *recs_seq, const float *uv_seq, const uint32_t *bp_first, const float4 *bp_lo,
+                       const float4 *bp_hi, const uint32_t *order, const uint32_t *off, int n_bp, float4 *recs,
+                       float *uv, float4 *nodes, float *cost, int *depth) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_bp) return;
+  d_emit(j, recs_seq, uv_seq, bp_first, bp_lo, bp_hi, order, off, n_bp, recs, uv, nodes, cost, depth);
+}
 
 // ---- Karras 2012: one thread per internal node ----------------------------------------------------
 __device__ __forceinline__ int lbvh_delta(const uint64_t *keys, int n, int i, int j) {
@@ -179,10 +197,8 @@ __device__ __forceinline__ int lbvh_delta(const uint64_t *keys, int n, int i, in
   if (a == b) return 64 + __clz(i ^ j);
   return __clzll(a ^ b);
 }
-__global__ void k_hierarchy(const uint64_t *keys, int n, uint32_t *left, uint32_t *right, uint32_t *parent,
-                            uint2 *range) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n - 1) return;
+__device__ __forceinline__ void d_hierarchy(int i, const uint64_t *keys, int n, uint32_t *left, uint32_t *right,
+                                            uint32_t *parent, uint2 *range) {
   int d = lbvh_delta(keys, n, i, i + 1) - lbvh_delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
   int dmin = lbvh_delta(keys, n, i, i - d);
   int lmax = 2;
@@ -208,6 +224,12 @@ __global__ void k_hierarchy(const uint64_t *keys, int n, uint32_t *left, uint32_
   range[i] = make_uint2((uint32_t)lo, (uint32_t)hi);
   if (i == 0) parent[0] = 0xffffffffu;
 }
+__global__ void k_hierarchy(const uint64_t *keys, int n, uint32_t *left, uint32_t *right, uint32_t *parent,
+                            uint2 *range) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n - 1) return;
+  d_hierarchy(i, keys, n, left, right, parent, range);
+}
 
 __device__ __forceinline__ float half_area(float4 lo, float4 hi) {
   float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
@@ -216,11 +238,9 @@ __device__ __forceinline__ float half_area(float4 lo, float4 hi) {
 
 // Bottom-up refit: the second thread to reach a node owns it.  Writes the node's box and words;
 // collapses the subtree into a leaf when the SAH says so (records of a subtree are contiguous).
-__global__ void k_refit(const uint32_t *left, const uint32_t *right, const uint32_t *parent, const uint2 *range,
-                        const uint32_t *off, int n, int max_leaf, float c_trav, uint32_t *visits, float4 *nodes,
-                        float *cost, int *depth) {
-  int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n) return;
+__device__ __forceinline__ void d_refit(int j, const uint32_t *left, const uint32_t *right, const uint32_t *parent,
+                                        const uint2 *range, const uint32_t *off, int n, int max_leaf, float c_trav,
+                                        uint32_t *visits, float4 *nodes, float *cost, int *depth) {
   uint32_t cur = parent[(size_t)(n - 1) + j];
   while (cur != 0xffffffffu) {
     __threadfence();
@@ -252,6 +272,103 @@ __global__ void k_refit(const uint32_t *left, const uint32_t *right, const uint3
     nodes[2 * (size_t)cur] = lo;
     nodes[2 * (size_t)cur + 1] = hi;
     cur = parent[cur];
+  }
+}
+__global__ void k_refit(const uint32_t *left, const uint32_t *right, const uint32_t *parent, const uint2 *range,
+                        const uint32_t *off, int n, int max_leaf, float c_trav, uint32_t *visits, float4 *nodes,
+                        float *cost, int *depth) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  d_refit(j, left, right, parent, range, off, n, max_leaf, c_trav, visits, nodes, cost, depth);
+}
+
+// ---- small scenes: the whole build in ONE launch ----------------------------------------------------------------------
+// A scene of at most SMALL_MAX_SEQ records / SMALL_MAX_BP build primitives (the Cornell box, birthday, the 489 spheres of
+// scenes/spheres.cu) is built by one block of 1024 threads that runs the steps above back to back with a block barrier
+// in between — head flags + scan, boxes, Morton keys, a block-wide radix sort (stable, like the device-wide sort: equal
+// keys keep Append order), record offsets, leaf emission, Karras hierarchy, refit — and leaves the root words, SAH cost
+// and depth in `result` for ONE read-back.  Same bodies, same arithmetic: the tree is the tree of the step-per-launch
+// path bit for bit (tests/test_gpu_parity.py::test_small_scene_builder_identical).  The step-per-launch path costs
+// ~15 launches and three host round trips, which on the spheres config outlasted the 0.8 ms frame it prepares.
+constexpr int SMALL_T = 1024, SMALL_MAX_BP = SMALL_T, SMALL_MAX_SEQ = 2 * SMALL_T;
+struct SmallBuild {
+  const float4 *recs_seq;
+  const float *uv_seq;
+  int n_seq, n_bp, max_leaf;
+  float c_trav;
+  uint32_t *bp_first, *order, *off, *left, *right, *parent, *visits;
+  float4 *bp_lo, *bp_hi, *recs, *nodes;
+  uint64_t *keys;
+  uint2 *range;
+  float *uv, *cost;
+  int *depth;
+  uint32_t *result;  // [0..7] root node, [8] SAH cost (float bits), [9] depth, [10] primitives found, [11] records emitted
+};
+__global__ void __launch_bounds__(SMALL_T) k_build_small(SmallBuild a) {
+  using Scan = cub::BlockScan<uint32_t, SMALL_T>;
+  using Sort = cub::BlockRadixSort<uint64_t, SMALL_T, 1, uint32_t>;
+  __shared__ union {
+    typename Scan::TempStorage scan;
+    typename Sort::TempStorage sort;
+  } tmp;
+  __shared__ uint32_t s_bounds[6];
+  const int t = threadIdx.x, n_bp = a.n_bp;
+  // build primitives: the records that start one (two consecutive records per thread)
+  uint32_t flag[2], pos[2], found = 0;
+  for (int q = 0; q < 2; q++) flag[q] = 2 * t + q < a.n_seq ? d_head_flag(a.recs_seq, 2 * t + q) : 0u;
+  Scan(tmp.scan).ExclusiveSum(flag, pos, found);
+  if (found != (uint32_t)n_bp) {  // block-uniform; the host reports it (never seen: both counts come from one description)
+    if (t == 0) a.result[10] = found, a.result[11] = 0u;
+    return;
+  }
+  for (int q = 0; q < 2; q++)
+    if (flag[q]) a.bp_first[pos[q]] = 2 * t + q;
+  if (t < 6) s_bounds[t] = t < 3 ? 0xffffffffu : 0u;
+  __syncthreads();
+  if (t < n_bp) d_bp_bounds(t, a.recs_seq, a.bp_first, a.bp_lo, a.bp_hi, s_bounds);
+  __syncthreads();
+  // Morton order; the padding keys of the idle threads sort behind every real key (< 2^63)
+  uint64_t key[1] = {~0ull};
+  uint32_t val[1] = {0xffffffffu};
+  if (t < n_bp) {
+    key[0] = d_morton(t, a.bp_lo, a.bp_hi, s_bounds);
+    val[0] = (uint32_t)t;
+  }
+  Sort(tmp.sort).Sort(key, val);
+  __syncthreads();
+  uint32_t nrec = 0, first = 0, total = 0;
+  if (t < n_bp) {
+    a.keys[t] = key[0];
+    a.order[t] = val[0];
+    nrec = (uint32_t)__float_as_int(a.bp_lo[val[0]].w);
+  }
+  Scan(tmp.scan).ExclusiveSum(nrec, first, total);
+  if (t < n_bp) a.off[t] = first;
+  if (t == 0) a.off[n_bp] = total;
+  __syncthreads();
+  if (t < n_bp)
+    d_emit(t, a.recs_seq, a.uv_seq, a.bp_first, a.bp_lo, a.bp_hi, a.order, a.off, n_bp, a.recs, a.uv, a.nodes, a.cost,
+           a.depth);
+  if (n_bp > 1) {
+    if (t < n_bp - 1) {
+      d_hierarchy(t, a.keys, n_bp, a.left, a.right, a.parent, a.range);
+      a.visits[t] = 0u;
+    }
+    __syncthreads();
+    if (t < n_bp)
+      d_refit(t, a.left, a.right, a.parent, a.range, a.off, n_bp, a.max_leaf, a.c_trav, a.visits, a.nodes, a.cost, a.depth);
+  }
+  __syncthreads();
+  if (t == 0) {
+    const float4 lo = __ldcg(a.nodes), hi = __ldcg(a.nodes + 1);
+    a.result[0] = __float_as_uint(lo.x), a.result[1] = __float_as_uint(lo.y), a.result[2] = __float_as_uint(lo.z);
+    a.result[3] = __float_as_uint(lo.w);
+    a.result[4] = __float_as_uint(hi.x), a.result[5] = __float_as_uint(hi.y), a.result[6] = __float_as_uint(hi.z);
+    a.result[7] = __float_as_uint(hi.w);
+    a.result[8] = __float_as_uint(__ldcg(a.cost));
+    a.result[9] = (uint32_t)__ldcg(a.depth);
+    a.result[10] = found;
+    a.result[11] = total;
   }
 }
 
@@ -597,31 +714,92 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   RT_CUDA(flush());
 
   // ---- build primitives -------------------------------------------------------------------------
-  int n_bp = 0;
+  // Both counts follow from the description (a sphere / triangle / face is one primitive of one record, a
+  // parallelogram one primitive of two, the sky none): nothing is read back from the device to size the build.
+  const int n_bp = n_spheres + n_tris + n_quads;
+  const size_t n_recs_expected = (size_t)n_spheres + (size_t)n_tris + 2 * (size_t)n_quads;
   DevBuf *S = ctx->scratch;
-  if (n_seq > 0) {
-    RT_CUDA(S[1].reserve((n_seq + 1) * 4));
-    RT_CUDA(S[2].reserve((n_seq + 1) * 4));
-    k_head_flags<<<nblk(n_seq), 256, 0, st>>>(recs_seq, (int)n_seq, S[1].as<uint32_t>());
-    size_t tmp = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, tmp, S[1].as<uint32_t>(), S[2].as<uint32_t>(), (int)n_seq, st);
-    RT_CUDA(S[5].reserve(tmp));
-    RT_CUDA(cub::DeviceScan::ExclusiveSum(S[5].p, tmp, S[1].as<uint32_t>(), S[2].as<uint32_t>(), (int)n_seq, st));
-    uint32_t last_flag = 0, last_pos = 0;
-    RT_CUDA(cudaMemcpyAsync(&last_flag, S[1].as<uint32_t>() + n_seq - 1, 4, cudaMemcpyDeviceToHost, st));
-    RT_CUDA(cudaMemcpyAsync(&last_pos, S[2].as<uint32_t>() + n_seq - 1, 4, cudaMemcpyDeviceToHost, st));
-    RT_CUDA(cudaStreamSynchronize(st));
-    n_bp = (int)(last_flag + last_pos);
-  }
   size_t n_recs = 0;
   int n_nodes = 0, max_depth = 0;
   float sah = 0.f;
   uint32_t root_words[2] = {0, LEAF_FLAG};
-  if (n_bp > 0) {
-    const char *env = getenv("RT_MAX_LEAF");
-    int max_leaf = env ? std::min(std::max(1, atoi(env)), 7) : 4;
-    env = getenv("RT_SAH_CT");
-    float c_trav = env ? (float)atof(env) : 1.2f;
+  const char *env = getenv("RT_MAX_LEAF");
+  const int max_leaf = env ? std::min(std::max(1, atoi(env)), 7) : 4;
+  env = getenv("RT_SAH_CT");
+  const float c_trav = env ? (float)atof(env) : 1.2f;
+  env = getenv("RT_BUILD_SMALL");  // 0: small scenes through the step-per-launch path too (tests compare the two)
+  const bool small = n_bp > 0 && n_bp <= SMALL_MAX_BP && n_seq <= (size_t)SMALL_MAX_SEQ && !(env && atoi(env) == 0);
+  bool flat_done = false;
+  if (small) {
+    // ---- one launch (k_build_small), one read-back ----
+    n_recs = n_recs_expected;
+    n_nodes = 2 * n_bp - 1;
+    RT_CUDA(ctx->recs.reserve(n_recs * 48));
+    RT_CUDA(ctx->nodes.reserve((size_t)n_nodes * 32));
+    if (any_uv) RT_CUDA(ctx->face_uv.reserve(n_recs * 24));
+    RT_CUDA(S[0].reserve((size_t)n_nodes * 8));
+    RT_CUDA(S[2].reserve(((size_t)n_bp + 1) * 4));
+    RT_CUDA(S[3].reserve((size_t)n_bp * 4));
+    RT_CUDA(S[4].reserve(((size_t)n_bp * 2 + (size_t)n_nodes) * 4));
+    RT_CUDA(S[6].reserve((size_t)n_bp * 16));
+    RT_CUDA(S[7].reserve((size_t)n_bp * 16));
+    RT_CUDA(S[8].reserve((size_t)n_bp * 8));
+    RT_CUDA(S[9].reserve((size_t)n_bp * 4));
+    RT_CUDA(S[10].reserve(64));
+    RT_CUDA(S[11].reserve((size_t)n_bp * 12));
+    SmallBuild a;
+    a.recs_seq = recs_seq;
+    a.uv_seq = uv_seq;
+    a.n_seq = (int)n_seq;
+    a.n_bp = n_bp;
+    a.max_leaf = max_leaf;
+    a.c_trav = c_trav;
+    a.bp_first = S[3].as<uint32_t>();
+    a.order = S[9].as<uint32_t>();
+    a.off = S[2].as<uint32_t>();
+    a.left = S[4].as<uint32_t>();
+    a.right = a.left + n_bp;
+    a.parent = a.right + n_bp;
+    a.range = S[11].as<uint2>();
+    a.visits = (uint32_t *)(a.range + n_bp);
+    a.bp_lo = S[6].as<float4>();
+    a.bp_hi = S[7].as<float4>();
+    a.recs = ctx->recs.as<float4>();
+    a.nodes = ctx->nodes.as<float4>();
+    a.keys = S[8].as<uint64_t>();
+    a.uv = any_uv ? ctx->face_uv.as<float>() : nullptr;
+    a.cost = S[0].as<float>();
+    a.depth = (int *)(a.cost + n_nodes);
+    a.result = S[10].as<uint32_t>();
+    k_build_small<<<1, SMALL_T, 0, st>>>(a);
+    RT_CUDA(cudaGetLastError());
+    uint32_t res[12];
+    RT_CUDA(cudaMemcpyAsync(res, a.result, sizeof(res), cudaMemcpyDeviceToHost, st));
+    if (n_bp <= FLAT_MAX)  // the box list of rt_flat.cuh rides on the same round trip
+      RT_CUDA(cudaMemcpyAsync(ctx->flat.box, ctx->nodes.as<float4>() + 2 * (size_t)(n_bp - 1), (size_t)n_bp * 32,
+                              cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    flat_done = true;
+    if (res[10] != (uint32_t)n_bp || res[11] != (uint32_t)n_recs) {
+      set_error("rt_scene_commit: the device build found " + std::to_string(res[10]) + " primitives / " +
+                std::to_string(res[11]) + " records, the description has " + std::to_string(n_bp) + " / " +
+                std::to_string(n_recs));
+      return RT_ERR_CUDA;
+    }
+    root_words[0] = res[3];
+    root_words[1] = res[7];
+    memcpy(&sah, &res[8], 4);
+    max_depth = (int)res[9];
+  } else if (n_bp > 0) {
+    RT_CUDA(S[1].reserve((n_seq + 1) * 4));
+    RT_CUDA(S[2].reserve((n_seq + 1) * 4));
+    k_head_flags<<<nblk(n_seq), 256, 0, st>>>(recs_seq, (int)n_seq, S[1].as<uint32_t>());
+    {
+      size_t tmp = 0;
+      cub::DeviceScan::ExclusiveSum(nullptr, tmp, S[1].as<uint32_t>(), S[2].as<uint32_t>(), (int)n_seq, st);
+      RT_CUDA(S[5].reserve(tmp));
+      RT_CUDA(cub::DeviceScan::ExclusiveSum(S[5].p, tmp, S[1].as<uint32_t>(), S[2].as<uint32_t>(), (int)n_seq, st));
+    }
     // S[3] bp_first, S[6] bp_lo, S[7] bp_hi, S[8] scene bounds + keys, S[9] vals ...
     RT_CUDA(S[3].reserve((size_t)n_bp * 4));
     k_scatter_heads<<<nblk(n_seq), 256, 0, st>>>(S[1].as<uint32_t>(), S[2].as<uint32_t>(), (int)n_seq,
@@ -652,10 +830,9 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
     cub::DeviceScan::ExclusiveSum(nullptr, tmp, S[1].as<uint32_t>(), S[2].as<uint32_t>(), n_bp + 1, st);
     RT_CUDA(S[5].reserve(tmp));
     RT_CUDA(cub::DeviceScan::ExclusiveSum(S[5].p, tmp, S[1].as<uint32_t>(), S[2].as<uint32_t>(), n_bp + 1, st));
-    uint32_t total = 0;
+    uint32_t total = 0;  // checked against the description with the root read-back below
     RT_CUDA(cudaMemcpyAsync(&total, S[2].as<uint32_t>() + n_bp, 4, cudaMemcpyDeviceToHost, st));
-    RT_CUDA(cudaStreamSynchronize(st));
-    n_recs = total;
+    n_recs = n_recs_expected;
     n_nodes = 2 * n_bp - 1;
     RT_CUDA(ctx->recs.reserve(n_recs * 48));
     RT_CUDA(ctx->nodes.reserve((size_t)n_nodes * 32));
@@ -685,6 +862,11 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
     RT_CUDA(cudaMemcpyAsync(&sah, cost, 4, cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaMemcpyAsync(&max_depth, depth, 4, cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaStreamSynchronize(st));
+    if ((size_t)total != n_recs) {
+      set_error("rt_scene_commit: the device build emitted " + std::to_string(total) + " records, the description has " +
+                std::to_string(n_recs));
+      return RT_ERR_CUDA;
+    }
     // ---- large scenes: the tree above the leaves rebuilt by PLOC (RT_PLOC=0: keep the LBVH) ----
     {
       const char *ep = getenv("RT_PLOC");
@@ -808,8 +990,9 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   // box list for the flat traversal (rt_flat.cuh): the single-primitive leaf nodes k_emit wrote
   ctx->flat.n = 0;
   if (n_bp > 0 && n_bp <= FLAT_MAX) {
-    RT_CUDA(cudaMemcpy(ctx->flat.box, ctx->nodes.as<float4>() + 2 * (size_t)(n_bp - 1), (size_t)n_bp * 32,
-                       cudaMemcpyDeviceToHost));
+    if (!flat_done)
+      RT_CUDA(cudaMemcpy(ctx->flat.box, ctx->nodes.as<float4>() + 2 * (size_t)(n_bp - 1), (size_t)n_bp * 32,
+                         cudaMemcpyDeviceToHost));
     ctx->flat.n = n_bp;
     // {lo, hi} -> {centre, half extent}: the half extent covers the rounding of the centre
     for (int i = 0; i < n_bp; i++) {

@@ -305,6 +305,74 @@ def test_work_distribution_does_not_change_the_image(ctx, name, hw, spp, monkeyp
             assert st.chunk_samples == min(int(chunk), spp)
 
 
+def _mixed_small(n, seed):
+    """n primitives of all three kinds + a sky in the middle of the list (records: n/3 spheres, n/3 triangles, 2n/3 quad halves)."""
+    rng = np.random.RandomState(seed)
+    mats = [scenes._mat(abi.RT_MAT_LAMBERTIAN, (0.5, 0.5, 0.5)), scenes._mat(abi.RT_MAT_METAL, (0.7, 0.6, 0.5), fuzz=0.3),
+            scenes._mat(abi.RT_MAT_SKY)]
+    hs = []
+    for i in range(n):
+        k = i % 3
+        if k == 0:
+            hs.append(scenes._hit(abi.RT_HIT_SPHERE, i % 2, [rng.uniform(-3, 3, 3)], radius=float(rng.uniform(0.05, 0.5))))
+        elif k == 1:
+            hs.append(scenes._hit(abi.RT_HIT_TRIANGLE, i % 2, rng.uniform(-3, 3, (3, 3))))
+        else:
+            hs.append(scenes.parallelogram(rng.uniform(-3, 3, (3, 3)), i % 2))
+        if i == n // 2:
+            hs.append(scenes._hit(abi.RT_HIT_SKY, 2))
+    return abi.SceneData(np.stack(hs), np.stack(mats))
+
+
+@pytest.mark.parametrize("name", ["cornell_box", "birthday", "spheres", "one", "two", "mixed33", "mixed1024", "mixed1025",
+                                  "dup_keys"])
+def test_small_scene_builder_identical(ctx, name, monkeypatch):
+    """Scenes of at most 1024 primitives / 2048 records are built by ONE launch (k_build_small: every step of the
+    LBVH build in one block); RT_BUILD_SMALL=0 sends them through the step-per-launch path of the large scenes.  Same
+    per-element bodies, same arithmetic, a stable sort in both: the two trees must be the same tree — node count, depth
+    and SAH cost equal bit for bit, the same hits, and the same number of box and record tests on the same rays (a
+    different tree would visit different nodes).  1025 primitives take the step-per-launch path either way."""
+    cam = None
+    if name in ("cornell_box", "birthday", "spheres"):
+        s, cam = _named(name)
+    elif name == "one":
+        s = abi.SceneData(np.stack([scenes._hit(abi.RT_HIT_TRIANGLE, 0, [[-5, -5, 2], [5, -5, 2], [0, 5, 2]])]),
+                          np.stack([scenes._mat(abi.RT_MAT_LAMBERTIAN, (0.5, 0.5, 0.5))]))
+    elif name == "two":
+        s = _mixed_small(2, 4)
+    elif name == "dup_keys":  # coincident primitives: equal Morton keys, the order is the sort's stability
+        rng = np.random.RandomState(12)
+        tri = rng.uniform(-2, 2, (3, 3))
+        hs = [scenes._hit(abi.RT_HIT_TRIANGLE, 0, tri + (0.0 if i % 4 else 0.25 * (i // 4))) for i in range(40)]
+        s = abi.SceneData(np.stack(hs), np.stack([scenes._mat(abi.RT_MAT_LAMBERTIAN, (0.5, 0.5, 0.5))]))
+    else:
+        s = _mixed_small(int(name[5:]), 17)
+    lo, hi = _BOX.get(name, (-4, 4))
+    rr = ck.random_rays(30000, 9, lo, hi)
+    res = {}
+    for small in ("0", "1"):
+        monkeypatch.setenv("RT_BUILD_SMALL", small)
+        bs = ctx.commit(s)
+        if cam is not None:
+            ctx.set_camera(rt.core.camera_look_at(cam))
+        else:
+            ctx.set_camera(rt.core.camera_look_at(scenes.cornell_box()[1]))
+        hits = ctx.trace_closest(rr, mode=3)
+        hits_default = ctx.trace_closest(rr, mode=0)
+        _, _, st = ctx.render_host(27, 48, 2, seed=5, flags=abi.RT_RENDER_FUSED | abi.RT_RENDER_PROFILE)
+        res[small] = ((bs.n_prims, bs.n_nodes, bs.max_depth, np.float32(bs.sah_cost).view(np.uint32).item(), bs.n_spheres,
+                       bs.n_quads, bs.n_tris), hits, hits_default, (st.rays, st.node_visits, st.prim_tests))
+    monkeypatch.delenv("RT_BUILD_SMALL")
+    a, b = res["0"], res["1"]
+    assert a[0] == b[0], (a[0], b[0])
+    assert a[1].tobytes() == b[1].tobytes() and a[2].tobytes() == b[2].tobytes()
+    assert a[3] == b[3], (a[3], b[3])
+    o = ck.OracleScene(s)
+    want = o.trace(rr, quirks=0)
+    fields = ("t", "obj", "sub", "normal", "material")
+    assert len(ck.hits_equal(b[1], want, fields)) == 0 and len(ck.hits_equal(b[2], want, fields)) == 0
+
+
 def test_render_textured_sphere_close(ctx):
     s, cam, o = _setup(ctx, "birthday")
     H, W, spp = 54, 96, 8

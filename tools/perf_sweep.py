@@ -9,12 +9,30 @@ import torch
 rt = importlib.import_module("ray-tracing-cuda_b200")
 
 CASES = {"cornell_box": (1024, 1024, 64), "spheres": (720, 1280, 32), "bunny": (1080, 1920, 16),
-         "birthday": (1080, 1920, 32), "soup1m": (1080, 1920, 4), "soup100k": (1080, 1920, 8), "soup10m": (2160, 3840, 2), "soup1m4k": (2160, 3840, 4), "soup1m16": (1080, 1920, 16), "soup10m8": (1080, 1920, 8)}
+         "birthday": (1080, 1920, 32), "soup1m": (1080, 1920, 4), "soup100k": (1080, 1920, 8), "soup10m": (2160, 3840, 2), "soup1m4k": (2160, 3840, 4), "soup1m16": (1080, 1920, 16), "soup10m8": (1080, 1920, 8),
+         # scene classes between the named configs (the thresholds of default_trav): meshes and soups of 1 k - 100 k triangles,
+         # a Cornell box of 54 parallelograms (three more blocks: no box list above 32 primitives)
+         "bunny1k": (1080, 1920, 16), "bunny3k": (1080, 1920, 16), "bunny6k": (1080, 1920, 16), "bunny20k": (1080, 1920, 16),
+         "soup2k": (1080, 1920, 8), "soup6k": (1080, 1920, 8), "soup20k": (1080, 1920, 8), "cornell54": (1024, 1024, 64)}
 
 def scene_of(name):
     if name.startswith("soup"):
-        n = {"soup1m": 1000000, "soup100k": 100000, "soup10m": 10000000, "soup1m4k": 1000000, "soup1m16": 1000000, "soup10m8": 10000000}[name]
+        n = {"soup2k": 2000, "soup6k": 6000, "soup20k": 20000, "soup1m": 1000000, "soup100k": 100000, "soup10m": 10000000, "soup1m4k": 1000000, "soup1m16": 1000000, "soup10m8": 10000000}[name]
         return rt.scenes.soup(n)
+    if name.startswith("bunny") and name != "bunny":
+        return rt.scenes.bunny(rt.scenes.bunny_mesh(int(name[5:-1]) * 1000))
+    if name == "cornell54":
+        s, cam = rt.scenes.cornell_box()
+        rng = np.random.RandomState(4)
+        hs = list(s.hitables)
+        for b in range(6):  # six more small blocks on the floor, six parallelograms each
+            o = np.array([rng.uniform(40, 480), 0.0, rng.uniform(40, 480)])
+            e = [np.array([rng.uniform(30, 60), 0, rng.uniform(-20, 20)]), np.array([0, rng.uniform(30, 120), 0]), None]
+            e[2] = np.array([-e[0][2], 0, e[0][0]])
+            for a, b2, c in ((0, 1, 2), (1, 2, 0), (2, 0, 1)):
+                for off in (np.zeros(3), e[c]):
+                    hs.append(rt.scenes.parallelogram(np.stack([o + off, o + off + e[a], o + off + e[b2]]), 0))
+        return rt.abi.SceneData(np.stack(hs), s.materials, name="cornell54"), cam
     return rt.scenes.by_name(name)
 
 def main():
@@ -54,9 +72,9 @@ def main():
                 key = f"{name} trav={tv}" + (f" {ex[0]}={ex[1]}" if ex else "")
                 res[key] = dict(msamples=H * W * spp / best / 1e3, mrays=st.rays / best / 1e3, ms=best,
                                 nodes_per_ray=nodes / max(rays1, 1), recs_per_ray=prims / max(rays1, 1),
-                                build_ms=bs.build_ms, nodes=bs.n_nodes, depth=bs.max_depth, simt=simt)
+                                build_ms=bs.build_ms, nodes=bs.n_nodes, depth=bs.max_depth, simt=simt, sah=bs.sah_cost)
                 r = res[key]
-                print(f"{key:40s} {r['msamples']:9.1f} Msamp/s {r['mrays']:9.1f} Mrays/s {r['ms']:8.2f} ms  nodes/ray {r['nodes_per_ray']:.1f} recs/ray {r['recs_per_ray']:.1f}  build {r['build_ms']:.2f} ms depth {r['depth']} simt {r['simt']:.2f}", flush=True)
+                print(f"{key:40s} {r['msamples']:9.1f} Msamp/s {r['mrays']:9.1f} Mrays/s {r['ms']:8.2f} ms  nodes/ray {r['nodes_per_ray']:.1f} recs/ray {r['recs_per_ray']:.1f}  build {r['build_ms']:.2f} ms depth {r['depth']} sah {r['sah']:.1f}", flush=True)
     print(json.dumps(res))
 
 if __name__ == "__main__":
