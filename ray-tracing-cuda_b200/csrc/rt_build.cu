@@ -1014,7 +1014,7 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   rt_build_stats &bs = ctx->build_stats;
   // the traversal this scene renders with (RT_TRAV / RT_STRATEGY are read here, once per commit) and its tree;
   // part of the build time
-  ctx->trav = default_trav(ctx);
+  ctx->trav = default_trav(ctx, sah);
   {
     const char *env = getenv("RT_STRATEGY");
     ctx->opt_wavefront = env && strcmp(env, "wavefront") == 0;

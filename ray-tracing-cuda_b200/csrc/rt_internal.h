@@ -52,7 +52,7 @@ struct RenderCounters {  // device-side counters of one rt_render call
 struct rt_ctx;
 namespace rtc {
 void static_scratch_setup(int device);               // rt_render.cu: address of the static scratch array (rt_render_static)
-int default_trav(const rt_ctx *ctx);                  // rt_render.cu: the scene's traversal (RT_TRAV overrides), read at commit
+int default_trav(const rt_ctx *ctx, float sah_cost);  // rt_render.cu: the scene's traversal (RT_TRAV overrides), read at commit
 }  // namespace rtc
 
 struct rt_ctx {

@@ -16,23 +16,27 @@ namespace rtc {
 
 // Work distribution of one rt_render call (k_render).  A SUB-UNIT is (pixel, chunk of samples): what one lane renders
 // before it asks for more work.  An ITEM is (8x4-pixel tile, some consecutive chunks) = 32 sub-units per chunk: what a
-// warp draws from the global counter with one atomic.  The sample range is cut in two phases:
-//   phase 1 — the first ~3/4 of the samples: chunks of ch1 = 16 samples, r1 chunks per item.  Big pieces: a warp
-//             stays on its tile (its rays keep touching the same part of the tree) and the hand-out is rare;
-//   phase 2 — the rest: chunks of ch2 <= 4 samples, one chunk per item.  Small pieces: whatever the cost of a sample
-//             varies by across the image, the launch ends within a few samples' time on every SM.
+// warp draws from the global counter with one atomic.  The sample range is cut into up to PLAN_MAX PHASES of
+// decreasing item size (plan_work): big items first — a warp stays on its tile and both the per-lane hand-out and the
+// draw of a new item are rare — small items last, so that the launch ends within a few samples' time on every SM.
 // Items are numbered phase, then chunk group, then tile, so every pass sweeps the whole image and the expensive
 // tiles are spread over the launch.
+constexpr int PLAN_MAX = 4;
+struct PlanPhase {
+  uint32_t item_begin;  // first item of the phase
+  int32_t k_begin;      // first sample of the phase (absolute index)
+  int32_t ch, r;        // samples per chunk, chunks per item
+};
 struct RenderArgs {
   int32_t height, width;
   int32_t spp_begin, spp_end;
   int32_t max_depth;
   uint32_t k0, k1;
-  int32_t ch1, r1, n_chunks1, spp1;  // phase 1 (spp1 = samples it covers; 0: none)
-  int32_t ch2;                       // phase 2
+  int32_t n_phases;
+  PlanPhase phase[PLAN_MAX + 1];  // phase[n_phases] = {n_items, spp_end, -, -}: the end of the last phase
   int32_t tiles_x, n_tiles;
   uint32_t tile_stride;  // tile of the i-th item of a sweep = i * tile_stride mod n_tiles (1: raster order)
-  uint32_t n_items1, n_items;
+  uint32_t n_items;
   unsigned int *work_counter;
   long long *fixed;  // [height * width * 3] radiance sums, 2^-30 units
 };
@@ -200,6 +204,9 @@ __device__ __forceinline__ void flush_counters(RenderCounters *ctr, unsigned lon
 // Out-of-line forms of the rare steps (64-register kernels): the node step is the hot loop of a long query and must
 // not carry the registers (or the spills) of shading and camera sampling.  Everything goes in and out BY VALUE: a
 // reference parameter would pin the traversal state of the hot loop in local memory.
+#ifndef RT_WW_MINB  // resident blocks per SM of the while-while kernel (experiment builds: 8 = 64 registers, shading out of line)
+#define RT_WW_MINB 6
+#endif
 struct ShadeRet {
   RayQ ray;
   V3 T, L;
@@ -250,26 +257,31 @@ __device__ __forceinline__ void hand_out(const RenderArgs &a, WorkPool &p, bool 
         finished |= want;
         break;
       }
-      const bool p1 = it < a.n_items1;
-      const uint32_t it2 = p1 ? it : it - a.n_items1;
+      int ph = 0;
+#pragma unroll
+      for (int q = 1; q < PLAN_MAX; q++) ph += (q < a.n_phases && it >= a.phase[q].item_begin) ? 1 : 0;
+      const PlanPhase pp = a.phase[ph];
+      const uint32_t it2 = it - pp.item_begin;
       const uint32_t group = it2 / (uint32_t)a.n_tiles;
       const uint32_t tile = (uint32_t)(((unsigned long long)(it2 - group * (uint32_t)a.n_tiles) * a.tile_stride) % (uint32_t)a.n_tiles);
       p.tile_px = (int)(tile % (uint32_t)a.tiles_x) * 8;
       p.tile_py = (int)(tile / (uint32_t)a.tiles_x) * 4;
-      p.ch = p1 ? a.ch1 : a.ch2;
-      p.k0 = p1 ? a.spp_begin + (int)group * a.r1 * a.ch1 : a.spp_begin + a.spp1 + (int)group * a.ch2;
-      p.kend = p1 ? a.spp_begin + a.spp1 : a.spp_end;
+      p.ch = pp.ch;
+      p.k0 = pp.k_begin + (int)group * pp.r * pp.ch;
+      p.kend = a.phase[ph + 1].k_begin;
       p.next = 0;
-      p.end = 32u * (uint32_t)(p1 ? a.r1 : 1);
+      p.end = 32u * (uint32_t)pp.r;
     }
     const uint32_t rank = __popc(wm & lt_mask), take = min((uint32_t)__popc(wm), p.end - p.next);
     if (want && rank < take) {
       const uint32_t su = p.next + rank;
       pj = p.tile_px + (int)(su & 7u);
       pi = p.tile_py + (int)((su >> 3) & 3u);
-      if (pi < a.height && pj < a.width) {  // edge tiles: sub-units outside the image are dropped
-        k = p.k0 + (int)(su >> 5) * p.ch;
-        k_end = min(k + p.ch, p.kend);
+      const int kk = p.k0 + (int)(su >> 5) * p.ch;
+      // edge tiles: sub-units outside the image are dropped; so are the chunks of a phase's last item beyond its end
+      if (pi < a.height && pj < a.width && kk < p.kend) {
+        k = kk;
+        k_end = min(kk + p.ch, p.kend);
         pixel = (uint32_t)(pi * a.width + pj);
         want = false;
       }
@@ -709,13 +721,18 @@ int check_ready(rt_ctx *ctx, bool need_camera, const char *who) {
 
 // Traversal of the render kernel, chosen at commit (RT_TRAV overrides it for diagnostics, read once per commit).
 //   <= 32 primitives (Cornell, birthday): no tree — box list, every lane tests every box (rt_flat.cuh);
-//   <= 4096 records (spheres): binary tree, while-while loop — incoherent bounce rays in an L1-resident tree;
-//   larger (bunny, soups): binary tree, if-if loop at 64 registers with the first stack levels in shared memory.
-// Round 1 also kept an 8-wide tree for 4 k - 500 k records (bunny +13 % over the binary if-if loop of the time); with
-// the shared-memory stack the binary loop is level with it (bunny 10 208 vs 9 956 Msamples/s,
-// profiles/r02_opq_large_scene_experiments.txt) and the wide tree, its builder and its kernel are gone.
-int rtc::default_trav(const rt_ctx *ctx) {
-  int dflt = ctx->scene.n_recs <= 4096 ? 1 : 0;
+//   otherwise one binary tree, walked by
+//     the while-while loop at 80 registers when a ray's walk is short — at most 4096 records, or a tree of SAH cost
+//     below 40 (spheres 3.4, bunny 2.2, a 54-parallelogram Cornell box 18: 9 - 25 box tests per ray, L1-resident);
+//     the if-if loop at 64 registers with the first stack levels in shared memory when it is long and incoherent
+//     (random soups: SAH cost 61 at 6 k triangles, 95 at 20 k, 372 at 1 M; 38 - 275 box tests per ray, latency bound).
+// Measured per scene class (profiles/r02_z_small_builder_overhead_inbetween.txt, r02_za_trav_rule.txt): meshes of
+// 1 k - 69 k triangles prefer while-while by 16 - 25 % (bunny 10 677 -> 12 815 Msamples/s), soups of 6 k triangles
+// and more prefer if-if by 8 - 45 %; the record count alone (round 1's rule: <= 4096) put the bunny on the wrong side.
+// Round 1 also kept an 8-wide tree for 4 k - 500 k records; the binary loops are level with it
+// (profiles/r02_opq_large_scene_experiments.txt) and the wide tree, its builder and its kernel are gone.
+int rtc::default_trav(const rt_ctx *ctx, float sah_cost) {
+  int dflt = (ctx->scene.n_recs <= 4096 || sah_cost < 40.0f) ? 1 : 0;
   if (ctx->flat.n > 0) dflt = 20;
   const char *e = getenv("RT_TRAV");
   int v = e ? atoi(e) : dflt;
@@ -865,39 +882,29 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, boo
   return RT_OK;
 }
 
-// Work distribution of a k_render launch (RenderArgs), sized against a lane's share of the samples.  Measured on the
-// B200 (profiles/r02_*):
-//  * 4-sample chunks everywhere cost the uniform scenes 4-5 % (the hand-out, ~35 warp instructions, then runs in
-//    almost every iteration of a warp), so scenes whose cost per ray is BOUNDED BY CONSTRUCTION — the box list: every
-//    ray tests the same <= 32 boxes — get the two phases (Cornell 3 969 -> 4 160 Msamples/s);
+// Work distribution of a k_render launch (RenderArgs), sized against a warp's share of the samples.  Measured on the
+// B200 (profiles/r02_*; Cornell box 1024 x 1024, ms per sample-per-pixel with every item of the launch alike):
+//     4-sample chunks, 1 chunk per item   0.2723  (fixed cost of the launch 0.26 ms)
+//    16-sample chunks, 1 chunk per item   0.2672  (0.8 ms: the last items are 512 samples = 0.45 ms of a warp)
+//    16-sample chunks, 4 chunks per item  0.2600  (1.7 ms)
+// — the per-lane hand-out (~35 warp instructions) and the draw of a new item both cost, and big items leave a tail.
+//  * scenes whose cost per ray is BOUNDED BY CONSTRUCTION (the box list: every ray tests the same <= 32 boxes) get
+//    three phases: A = 16-sample chunks, rA chunks per item; B = 16-sample chunks, one per item, long enough to
+//    absorb the last items of A (3 of them per warp); C = chunks of <= 4 samples, long enough to absorb the last
+//    items of B.  Round 2's first plan was A + C with C = 1/4 of the samples;
 //  * behind a tree the cost of a sample is unbounded in practice: the bunny frame has 8x4 tiles whose rays need 40x the
 //    box tests of the average mesh tile (644 against 14.7 per ray), one such tile as an 80-samples-per-pixel item is
 //    22 ms on one warp, and it held the launch for 39 % of its time (profiles/r02_i_bunny_two_phase_ncu_summary.txt:
-//    one SM active for 130.7 M cycles, the others for 88-90 M).  Tree scenes are therefore all phase 2: 4-sample
+//    one SM active for 130.7 M cycles, the others for 88-90 M).  Tree scenes are therefore all phase C: 4-sample
 //    chunks, one chunk per item (bunny 7 423 -> 10 222; the 1 M soup pays 5 % for the lost tile locality, 494 -> 468);
 //  * a launch with little work per lane (spheres 400x225x16: 13 samples) uses 1-sample chunks.
-// RT_CHUNK / RT_ITEM_CHUNKS (diagnostics, tests): phase 1 with that chunk size and that many chunks per item over all
-// whole items, the remainder in phase 2 with the same chunk size.
+// Diagnostics / tests: RT_PLAN="16x4:64,16x1:48,4x1" (chunk x chunks-per-item : samples, the last phase takes the
+// rest); RT_CHUNK / RT_ITEM_CHUNKS: one phase with that chunk size and that many chunks per item over all whole
+// items, the remainder with the same chunk size, one chunk per item.
 static void plan_work(const rt_ctx *ctx, RenderArgs &a, int minb, bool bounded_cost) {
-  const long long lanes = (long long)ctx->n_sm * minb * 128;
-  const long long spp = a.spp_end - a.spp_begin;
-  const long long per_lane = std::max<long long>(1, (long long)a.height * a.width * spp / lanes);
-  const char *ec = getenv("RT_CHUNK"), *ei = getenv("RT_ITEM_CHUNKS");
-  long long ch1 = 16, r1 = std::min<long long>(std::max<long long>(per_lane / 1024, 1), 16), spp1 = 0;
-  long long ch2 = std::min<long long>(std::max<long long>(per_lane / 64, 1), 4);
-  if (ec) {
-    ch1 = ch2 = std::min<long long>(std::max<long long>(atoll(ec), 1), 16);
-    r1 = std::min<long long>(std::max<long long>(ei ? atoll(ei) : 1, 1), 16);
-    spp1 = r1 > 1 ? spp / (ch1 * r1) * (ch1 * r1) : 0;
-  } else if (bounded_cost && per_lane >= 1024 && spp >= 64) {
-    spp1 = spp * 3 / 4 / (ch1 * r1) * (ch1 * r1);
-  }
-  ch2 = std::min<long long>(ch2, std::max<long long>(spp, 1));
-  a.ch1 = (int)ch1;
-  a.r1 = (int)r1;
-  a.spp1 = (int)spp1;
-  a.n_chunks1 = (int)(spp1 / ch1);
-  a.ch2 = (int)ch2;
+  const long long lanes = (long long)ctx->n_sm * minb * 128, warps = lanes / 32;
+  const long long spp = a.spp_end - a.spp_begin, px = (long long)a.height * a.width;
+  const long long per_lane = std::max<long long>(1, px * spp / lanes);
   a.tiles_x = (a.width + 7) / 8;
   a.n_tiles = a.tiles_x * ((a.height + 3) / 4);
   {  // RT_TILE_ORDER (experiment): 0 raster (default), 1 golden-ratio stride (heavy image regions spread over a sweep)
@@ -910,8 +917,78 @@ static void plan_work(const rt_ctx *ctx, RenderArgs &a, int minb, bool bounded_c
       a.tile_stride = (uint32_t)std::max<long long>(st, 1);
     }
   }
-  a.n_items1 = (uint32_t)(spp1 / (ch1 * r1) * a.n_tiles);
-  a.n_items = a.n_items1 + (uint32_t)((spp - spp1 + ch2 - 1) / ch2 * a.n_tiles);
+  struct P { long long ch, r, n; };  // n: samples of the phase
+  P ph[PLAN_MAX];
+  int np = 0;
+  auto clampll = [](long long v, long long lo, long long hi) { return std::min(std::max(v, lo), hi); };
+  const long long ch_small = clampll(per_lane / 64, 1, 4);
+  const char *ep = getenv("RT_PLAN"), *ec = getenv("RT_CHUNK"), *ei = getenv("RT_ITEM_CHUNKS");
+  if (ep && *ep) {
+    long long left = spp;
+    const char *q = ep;
+    while (*q && np < PLAN_MAX && left > 0) {
+      char *e = nullptr;
+      long long ch = strtoll(q, &e, 10), r = 1, n = left;
+      if (e == q) break;  // not a number
+      if (*e == 'x') r = strtoll(e + 1, &e, 10);
+      if (*e == ':') n = clampll(strtoll(e + 1, &e, 10), 0, left);
+      q = *e == ',' ? e + 1 : e;
+      if (*q == 0 || np == PLAN_MAX - 1) n = left;  // the last phase takes the rest
+      if (n > 0) {
+        ph[np++] = {clampll(ch, 1, 64), clampll(r, 1, 64), n};
+        left -= n;
+      }
+    }
+    if (left > 0) {
+      if (np == 0) ph[np++] = {ch_small, 1, left};
+      else ph[np - 1].n += left;
+    }
+  } else if (ec) {
+    const long long ch = std::min(clampll(atoll(ec), 1, 16), std::max<long long>(spp, 1)), r = clampll(ei ? atoll(ei) : 1, 1, 16);
+    const long long n1 = r > 1 ? spp / (ch * r) * (ch * r) : 0;
+    if (n1 > 0) ph[np++] = {ch, r, n1};
+    if (spp - n1 > 0) ph[np++] = {ch, 1, spp - n1};
+  } else if (bounded_cost && per_lane >= 512 && spp >= 64) {
+    // Geometric cascade: 16-sample chunks in items of r, r/4, 1 chunks, then chunks of ch_small.  A phase takes as
+    // many whole sweeps of the image as leave, after it, the samples that absorb its tail: 3 of its items per warp
+    // (spp_for).  r starts at 1/12 of a warp's share of the launch (<= 32).  Cornell 1024 spp: 16x32:512, 16x8:384,
+    // 16x1:112, 4x1:16 — the best of the plans measured (profiles/r02_zb_plan_sweep.txt), 262.2 ms against 266.8 ms
+    // for round 2's first plan (16x9:720, 4x1:304); at 128 spp (the 8-GPU share) 16x6:96, 16x1:16, 4x1:16.
+    auto spp_for = [&](long long s) { return (s * warps + px - 1) / px; };  // samples per pixel = s samples per warp
+    const long long nC = std::max<long long>(2 * ch_small, (spp_for(3 * 512) + ch_small - 1) / ch_small * ch_small);
+    long long left = spp, r = clampll(per_lane / 192, 1, 32);
+    while (np < PLAN_MAX - 1 && left > nC) {
+      const long long reserve = r == 1 ? nC : std::max(nC, spp_for(3 * 512 * r));
+      const long long n = left > reserve ? (left - reserve) / (16 * r) * (16 * r) : 0;
+      if (n > 0) {
+        ph[np++] = {16, r, n};
+        left -= n;
+        if (r == 1) break;
+        r = r >= 16 ? r / 4 : 1;
+      } else {
+        if (r == 1) break;
+        r = r > 2 ? r / 2 : 1;  // the sweep does not fit: smaller items
+      }
+    }
+    ph[np++] = {ch_small, 1, left};
+  } else {
+    ph[np++] = {std::min<long long>(ch_small, std::max<long long>(spp, 1)), 1, spp};
+  }
+  long long k = a.spp_begin, item = 0;
+  a.n_phases = np;
+  for (int i = 0; i < np; i++) {
+    a.phase[i].item_begin = (uint32_t)item;
+    a.phase[i].k_begin = (int32_t)k;
+    a.phase[i].ch = (int32_t)ph[i].ch;
+    a.phase[i].r = (int32_t)ph[i].r;
+    const long long per_item = ph[i].ch * ph[i].r;
+    item += (ph[i].n + per_item - 1) / per_item * a.n_tiles;
+    k += ph[i].n;
+  }
+  a.phase[np].item_begin = (uint32_t)item;
+  a.phase[np].k_begin = a.spp_end;
+  a.phase[np].ch = a.phase[np].r = 1;
+  a.n_items = (uint32_t)item;
 }
 
 // Renders the samples of `p` into the fixed-point sums `fixed` (added).
@@ -940,7 +1017,7 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
     const int trav = ctx->trav;
     // resident blocks per SM the kernel is compiled for (register budget): 6 (80 registers) for the cache-resident
     // scenes (box list, while-while), 8 (64 registers) for the if-if loop of large scenes, which is latency bound
-    const int minb = trav == 0 ? 8 : 6;
+    const int minb = trav == 0 ? 8 : (trav == 1 ? RT_WW_MINB : 6);
     plan_work(ctx, a, minb, trav == 20);
     const int grid = ctx->n_sm * minb;
 #define RT_LAUNCH(T, M, ...)                                                                             \
@@ -956,7 +1033,7 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
     if (trav == 20) {
       RT_LAUNCH(20, 6, ctx->flat)
     } else if (trav == 1) {
-      RT_LAUNCH(1, 6)
+      RT_LAUNCH(1, RT_WW_MINB)
     } else {
       RT_LAUNCH(0, 8)
     }
@@ -970,7 +1047,7 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
   }
   ctx->last_iterations = iterations;
   ctx->last_launches = launches;
-  ctx->last_chunk = a.spp1 > 0 ? a.ch1 : a.ch2;
+  ctx->last_chunk = a.phase[0].ch;
   ctx->last_items = a.n_items;
   (void)stats;
   return RT_OK;
@@ -1116,7 +1193,7 @@ extern "C" int rt_render_static(rt_ctx *ctx, const rt_render_params *p, float *d
     a.fixed = sums;
     a.work_counter = reinterpret_cast<unsigned int *>(ctr + 1);
     const int trav = ctx->trav;
-    const int minb = trav == 0 ? 8 : 6;
+    const int minb = trav == 0 ? 8 : (trav == 1 ? RT_WW_MINB : 6);
     plan_work(ctx, a, minb, trav == 20);
     const int grid = ctx->n_sm * minb;
     const bool sph = ctx->scene.has_spheres != 0;
@@ -1128,7 +1205,7 @@ extern "C" int rt_render_static(rt_ctx *ctx, const rt_render_params *p, float *d
     if (trav == 20) {
       RT_LAUNCH_STATIC(20, 6, ctx->flat)
     } else if (trav == 1) {
-      RT_LAUNCH_STATIC(1, 6)
+      RT_LAUNCH_STATIC(1, RT_WW_MINB)
     } else {
       RT_LAUNCH_STATIC(0, 8)
     }

@@ -303,6 +303,17 @@ def test_work_distribution_does_not_change_the_image(ctx, name, hw, spp, monkeyp
         assert st.kernel_launches == 1 and st.work_items > 0
         if chunk:
             assert st.chunk_samples == min(int(chunk), spp)
+    monkeypatch.delenv("RT_CHUNK", raising=False)
+    monkeypatch.delenv("RT_ITEM_CHUNKS", raising=False)
+    # explicit phase lists (chunk x chunks-per-item : samples): ragged last items inside a phase, four phases, a phase
+    # list that stops short of / overshoots the sample range
+    for plan in ("4x2:6,3x3:1,2x1", "16x4", "2x3:4,1x1:1,5x2:2,3x1", "1x64:3,4x1", "8x1:1000"):
+        monkeypatch.setenv("RT_PLAN", plan)
+        st = ctx.render_fixed_device(q.data_ptr(), H, W, spp, 0, seed=77, flags=abi.RT_RENDER_CLEAR)
+        torch.cuda.synchronize()
+        assert np.array_equal(q.cpu().numpy(), want), plan
+        assert (st.samples, st.rays, st.rays_ref_equiv) == tuple(int(x) for x in cnt), plan
+    monkeypatch.delenv("RT_PLAN")
 
 
 def _mixed_small(n, seed):

@@ -6,6 +6,7 @@
 #   smoke                        __graft_entry__.smoke()
 #   bench                        the default bench line  -> gpurun_out/<tag>_bench_default.json
 #   w:<workload>[:ENV=V,...]     one workload alone      -> gpurun_out/<tag>_<workload>[_ENV=V...].json, one summary line
+#   env:VAR=value / unset:VAR    set / clear a variable for the following steps (values may hold ':' and ',')
 #   lib:<path.so>                the following steps load this build of the core (RT_CORE_LIB; experiment builds)
 #   ncu:<workload>:<spp>         ncu --set full of k_render on one launch -> gpurun_out/<tag>_<workload>.ncu-rep
 #   launches                     ncu launch list of the default bench     -> gpurun_out/<tag>_launches.csv
@@ -30,11 +31,13 @@ for step in "$@"; do
     smoke) timeout 300 python __graft_entry__.py smoke 2>&1 | tail -1;;
     bench) ( time timeout 900 python bench.py > gpurun_out/${tag}_bench_default.json 2> gpurun_out/${tag}_bench_default.err ) 2>&1 | grep real
       line gpurun_out/${tag}_bench_default.json default;;
+    env:*) export "${step#env:}"; ENVTAG="${ENVTAG} ${step#env:}"; echo "export ${step#env:}";;
+    unset:*) unset "${step#unset:}"; ENVTAG=""; echo "unset ${step#unset:}";;
     lib:*) export RT_CORE_LIB=$PWD/${step#lib:}; echo "RT_CORE_LIB=$RT_CORE_LIB";;
     w:*) IFS=: read -r _ w envs <<< "$step"
-      out=gpurun_out/${tag}_${w}${envs:+_${envs//,/_}}${RT_CORE_LIB:+_$(basename $RT_CORE_LIB .so)}.json
+      n=$((n + 1)); out=gpurun_out/${tag}_${n}_${w}${envs:+_${envs//,/_}}${RT_CORE_LIB:+_$(basename $RT_CORE_LIB .so)}.json
       ( [ -n "$envs" ] && export ${envs//,/ }; timeout 600 python bench.py --workload $w --no-cpu-baseline --steps 3 --warmup 3 > $out 2> ${out%.json}.err )
-      line $out "$w ${envs} ${RT_CORE_LIB:+$(basename $RT_CORE_LIB .so)}";;
+      line $out "$w ${envs}${ENVTAG} ${RT_CORE_LIB:+$(basename $RT_CORE_LIB .so)}";;
     ncu:*) IFS=: read -r _ w spp <<< "$step"
       timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_render -c 1 -f -o gpurun_out/${tag}_$w \
         python bench.py --workload $w --spp $spp --no-cpu-baseline --steps 1 --warmup 0 > gpurun_out/${tag}_ncu_$w.log 2>&1
