@@ -72,7 +72,7 @@ extern "C" int rt_ctx_destroy(rt_ctx *c) {
   for (DevBuf *b : bufs) b->release();
   for (DevBuf &b : c->scratch) b.release();
   for (DevBuf &b : c->wf) b.release();
-  for (void *p : c->tex_allocs) cudaFree(p);
+  for (DevBuf &b : c->tex_allocs) b.release();
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   if (c->ev2) cudaEventDestroy(c->ev2);

@@ -563,8 +563,9 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
   RT_CUDA(cudaMemcpyAsync(ctx->mats.p, hm.data(), hm.size() * sizeof(DMaterial), cudaMemcpyHostToDevice, st));
 
   // ---- textures --------------------------------------------------------------------------------
-  for (void *p : ctx->tex_allocs) cudaFree(p);
-  ctx->tex_allocs.clear();
+  // texel buffers are kept per texture slot and only grow: a re-commit of the same scene (every frame of a caller that
+  // rebuilds per frame, every e2e step of bench.py) neither frees nor allocates
+  if ((int)ctx->tex_allocs.size() < d->n_textures) ctx->tex_allocs.resize(d->n_textures);
   std::vector<DTexture> ht(std::max(d->n_textures, 1));
   for (int i = 0; i < d->n_textures; i++) {
     const rt_texture &t = d->textures[i];
@@ -572,10 +573,9 @@ extern "C" int rt_scene_commit(rt_ctx *ctx, const rt_scene_desc *d, rt_build_sta
       set_error("rt_scene_commit: bad texture");
       return RT_ERR_INVALID;
     }
-    void *p = nullptr;
     size_t bytes = (size_t)t.pitch_bytes * t.height;
-    RT_CUDA(cudaMalloc(&p, bytes));
-    ctx->tex_allocs.push_back(p);
+    RT_CUDA(ctx->tex_allocs[i].reserve(bytes));
+    void *p = ctx->tex_allocs[i].p;
     RT_CUDA(cudaMemcpyAsync(p, t.h_rgba, bytes, cudaMemcpyHostToDevice, st));
     ht[i].rgba = (const uint8_t *)p;
     ht[i].height = t.height;

@@ -67,7 +67,7 @@ struct rt_ctx {
   rt_camera camera_host{};
   // scene storage
   rtc::DevBuf nodes, nodes_ploc, recs, recs_seq, face_uv, face_uv_seq, mats, textures, tex_pixels;
-  std::vector<void *> tex_allocs;
+  std::vector<rtc::DevBuf> tex_allocs;  // texel storage, one buffer per texture slot, reused across commits
   // build scratch
   rtc::DevBuf scratch[12];
   // render scratch
