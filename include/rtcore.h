@@ -284,6 +284,16 @@ int rt_render_host(rt_ctx *ctx, const rt_render_params *params, float *h_accum_r
 /* Replaces GetWorkload (utils.cu:111-113): samples of rank `rank`, and its first global index. */
 int rt_get_workload(int rank, int world_size, int spp, int *spp_begin /*nullable*/);
 
+/* The work plan of a path-kernel launch as data (no device needed): how the samples
+ * [spp_begin, spp_begin + spp_count) of a height x width frame are cut into phases of (chunk, chunks per item) for a grid
+ * of n_sm x blocks_per_sm blocks.  Replaces, as far as anything does, the fixed pixel -> thread map of the PathTracing
+ * launch (utils.cu:158-162, ray_tracing.cu:61-64); exists for diagnostics and the CPU tests of the plan arithmetic.
+ * phases = 5 x 4 int32: {first item, first sample, samples per chunk, chunks per item} per phase, closed by
+ * {items of the launch, spp_begin + spp_count, 1, 1}.  Honours RT_PLAN / RT_CHUNK / RT_ITEM_CHUNKS like rt_render.
+ * Returns the number of phases (1..4) or a negative RT_ERR_*. */
+int rt_work_plan(int n_sm, int blocks_per_sm, int height, int width, int spp_begin, int spp_count,
+                 int bounded_cost, int32_t *phases, int32_t *n_tiles /*nullable*/);
+
 /* Replaces D2H + MPI_Reduce in GatherImageData (utils.cu:115-125,232-238): in-place SUM of the
  * accumulation buffers of all ranks to `root` with one ncclReduce on `stream`.
  * `nccl_comm` is an ncclComm_t passed as void*. */

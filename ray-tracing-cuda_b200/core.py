@@ -51,6 +51,7 @@ def lib():
     L.rt_reduce_fixed.argtypes = [vp, vp, vp, i64, C.c_int, vp]
     L.rt_render_host.argtypes = [vp, C.POINTER(abi.RtRenderParams), vp, vp, C.POINTER(abi.RtRenderStats)]
     L.rt_get_workload.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]
+    L.rt_work_plan.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.POINTER(C.c_int32)]
     L.rt_reduce.argtypes = [vp, vp, vp, i64, C.c_int, vp]
     L.rt_peer_frame_create.argtypes = [vp, C.c_int, C.c_int, vp]
     L.rt_peer_frame_open.argtypes = [vp, C.c_int, C.c_int, vp]
@@ -88,6 +89,18 @@ def get_workload(rank, world_size, spp):
     b = C.c_int()
     n = lib().rt_get_workload(rank, world_size, spp, C.byref(b))
     return n, b.value
+
+
+def work_plan(n_sm, blocks_per_sm, height, width, spp_begin, spp_count, bounded_cost):
+    """rt_work_plan: (phases [(first item, first sample, samples per chunk, chunks per item)], items of the launch, tiles)."""
+    ph = np.zeros((5, 4), np.int32)
+    nt = C.c_int32()
+    n = lib().rt_work_plan(n_sm, blocks_per_sm, height, width, spp_begin, spp_count, int(bounded_cost), ph.ctypes.data,
+                           C.byref(nt))
+    if n < 0:
+        _check(n)
+    assert tuple(ph[n, 1:]) == (spp_begin + spp_count, 1, 1)
+    return [tuple(int(x) for x in ph[i]) for i in range(n)], int(ph[n, 0]), nt.value
 
 
 class Context:

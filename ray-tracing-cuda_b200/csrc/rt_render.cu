@@ -901,8 +901,8 @@ static int render_wavefront(rt_ctx *ctx, const RenderArgs &a, bool stats_on, boo
 // Diagnostics / tests: RT_PLAN="16x4:64,16x1:48,4x1" (chunk x chunks-per-item : samples, the last phase takes the
 // rest); RT_CHUNK / RT_ITEM_CHUNKS: one phase with that chunk size and that many chunks per item over all whole
 // items, the remainder with the same chunk size, one chunk per item.
-static void plan_work(const rt_ctx *ctx, RenderArgs &a, int minb, bool bounded_cost) {
-  const long long lanes = (long long)ctx->n_sm * minb * 128, warps = lanes / 32;
+static void plan_work(int n_sm, RenderArgs &a, int minb, bool bounded_cost) {
+  const long long lanes = (long long)n_sm * minb * 128, warps = lanes / 32;
   const long long spp = a.spp_end - a.spp_begin, px = (long long)a.height * a.width;
   const long long per_lane = std::max<long long>(1, px * spp / lanes);
   a.tiles_x = (a.width + 7) / 8;
@@ -991,6 +991,34 @@ static void plan_work(const rt_ctx *ctx, RenderArgs &a, int minb, bool bounded_c
   a.n_items = (uint32_t)item;
 }
 
+// The plan as data (diagnostics and the CPU tests of the plan arithmetic; no device needed): what a k_render launch of
+// this shape would be handed.  phases[i] = {first item, first sample, samples per chunk, chunks per item}; entry
+// n_phases closes the last phase ({items of the launch, spp_begin + spp_count, -, -}).
+extern "C" int rt_work_plan(int n_sm, int blocks_per_sm, int height, int width, int spp_begin, int spp_count,
+                            int bounded_cost, int32_t *phases /* [5][4] */, int32_t *n_tiles) {
+  if (n_sm <= 0 || blocks_per_sm <= 0 || height <= 0 || width <= 0 || spp_begin < 0 || spp_count <= 0 || !phases ||
+      (int64_t)height * width > 0x3fffffff || (int64_t)spp_begin + spp_count > 0x7fffffff) {
+    set_error("rt_work_plan: bad argument");
+    return RT_ERR_INVALID;
+  }
+  RenderArgs a;
+  memset(&a, 0, sizeof(a));
+  a.height = height;
+  a.width = width;
+  a.spp_begin = spp_begin;
+  a.spp_end = spp_begin + spp_count;
+  plan_work(n_sm, a, blocks_per_sm, bounded_cost != 0);
+  for (int i = 0; i <= PLAN_MAX; i++) {
+    const bool used = i <= a.n_phases;
+    phases[4 * i + 0] = used ? (int32_t)a.phase[i].item_begin : 0;
+    phases[4 * i + 1] = used ? a.phase[i].k_begin : 0;
+    phases[4 * i + 2] = used ? a.phase[i].ch : 0;
+    phases[4 * i + 3] = used ? a.phase[i].r : 0;
+  }
+  if (n_tiles) *n_tiles = a.n_tiles;
+  return a.n_phases;
+}
+
 // Renders the samples of `p` into the fixed-point sums `fixed` (added).
 static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *fixed, rt_render_stats *stats,
                              cudaStream_t st, bool record_begin) {
@@ -1018,7 +1046,7 @@ static int render_into_fixed(rt_ctx *ctx, const rt_render_params *p, long long *
     // resident blocks per SM the kernel is compiled for (register budget): 6 (80 registers) for the cache-resident
     // scenes (box list, while-while), 8 (64 registers) for the if-if loop of large scenes, which is latency bound
     const int minb = trav == 0 ? 8 : (trav == 1 ? RT_WW_MINB : 6);
-    plan_work(ctx, a, minb, trav == 20);
+    plan_work(ctx->n_sm, a, minb, trav == 20);
     const int grid = ctx->n_sm * minb;
 #define RT_LAUNCH(T, M, ...)                                                                             \
   if (stats_on && sph)                                                                                   \
@@ -1194,7 +1222,7 @@ extern "C" int rt_render_static(rt_ctx *ctx, const rt_render_params *p, float *d
     a.work_counter = reinterpret_cast<unsigned int *>(ctr + 1);
     const int trav = ctx->trav;
     const int minb = trav == 0 ? 8 : (trav == 1 ? RT_WW_MINB : 6);
-    plan_work(ctx, a, minb, trav == 20);
+    plan_work(ctx->n_sm, a, minb, trav == 20);
     const int grid = ctx->n_sm * minb;
     const bool sph = ctx->scene.has_spheres != 0;
 #define RT_LAUNCH_STATIC(T, M, ...)                                                                      \

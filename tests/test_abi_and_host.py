@@ -57,6 +57,69 @@ def test_get_workload_matches_reference_formula():
                 assert [n for n, _ in parts] == [ck.ref_lib().ref_get_workload(r, ws, spp) for r in range(ws)]
 
 
+def _samples_of_plan(phases, n_items, n_tiles, spp_begin, spp_end):
+    """What hand_out (rt_render.cu) makes of a plan, for ONE pixel of one tile: the sample ranges its sub-units cover.
+    Item it of phase p: group = (it - first item) // tiles, sample k0 = first sample + group * r * ch; chunk c of the
+    item covers [k0 + c * ch, min(k0 + (c + 1) * ch, end of the phase)) and is dropped when it starts at or beyond that
+    end."""
+    cover = []
+    bounds = [p[0] for p in phases] + [n_items]
+    ends = [p[1] for p in phases[1:]] + [spp_end]
+    for p, (first_item, k_begin, ch, r) in enumerate(phases):
+        n_it = bounds[p + 1] - first_item
+        assert n_it % n_tiles == 0
+        for group in range(n_it // n_tiles):
+            k0 = k_begin + group * r * ch
+            for c in range(r):
+                kk = k0 + c * ch
+                if kk < ends[p]:
+                    cover.append((kk, min(kk + ch, ends[p])))
+    return cover
+
+
+def test_work_plan_covers_every_sample_once(monkeypatch):
+    """The work plan of a path-kernel launch (rt_work_plan: the host arithmetic behind rt_render's phases of
+    (chunk, chunks per item)) hands out every sample of the range exactly once, for the BASELINE frames, one GPU's share
+    of an 8-GPU run, ragged sample counts, a non-zero first sample, both scene classes, and explicit RT_PLAN /
+    RT_CHUNK lists (ragged last items inside a phase, lists that stop short or overshoot)."""
+    for v in ("RT_PLAN", "RT_CHUNK", "RT_ITEM_CHUNKS"):
+        monkeypatch.delenv(v, raising=False)
+    cases = [(1024, 1024, 0, 1024, 1), (1024, 1024, 896, 128, 1), (1080, 1920, 0, 512, 1), (1080, 1920, 64, 64, 1),
+             (225, 400, 0, 16, 0), (1080, 1920, 0, 256, 0), (2160, 3840, 0, 64, 0), (67, 125, 3, 37, 1), (128, 128, 0, 4096, 1),
+             (1024, 1024, 0, 1000, 1), (1024, 1024, 0, 63, 1), (33, 65, 0, 1, 1), (1024, 1024, 5, 777, 1)]
+    envs = [{}, {"RT_PLAN": "4x2:6,3x3:1,2x1"}, {"RT_PLAN": "16x4"}, {"RT_PLAN": "2x3:4,1x1:1,5x2:2,3x1"},
+            {"RT_PLAN": "1x64:3,4x1"}, {"RT_PLAN": "8x1:100000"}, {"RT_PLAN": "garbage"}, {"RT_CHUNK": "3", "RT_ITEM_CHUNKS": "5"},
+            {"RT_CHUNK": "16"}]
+    seen_cascade = False
+    for env in envs:
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        for (H, W, b, n, bounded) in (cases if not env else cases[:2] + cases[7:8] + cases[11:]):
+            for minb in (6, 8):
+                phases, n_items, n_tiles = rt.core.work_plan(148, minb, H, W, b, n, bounded)
+                assert n_tiles == ((W + 7) // 8) * ((H + 3) // 4)
+                assert 1 <= len(phases) <= 4 and phases[0][0] == 0 and phases[0][1] == b
+                assert all(p[2] >= 1 and p[3] >= 1 for p in phases)
+                cover = sorted(_samples_of_plan(phases, n_items, n_tiles, b, b + n))
+                assert cover[0][0] == b and cover[-1][1] == b + n, (env, H, W, b, n, phases)
+                assert all(cover[i][1] == cover[i + 1][0] for i in range(len(cover) - 1)), (env, H, W, b, n, phases)
+                if not env and bounded and n >= 64 and H * W * n // (148 * minb * 128) >= 512:
+                    # the geometric cascade of the box-list scenes: item sizes decrease from phase to phase
+                    sizes = [p[2] * p[3] for p in phases]
+                    assert sizes == sorted(sizes, reverse=True) and len(phases) >= 2 and sizes[-1] <= 4 and sizes[0] >= 16
+                    seen_cascade = True
+                if not env and not bounded:
+                    assert len(phases) == 1 and phases[0][3] == 1 and phases[0][2] <= 4
+        for k in env:
+            monkeypatch.delenv(k)
+    assert seen_cascade
+    # Cornell at 1024 spp and at one GPU's share of an 8-GPU run: the plans DESIGN.md quotes
+    assert [(p[2], p[3]) for p in rt.core.work_plan(148, 6, 1024, 1024, 0, 1024, 1)[0]] == [(16, 32), (16, 8), (16, 1), (4, 1)]
+    assert [(p[2], p[3]) for p in rt.core.work_plan(148, 6, 1024, 1024, 0, 128, 1)[0]] == [(16, 6), (16, 1), (4, 1)]
+    with pytest.raises(Exception):
+        rt.core.work_plan(148, 6, 0, 10, 0, 1, 1)
+
+
 def test_philox4x32_10_known_answers():
     """Random123 kat_vectors for philox4x32-10."""
     lib = ck.oracle_lib()
