@@ -13,7 +13,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pkg = importlib.import_module("ray-tracing-cuda_b200")
 abi = pkg.abi
 
-_ORACLE = os.path.join(ROOT, "oracle", "librt_oracle.so")
+# RT_ORACLE_LIB: another build of the same restatement (tools/sanitize_oracle.sh: the ASan + UBSan build)
+_ORACLE = os.environ.get("RT_ORACLE_LIB") or os.path.join(ROOT, "oracle", "librt_oracle.so")
 _REF = os.path.join(ROOT, "oracle", "_ref", "libref_host.so")
 
 
