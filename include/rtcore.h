@@ -105,7 +105,8 @@ typedef struct rt_camera {
 
 typedef struct rt_scene_desc {
   const rt_hitable *hitables;
-  int32_t n_hitables; /* <= 1024 after grouping, as HitableList::kMaxHitables (hitable_list.cuh:10) */
+  int32_t n_hitables; /* the reference's HitableList holds at most 1024 (hitable_list.cuh:10; the scene API's Append
+                         enforces it); rt_scene_commit itself accepts any count whose records fit 2^29 */
   const rt_material *materials;
   int32_t n_materials;
   const rt_mesh *meshes;
